@@ -1,0 +1,122 @@
+// common.cuh — shared helpers for libexg.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include "../../include/exg.h"
+
+#define EXG_WARP 32
+
+// ---------------------------------------------------------------- error plumbing
+void exg_set_error(const char* fmt, ...);
+void exg_count_launch(int n = 1);
+
+#define EXG_CHECK_ARG(cond, ...)                       \
+  do {                                                 \
+    if (!(cond)) {                                     \
+      exg_set_error(__VA_ARGS__);                      \
+      return EXG_EINVAL;                               \
+    }                                                  \
+  } while (0)
+
+#define EXG_LAUNCH_CHECK(name)                                              \
+  do {                                                                      \
+    cudaError_t e__ = cudaGetLastError();                                   \
+    if (e__ != cudaSuccess) {                                               \
+      exg_set_error("%s: launch failed: %s", name, cudaGetErrorString(e__)); \
+      return (int)e__;                                                      \
+    }                                                                       \
+    exg_count_launch();                                                     \
+  } while (0)
+
+#define EXG_CUDA(call)                                                           \
+  do {                                                                           \
+    cudaError_t e__ = (call);                                                    \
+    if (e__ != cudaSuccess) {                                                    \
+      exg_set_error("%s failed: %s", #call, cudaGetErrorString(e__));            \
+      return (int)e__;                                                           \
+    }                                                                            \
+  } while (0)
+
+static inline bool exg_valid_dtype(int d) { return d == EXG_F32 || d == EXG_BF16; }
+static inline size_t exg_dtype_size(int d) { return d == EXG_F32 ? 4 : 2; }
+
+// ---------------------------------------------------------------- device helpers
+__device__ __forceinline__ long exg_map_row(const exg_rowmap& m, long r) {
+  return (r / m.group) * m.group_stride + (r % m.group) + m.offset;
+}
+
+__device__ __forceinline__ float bf16_bits_to_float(uint16_t b) {
+  return __uint_as_float(((uint32_t)b) << 16);
+}
+__device__ __forceinline__ uint16_t float_to_bf16_bits(float f) {
+  __nv_bfloat16 h = __float2bfloat16_rn(f);
+  return *reinterpret_cast<uint16_t*>(&h);
+}
+
+// Load 4 consecutive elements (element index `i`, multiple of 4) as float4 from a dtype-tagged buffer.
+__device__ __forceinline__ float4 load4(const void* p, int dtype, long i) {
+  if (dtype == EXG_F32) {
+    return *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + i);
+  } else {
+    uint2 u = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint16_t*>(p) + i);
+    float4 r;
+    r.x = __uint_as_float(u.x << 16);
+    r.y = __uint_as_float(u.x & 0xffff0000u);
+    r.z = __uint_as_float(u.y << 16);
+    r.w = __uint_as_float(u.y & 0xffff0000u);
+    return r;
+  }
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ void store4(void* p, int dtype, long i, float4 v) {
+  if (dtype == EXG_F32) {
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p) + i) = v;
+  } else {
+    uint2 u;
+    u.x = pack_bf16x2(v.x, v.y);
+    u.y = pack_bf16x2(v.z, v.w);
+    *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(p) + i) = u;
+  }
+}
+__device__ __forceinline__ float load1(const void* p, int dtype, long i) {
+  if (dtype == EXG_F32) return reinterpret_cast<const float*>(p)[i];
+  return bf16_bits_to_float(reinterpret_cast<const uint16_t*>(p)[i]);
+}
+__device__ __forceinline__ void store1(void* p, int dtype, long i, float v) {
+  if (dtype == EXG_F32) reinterpret_cast<float*>(p)[i] = v;
+  else reinterpret_cast<uint16_t*>(p)[i] = float_to_bf16_bits(v);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float quick_gelu(float v) { return v / (1.0f + __expf(-1.702f * v)); }
+__device__ __forceinline__ float quick_gelu_grad(float u) {
+  float s = 1.0f / (1.0f + __expf(-1.702f * u));
+  return s + 1.702f * u * s * (1.0f - s);
+}
+
+static inline int exg_num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}

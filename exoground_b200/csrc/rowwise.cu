@@ -1,0 +1,477 @@
+// rowwise.cu — HBM-bound row-wise kernels: LayerNorm fwd/bwd, broadcast add, L2 normalise fwd/bwd,
+// column sums, casts.  One warp owns one row; a lane owns float4 chunks (j*32+lane)*4 so every
+// warp-level load/store is a contiguous 512-byte (fp32) or 256-byte (bf16) segment.
+// Reference ops replaced: nn.LayerNorm (model/tfm_model.py:22,28,63,70,71; model/tan_model.py:44-48),
+// pos-embed add (tan_model.py:161,193), x / x.norm() (tan_model.py:110-111,130-131).
+#include "common.cuh"
+
+namespace {
+
+constexpr int kLnThreads = 128;  // 4 warps = 4 rows per CTA
+
+template <int NCH>
+__global__ void __launch_bounds__(kLnThreads)
+ln_fwd_kernel(const void* __restrict__ x, int xd, const float* __restrict__ gamma,
+              const float* __restrict__ beta, void* __restrict__ y, int yd, exg_rowmap map_y,
+              void* __restrict__ y2, int y2d, const float* __restrict__ add, long add_period,
+              float* __restrict__ mean_out, float* __restrict__ rstd_out, long rows, int C, float eps) {
+  const int lane = threadIdx.x & 31;
+  const long row = (long)blockIdx.x * (kLnThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  float4 v[NCH];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      v[j] = load4(x, xd, row * C + col);
+      s += v[j].x + v[j].y + v[j].z + v[j].w;
+    } else {
+      v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  const float mean = warp_sum(s) / (float)C;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      float a = v[j].x - mean, b = v[j].y - mean, c = v[j].z - mean, d = v[j].w - mean;
+      q += a * a + b * b + c * c + d * d;
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)C + eps);
+  if (lane == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+  const long orow = exg_map_row(map_y, row);
+  const long arow = add ? (row % add_period) : 0;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      float4 g = *reinterpret_cast<const float4*>(gamma + col);
+      float4 b = *reinterpret_cast<const float4*>(beta + col);
+      float4 o;
+      o.x = (v[j].x - mean) * rstd * g.x + b.x;
+      o.y = (v[j].y - mean) * rstd * g.y + b.y;
+      o.z = (v[j].z - mean) * rstd * g.z + b.z;
+      o.w = (v[j].w - mean) * rstd * g.w + b.w;
+      if (add) {
+        float4 a = *reinterpret_cast<const float4*>(add + arow * C + col);
+        o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      }
+      if (y) store4(y, yd, orow * C + col, o);
+      if (y2) store4(y2, y2d, row * C + col, o);
+    }
+  }
+}
+
+constexpr int kLnBwdThreads = 256;  // 8 warps
+
+template <int NCH>
+__global__ void __launch_bounds__(kLnBwdThreads)
+ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* __restrict__ dy2, int d2,
+              exg_rowmap m2, const void* __restrict__ x, int xd, const float* __restrict__ gamma,
+              const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+              const float* __restrict__ dres, float* __restrict__ dx, void* __restrict__ dxT, int dxTd,
+              float* __restrict__ dgamma, float* __restrict__ dbeta, long rows, int C, float eps) {
+  extern __shared__ float red[];  // [warps][2*C]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nwarps = kLnBwdThreads / 32;
+  float4 ag[NCH], ab[NCH];
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) ag[j] = ab[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 g[NCH];
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    g[j] = col < C ? *reinterpret_cast<const float4*>(gamma + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (long row = (long)blockIdx.x * nwarps + warp; row < rows; row += (long)gridDim.x * nwarps) {
+    float4 xv[NCH], dv[NCH];
+    const long r1 = exg_map_row(m1, row);
+    const long r2 = dy2 ? exg_map_row(m2, row) : 0;
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+      int col = (j * 32 + lane) * 4;
+      if (col < C) {
+        xv[j] = load4(x, xd, row * C + col);
+        dv[j] = load4(dy1, d1, r1 * C + col);
+        if (dy2) {
+          float4 t = load4(dy2, d2, r2 * C + col);
+          dv[j].x += t.x; dv[j].y += t.y; dv[j].z += t.z; dv[j].w += t.w;
+        }
+        s += xv[j].x + xv[j].y + xv[j].z + xv[j].w;
+      } else {
+        xv[j] = dv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    float mean, rstd;
+    if (mean_in && rstd_in) {
+      mean = mean_in[row];
+      rstd = rstd_in[row];
+    } else {
+      mean = warp_sum(s) / (float)C;
+      float q = 0.f;
+#pragma unroll
+      for (int j = 0; j < NCH; ++j) {
+        int col = (j * 32 + lane) * 4;
+        if (col < C) {
+          float a = xv[j].x - mean, b = xv[j].y - mean, c = xv[j].z - mean, d = xv[j].w - mean;
+          q += a * a + b * b + c * c + d * d;
+        }
+      }
+      rstd = rsqrtf(warp_sum(q) / (float)C + eps);
+    }
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+      // xv <- xhat ; accumulate dgamma/dbeta ; dv <- dy*gamma
+      xv[j].x = (xv[j].x - mean) * rstd; xv[j].y = (xv[j].y - mean) * rstd;
+      xv[j].z = (xv[j].z - mean) * rstd; xv[j].w = (xv[j].w - mean) * rstd;
+      int col = (j * 32 + lane) * 4;
+      if (col >= C) xv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      ag[j].x += dv[j].x * xv[j].x; ag[j].y += dv[j].y * xv[j].y;
+      ag[j].z += dv[j].z * xv[j].z; ag[j].w += dv[j].w * xv[j].w;
+      ab[j].x += dv[j].x; ab[j].y += dv[j].y; ab[j].z += dv[j].z; ab[j].w += dv[j].w;
+      dv[j].x *= g[j].x; dv[j].y *= g[j].y; dv[j].z *= g[j].z; dv[j].w *= g[j].w;
+      c1 += dv[j].x + dv[j].y + dv[j].z + dv[j].w;
+      c2 += dv[j].x * xv[j].x + dv[j].y * xv[j].y + dv[j].z * xv[j].z + dv[j].w * xv[j].w;
+    }
+    c1 = warp_sum(c1) / (float)C;
+    c2 = warp_sum(c2) / (float)C;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+      int col = (j * 32 + lane) * 4;
+      if (col < C) {
+        float4 o;
+        o.x = (dv[j].x - c1 - xv[j].x * c2) * rstd;
+        o.y = (dv[j].y - c1 - xv[j].y * c2) * rstd;
+        o.z = (dv[j].z - c1 - xv[j].z * c2) * rstd;
+        o.w = (dv[j].w - c1 - xv[j].w * c2) * rstd;
+        if (dres) {
+          float4 r = *reinterpret_cast<const float4*>(dres + row * C + col);
+          o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+        }
+        if (dx) *reinterpret_cast<float4*>(dx + row * C + col) = o;
+        if (dxT) store4(dxT, dxTd, row * C + col, o);
+      }
+    }
+  }
+  if (!dgamma && !dbeta) return;
+  // cross-warp reduction of the per-lane column partials, then one atomic per column per CTA
+  float* rg = red + (size_t)warp * 2 * C;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      *reinterpret_cast<float4*>(rg + col) = ag[j];
+      *reinterpret_cast<float4*>(rg + C + col) = ab[j];
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += kLnBwdThreads) {
+    float t = 0.f;
+    for (int w = 0; w < nwarps; ++w) t += red[(size_t)w * 2 * C + i];
+    if (i < C) { if (dgamma) atomicAdd(dgamma + i, t); }
+    else       { if (dbeta) atomicAdd(dbeta + (i - C), t); }
+  }
+}
+
+__global__ void add_rows_kernel(const float* __restrict__ x, exg_rowmap mx, const float* __restrict__ x2,
+                                exg_rowmap mx2, const float* __restrict__ add, long add_period,
+                                void* __restrict__ out, int od, exg_rowmap mo, void* __restrict__ out2,
+                                int o2d, long rows, int C) {
+  const int c4 = C / 4;
+  const long total = rows * c4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const long r = i / c4;
+    const int col = (int)(i % c4) * 4;
+    float4 v = *reinterpret_cast<const float4*>(x + exg_map_row(mx, r) * C + col);
+    if (x2) {
+      float4 t = *reinterpret_cast<const float4*>(x2 + exg_map_row(mx2, r) * C + col);
+      v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+    }
+    if (add) {
+      float4 t = *reinterpret_cast<const float4*>(add + (r % add_period) * C + col);
+      v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+    }
+    if (out) store4(out, od, exg_map_row(mo, r) * C + col, v);
+    if (out2) store4(out2, o2d, r * C + col, v);
+  }
+}
+
+template <int NCH>
+__global__ void __launch_bounds__(kLnThreads)
+l2n_fwd_kernel(const void* __restrict__ x, int xd, exg_rowmap mx, void* __restrict__ y, int yd,
+               float* __restrict__ inv_norm, long rows, int C) {
+  const int lane = threadIdx.x & 31;
+  const long row = (long)blockIdx.x * (kLnThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const long ir = exg_map_row(mx, row);
+  float4 v[NCH];
+  float ss = 0.f;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      v[j] = load4(x, xd, ir * C + col);
+      ss += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w;
+    }
+  }
+  const float inv = 1.0f / sqrtf(warp_sum(ss));   // no eps (tan_model.py:110): a zero row gives NaN
+  if (lane == 0 && inv_norm) inv_norm[row] = inv;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      float4 o = make_float4(v[j].x * inv, v[j].y * inv, v[j].z * inv, v[j].w * inv);
+      store4(y, yd, row * C + col, o);
+    }
+  }
+}
+
+template <int NCH>
+__global__ void __launch_bounds__(kLnThreads)
+l2n_bwd_kernel(const void* __restrict__ dy, int dyd, const void* __restrict__ y, int yd,
+               const float* __restrict__ inv_norm, void* __restrict__ dx, int dxd, exg_rowmap mdx,
+               int accumulate, long rows, int C) {
+  const int lane = threadIdx.x & 31;
+  const long row = (long)blockIdx.x * (kLnThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  float4 g[NCH], yy[NCH];
+  float dot = 0.f;
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      g[j] = load4(dy, dyd, row * C + col);
+      yy[j] = load4(y, yd, row * C + col);
+      dot += g[j].x * yy[j].x + g[j].y * yy[j].y + g[j].z * yy[j].z + g[j].w * yy[j].w;
+    }
+  }
+  dot = warp_sum(dot);
+  const float inv = inv_norm[row];
+  const long orow = exg_map_row(mdx, row);
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    int col = (j * 32 + lane) * 4;
+    if (col < C) {
+      float4 o;
+      o.x = (g[j].x - yy[j].x * dot) * inv; o.y = (g[j].y - yy[j].y * dot) * inv;
+      o.z = (g[j].z - yy[j].z * dot) * inv; o.w = (g[j].w - yy[j].w * dot) * inv;
+      if (accumulate) {
+        float4 p = load4(dx, dxd, orow * C + col);
+        o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+      }
+      store4(dx, dxd, orow * C + col, o);
+    }
+  }
+}
+
+// out[n] += sum over a slab of rows.  blockDim = (32, 8): x = 4-column group, y = row lane.
+__global__ void colsum_kernel(const void* __restrict__ x, int xd, long M, long N, long ldx,
+                              float* __restrict__ out, long rows_per_block) {
+  __shared__ float4 sm[8][32];
+  const long col = ((long)blockIdx.x * 32 + threadIdx.x) * 4;
+  const long r0 = (long)blockIdx.y * rows_per_block;
+  const long r1 = min(M, r0 + rows_per_block);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (col < N) {
+    for (long r = r0 + threadIdx.y; r < r1; r += 8) {
+      float4 v = load4(x, xd, r * ldx + col);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+  }
+  sm[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && col < N) {
+#pragma unroll
+    for (int k = 1; k < 8; ++k) {
+      float4 v = sm[k][threadIdx.x];
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    atomicAdd(out + col, acc.x); atomicAdd(out + col + 1, acc.y);
+    atomicAdd(out + col + 2, acc.z); atomicAdd(out + col + 3, acc.w);
+  }
+}
+
+__global__ void cast_kernel(const void* __restrict__ src, int sd, void* __restrict__ dst, int dd, long n) {
+  const long n4 = n / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x)
+    store4(dst, dd, i * 4, load4(src, sd, i * 4));
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    long i = n4 * 4 + threadIdx.x;
+    store1(dst, dd, i, load1(src, sd, i));
+  }
+}
+
+__global__ void stage_mean_kernel(const void* __restrict__ x, int xd, long stride, int S,
+                                  float* __restrict__ out, void* __restrict__ outT, int otd, long n) {
+  const long n4 = n / 4;
+  const float inv = 1.0f / (float)S;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s = 0; s < S; ++s) {
+      float4 v = load4(x, xd, (long)s * stride + i * 4);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    a.x *= inv; a.y *= inv; a.z *= inv; a.w *= inv;
+    if (out) *reinterpret_cast<float4*>(out + i * 4) = a;
+    if (outT) store4(outT, otd, i * 4, a);
+  }
+}
+
+inline int grid_for(long work_items, int threads, int max_blocks_per_sm = 8) {
+  long b = (work_items + threads - 1) / threads;
+  long cap = (long)exg_num_sms() * max_blocks_per_sm;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+bool rowmap_ok(const exg_rowmap& m) { return m.group > 0; }
+
+}  // namespace
+
+#define DISPATCH_NCH(C, ...)                                     \
+  do {                                                           \
+    if ((C) <= 512) { constexpr int NCH = 4; __VA_ARGS__; }      \
+    else if ((C) <= 1024) { constexpr int NCH = 8; __VA_ARGS__; } \
+    else if ((C) <= 2048) { constexpr int NCH = 16; __VA_ARGS__; } \
+    else { constexpr int NCH = 32; __VA_ARGS__; }                \
+  } while (0)
+
+extern "C" int exg_layernorm_fwd(const void* x, int x_dtype, const float* gamma, const float* beta,
+                                 void* y, int y_dtype, exg_rowmap map_y, void* y2, int y2_dtype,
+                                 const float* add, long add_period, float* mean, float* rstd,
+                                 long rows, int C, float eps, void* stream) {
+  EXG_CHECK_ARG(x && gamma && beta && (y || y2), "layernorm_fwd: null pointer");
+  EXG_CHECK_ARG(exg_valid_dtype(x_dtype) && exg_valid_dtype(y_dtype) && exg_valid_dtype(y2_dtype),
+                "layernorm_fwd: bad dtype");
+  EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096, "layernorm_fwd: C=%d must be a multiple of 4, <= 4096", C);
+  EXG_CHECK_ARG(rowmap_ok(map_y) && (!add || add_period > 0), "layernorm_fwd: bad row map");
+  if (rows <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  int blocks = (int)((rows + 3) / 4);
+  DISPATCH_NCH(C, ln_fwd_kernel<NCH><<<blocks, kLnThreads, 0, s>>>(
+                      x, x_dtype, gamma, beta, y, y_dtype, map_y, y2, y2_dtype, add, add_period, mean,
+                      rstd, rows, C, eps));
+  EXG_LAUNCH_CHECK("layernorm_fwd");
+  return 0;
+}
+
+extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1, const void* dy2,
+                                 int dy2_dtype, exg_rowmap map2, const void* x, int x_dtype,
+                                 const float* gamma, const float* mean, const float* rstd,
+                                 const float* dres, float* dx, void* dxT, int dxT_dtype, float* dgamma,
+                                 float* dbeta, long rows, int C, void* stream) {
+  EXG_CHECK_ARG(dy1 && x && gamma, "layernorm_bwd: null pointer");
+  EXG_CHECK_ARG(exg_valid_dtype(dy1_dtype) && exg_valid_dtype(dy2_dtype) && exg_valid_dtype(x_dtype) &&
+                    exg_valid_dtype(dxT_dtype), "layernorm_bwd: bad dtype");
+  EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096, "layernorm_bwd: C=%d unsupported", C);
+  EXG_CHECK_ARG(rowmap_ok(map1) && (!dy2 || rowmap_ok(map2)), "layernorm_bwd: bad row map");
+  if (rows <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int nwarps = kLnBwdThreads / 32;
+  long want = (rows + nwarps - 1) / nwarps;
+  int blocks = (int)(want < 2L * exg_num_sms() ? want : 2L * exg_num_sms());
+  size_t smem = (size_t)nwarps * 2 * C * sizeof(float);
+  const float eps = 1e-5f;
+#define LN_BWD_CALL                                                                               \
+  do {                                                                                            \
+    auto kfn = ln_bwd_kernel<NCH>;                                                                \
+    if (smem > 48 * 1024) cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    kfn<<<blocks, kLnBwdThreads, smem, s>>>(dy1, dy1_dtype, map1, dy2, dy2_dtype, map2, x, x_dtype, \
+                                            gamma, mean, rstd, dres, dx, dxT, dxT_dtype, dgamma,  \
+                                            dbeta, rows, C, eps);                                 \
+  } while (0)
+  DISPATCH_NCH(C, LN_BWD_CALL);
+#undef LN_BWD_CALL
+  EXG_LAUNCH_CHECK("layernorm_bwd");
+  return 0;
+}
+
+extern "C" int exg_add_rows(const float* x, exg_rowmap map_x, const float* x2, exg_rowmap map_x2,
+                            const float* add, long add_period, void* out, int out_dtype,
+                            exg_rowmap map_out, void* out2, int out2_dtype, long rows, int C,
+                            void* stream) {
+  EXG_CHECK_ARG(x && (out || out2), "add_rows: null pointer");
+  EXG_CHECK_ARG(exg_valid_dtype(out_dtype) && exg_valid_dtype(out2_dtype), "add_rows: bad dtype");
+  EXG_CHECK_ARG(C > 0 && C % 4 == 0, "add_rows: C must be a multiple of 4");
+  EXG_CHECK_ARG(rowmap_ok(map_x) && rowmap_ok(map_out) && (!x2 || rowmap_ok(map_x2)) &&
+                    (!add || add_period > 0), "add_rows: bad row map");
+  if (rows <= 0) return 0;
+  add_rows_kernel<<<grid_for(rows * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(
+      x, map_x, x2, map_x2, add, add_period, out, out_dtype, map_out, out2, out2_dtype, rows, C);
+  EXG_LAUNCH_CHECK("add_rows");
+  return 0;
+}
+
+extern "C" int exg_l2norm_fwd(const void* x, int x_dtype, exg_rowmap map_x, void* y, int y_dtype,
+                              float* inv_norm, long rows, int C, void* stream) {
+  EXG_CHECK_ARG(x && y, "l2norm_fwd: null pointer");
+  EXG_CHECK_ARG(exg_valid_dtype(x_dtype) && exg_valid_dtype(y_dtype), "l2norm_fwd: bad dtype");
+  EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096 && rowmap_ok(map_x), "l2norm_fwd: bad C / map");
+  if (rows <= 0) return 0;
+  int blocks = (int)((rows + 3) / 4);
+  DISPATCH_NCH(C, l2n_fwd_kernel<NCH><<<blocks, kLnThreads, 0, (cudaStream_t)stream>>>(
+                      x, x_dtype, map_x, y, y_dtype, inv_norm, rows, C));
+  EXG_LAUNCH_CHECK("l2norm_fwd");
+  return 0;
+}
+
+extern "C" int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y_dtype,
+                              const float* inv_norm, void* dx, int dx_dtype, exg_rowmap map_dx,
+                              int accumulate, long rows, int C, void* stream) {
+  EXG_CHECK_ARG(dy && y && inv_norm && dx, "l2norm_bwd: null pointer");
+  EXG_CHECK_ARG(exg_valid_dtype(dy_dtype) && exg_valid_dtype(y_dtype) && exg_valid_dtype(dx_dtype),
+                "l2norm_bwd: bad dtype");
+  EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096 && rowmap_ok(map_dx), "l2norm_bwd: bad C / map");
+  if (rows <= 0) return 0;
+  int blocks = (int)((rows + 3) / 4);
+  DISPATCH_NCH(C, l2n_bwd_kernel<NCH><<<blocks, kLnThreads, 0, (cudaStream_t)stream>>>(
+                      dy, dy_dtype, y, y_dtype, inv_norm, dx, dx_dtype, map_dx, accumulate, rows, C));
+  EXG_LAUNCH_CHECK("l2norm_bwd");
+  return 0;
+}
+
+extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, float* out,
+                          int accumulate, void* stream) {
+  EXG_CHECK_ARG(x && out && exg_valid_dtype(x_dtype), "colsum: bad argument");
+  EXG_CHECK_ARG(N > 0 && N % 4 == 0 && ldx % 4 == 0, "colsum: N and ldx must be multiples of 4");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!accumulate) EXG_CUDA(cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), s));
+  if (M <= 0) return 0;
+  long strips = (N + 127) / 128;
+  long target = 4L * exg_num_sms();
+  long splits = (target + strips - 1) / strips;
+  long rows_per_block = (M + splits - 1) / splits;
+  if (rows_per_block < 64) rows_per_block = 64;
+  splits = (M + rows_per_block - 1) / rows_per_block;
+  dim3 grid((unsigned)strips, (unsigned)splits), block(32, 8);
+  colsum_kernel<<<grid, block, 0, s>>>(x, x_dtype, M, N, ldx, out, rows_per_block);
+  EXG_LAUNCH_CHECK("colsum");
+  return 0;
+}
+
+extern "C" int exg_cast(const void* src, int src_dtype, void* dst, int dst_dtype, long n, void* stream) {
+  EXG_CHECK_ARG(src && dst && exg_valid_dtype(src_dtype) && exg_valid_dtype(dst_dtype), "cast: bad argument");
+  if (n <= 0) return 0;
+  cast_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(src, src_dtype, dst, dst_dtype, n);
+  EXG_LAUNCH_CHECK("cast");
+  return 0;
+}
+
+extern "C" int exg_stage_mean(const void* x, int x_dtype, long stage_stride, int S, float* out,
+                              void* outT, int outT_dtype, long n, void* stream) {
+  EXG_CHECK_ARG(x && (out || outT) && exg_valid_dtype(x_dtype) && exg_valid_dtype(outT_dtype) && S > 0,
+                "stage_mean: bad argument");
+  EXG_CHECK_ARG(n % 4 == 0 && stage_stride % 4 == 0, "stage_mean: n must be a multiple of 4");
+  if (n <= 0) return 0;
+  stage_mean_kernel<<<grid_for(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(x, x_dtype, stage_stride, S,
+                                                                          out, outT, outT_dtype, n);
+  EXG_LAUNCH_CHECK("stage_mean");
+  return 0;
+}

@@ -1,0 +1,173 @@
+/* exg.h — C ABI of libexg.so, the sm_100a CUDA side of exoground_b200.
+ *
+ * The reference (arjunrs1/ExoGround) is 100% Python/PyTorch and has no FFI; its boundary for this
+ * path is the Python signatures of model/tfm_model.py, model/tan_model.py, model/exo_ground_model.py,
+ * train/loss.py and train/loss_egoexo4d.py.  The Python mirror in exoground_b200/{model,train}
+ * keeps those signatures; every arithmetic step underneath goes through the entry points below
+ * (bound with ctypes in exoground_b200/ops/lib.py).  Each entry cites the
+ * reference op(s) it replaces.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all pointers are DEVICE pointers owned by the caller;
+ *   - every entry returns 0 on success, <0 for EXG_E* argument errors, >0 for a cudaError_t;
+ *     exg_last_error() gives a thread-local message;
+ *   - entries only enqueue work on `stream` (a cudaStream_t passed as void*): no allocation,
+ *     no synchronisation, safe under CUDA-graph capture;
+ *   - dtype tags: EXG_F32 / EXG_BF16.  "T" below means the compute dtype of the call.
+ */
+#ifndef EXG_H_
+#define EXG_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EXG_F32 0
+#define EXG_BF16 1
+
+#define EXG_EINVAL (-1)
+#define EXG_EUNSUPPORTED (-2)
+
+int exg_version(void);
+const char* exg_last_error(void);
+/* number of kernels this library has launched since load (process-wide; for bench gpu_launches) */
+long long exg_launch_count(void);
+
+/* Row addressing helper used by the row-wise kernels: logical row r of a [rows, C] operand lives at
+ * physical row  (r / group) * group_stride + (r % group) + offset.  {rows,rows,0} == contiguous.
+ * Lets kernels read/write the video / text slices of a joint [B, T+N, C] buffer in place
+ * (replaces torch.cat / slicing at model/tan_model.py:195-203). */
+typedef struct { long group; long group_stride; long offset; } exg_rowmap;
+
+/* ---------------------------------------------------------------- GEMM ------------------------
+ * C[b] = epilogue( alpha * op(A[b]) (M x K) * op(B[b]) (K x N) )            for b in [0,batch)
+ *   transA=0: A stored [M,K] (K contiguous, row stride lda);  transA=1: A stored [K,M] (M contiguous)
+ *   transB=0: B stored [N,K] (K contiguous, row stride ldb)  -- nn.Linear weight layout;
+ *   transB=1: B stored [K,N] (N contiguous)
+ * Replaces nn.Linear / F.linear / torch.einsum / torch.bmm at model/tfm_model.py:21-27,62-69,
+ * model/tan_model.py:42-43,112,132,256,274 and their autograd backward.
+ * bf16 inputs with 16-byte aligned operands run on tcgen05 tensor cores (TMA -> smem -> tcgen05.mma
+ * -> TMEM -> epilogue); everything else runs on the fp32 SIMT kernel.
+ */
+#define EXG_EPI_NONE 0       /* C = v                      (v = alpha*acc + bias[n] if bias) */
+#define EXG_EPI_QGELU 1      /* aux_out = v ; C = v*sigmoid(1.702 v)   (model/tfm_model.py:11-13) */
+#define EXG_EPI_RESID 2      /* C(fp32) = aux(fp32)[m,n] + v           (model/tfm_model.py:36-37) */
+#define EXG_EPI_QGELU_BWD 3  /* C = v * dQuickGELU(aux[m,n]), aux = saved pre-activation (T)  */
+#define EXG_EPI_RELU 4       /* C = max(v,0)                           (model/vi_encoder.py:217) */
+#define EXG_EPI_RELU_BWD 5   /* C = v * (aux[m,n] > 0), aux = forward output (T) */
+
+#define EXG_GEMM_AUTO 0
+#define EXG_GEMM_SIMT 1
+#define EXG_GEMM_TC 2
+
+typedef struct {
+  const void* A; const void* B; void* C;
+  int M, N, K;
+  long lda, ldb, ldc;
+  int transA, transB;
+  int batch; long strideA, strideB, strideC;     /* elements */
+  int in_dtype;                                  /* dtype of A and B */
+  int out_dtype;                                 /* dtype of C (and aux_out) */
+  int epilogue;
+  const float* bias;                             /* [N] fp32 or NULL */
+  const void* aux; long ldaux; long strideAux;   /* see epilogues */
+  void* aux_out;                                 /* QGELU pre-activation, same ld/stride as C */
+  float alpha;
+  int impl;                                      /* EXG_GEMM_AUTO | _SIMT | _TC */
+} exg_gemm_params;
+
+int exg_gemm(const exg_gemm_params* p, void* stream);
+/* 1 if the tcgen05 path accepts these parameters (alignment / dtype), else 0 */
+int exg_gemm_tc_supported(const exg_gemm_params* p);
+
+/* ---------------------------------------------------------------- row-wise kernels ------------
+ * LayerNorm forward (nn.LayerNorm eps=1e-5; model/tfm_model.py:22,28,63,70,71; tan_model.py:44-48):
+ *   y[map_y(r)] = (x[r]-mean)*rstd*gamma + beta  (+ add[r % add_period] if add)
+ * x: x_dtype [rows,C] contiguous;  y: y_dtype;  mean/rstd: fp32 [rows] (may be NULL);
+ * y2 (optional second output, y2_dtype, contiguous) receives the same values. */
+int exg_layernorm_fwd(const void* x, int x_dtype, const float* gamma, const float* beta,
+                      void* y, int y_dtype, exg_rowmap map_y, void* y2, int y2_dtype,
+                      const float* add, long add_period,
+                      float* mean, float* rstd, long rows, int C, float eps, void* stream);
+/* LayerNorm backward.  dy = dy1[map1(r)] (+ dy2[map2(r)] if dy2);
+ *   dx[r] = (dres ? dres[r] : 0) + LN'(dy)        written fp32 to dx and (optional) dtype copy dxT
+ *   dgamma[C] += sum_r dy*xhat ; dbeta[C] += sum_r dy    (fp32 atomics: caller zero-initialises) */
+int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1,
+                      const void* dy2, int dy2_dtype, exg_rowmap map2,
+                      const void* x, int x_dtype, const float* gamma,
+                      const float* mean, const float* rstd, const float* dres,
+                      float* dx, void* dxT, int dxT_dtype,
+                      float* dgamma, float* dbeta, long rows, int C, void* stream);
+/* out[map_out(r)] = x[map_x(r)] + (add ? add[r % add_period] : 0) (+ x2[map_x2(r)] if x2); fp32 in,
+ * out_dtype out.  Replaces `video_embed + ln_position_init(pos)` (tan_model.py:161,193) and torch.cat. */
+int exg_add_rows(const float* x, exg_rowmap map_x, const float* x2, exg_rowmap map_x2,
+                 const float* add, long add_period, void* out, int out_dtype, exg_rowmap map_out,
+                 void* out2, int out2_dtype, long rows, int C, void* stream);
+/* y[r] = x[map_x(r)] / ||x[map_x(r)]||_2  (NO eps: tan_model.py:110-111); inv_norm[r] saved (fp32). */
+int exg_l2norm_fwd(const void* x, int x_dtype, exg_rowmap map_x, void* y, int y_dtype,
+                   float* inv_norm, long rows, int C, void* stream);
+/* dx[map_dx(r)] = (dy[r] - y[r]*<dy[r],y[r]>) * inv_norm[r]   (+= if accumulate) ; dx dtype dx_dtype */
+int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y_dtype, const float* inv_norm,
+                   void* dx, int dx_dtype, exg_rowmap map_dx, int accumulate,
+                   long rows, int C, void* stream);
+/* out[n] (+)= sum_m x[m,n]  — bias gradients and broadcast-add gradients */
+int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, float* out, int accumulate,
+               void* stream);
+/* elementwise dtype conversion of n elements (fp32 master weights -> bf16 shadow copies) */
+int exg_cast(const void* src, int src_dtype, void* dst, int dst_dtype, long n, void* stream);
+/* mean over `S` stage slabs: out[r] = (1/S) sum_s x[s*stage_stride + r]   (exo_ground_model.py:153-154) */
+int exg_stage_mean(const void* x, int x_dtype, long stage_stride, int S, float* out, void* outT,
+                   int outT_dtype, long n, void* stream);
+
+/* ---------------------------------------------------------------- attention -------------------
+ * softmax(q k^T * scale + key_padding_mask) v per (batch, head); replaces nn.MultiheadAttention's
+ * scaled-dot-product core at model/tfm_model.py:32,75,79 (need_weights=False).
+ * q: rows b*Sq+i, row stride ldq, head h at column h*d;  k,v likewise with Sk / ldk / ldv.
+ * key_pad: uint8 [B,Sk] (1 = ignore key) or NULL.  lse: fp32 [B,H,Sq] (log-sum-exp of scaled scores).
+ */
+int exg_attn_fwd(const void* q, const void* k, const void* v, int dtype,
+                 long ldq, long ldk, long ldv, const uint8_t* key_pad,
+                 void* o, long ldo, float* lse, int B, int H, int Sq, int Sk, int d, float scale,
+                 void* stream);
+/* delta: fp32 workspace [B,H,Sq].  dq/dk/dv use the same strides as q/k/v. */
+int exg_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                 int dtype, long ldq, long ldk, long ldv, long ldo, const uint8_t* key_pad,
+                 const float* lse, float* delta, void* dq, void* dk, void* dv,
+                 int B, int H, int Sq, int Sk, int d, float scale, void* stream);
+
+/* ---------------------------------------------------------------- MIL-NCE ---------------------
+ * Masked bidirectional MIL-NCE over stage-major raw cosine logits L[S, R=B*T, Cc=B*N]
+ * (train/loss.py:234-278).  Positives: column (b,k) is positive for row (a,t) iff a==b and
+ * tgt[b,k,t]; columns with col_valid==0 (padded sentences, loss.py:244) are skipped.
+ * fwd: exp-sums with a fixed shift (|logit*inv_temp| <= inv_temp since |cos|<=1):
+ *   row_all[s,r]=sum_c e, row_pos[s,r]=sum_{c pos} e, col_all[s,c]=sum_r e, col_pos[s,c]=sum_{r pos} e,
+ *   e = exp(L*inv_temp - inv_temp).  col_* are accumulated with atomics: caller zero-initialises.
+ * bwd: G[s,r,c] = inv_temp * ( wr[r]*(e/row_all - pos*e/row_pos) + wc[c]*(e/col_all - pos*e/col_pos) )
+ *   written in g_dtype; invalid columns get 0.  wr/wc: fp32 per-row / per-column weights (0 = unused).
+ */
+int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid,
+                float* row_all, float* row_pos, float* col_all, float* col_pos,
+                int S, int B, int T, int N, float inv_temp, void* stream);
+int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid,
+                const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
+                const float* wr, const float* wc, void* G, int g_dtype,
+                int S, int B, int T, int N, float inv_temp, void* stream);
+/* own_max[b,k] = max_t L[stage, (b,t), (b,k)]   (train/loss.py:283-286) */
+int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B, int T, int N,
+                void* stream);
+
+/* ---------------------------------------------------------------- optimizer -------------------
+ * AdamW (torch.optim.AdamW semantics, train/main.py:418) on a flat fp32 segment; optional bf16
+ * shadow copy of the updated weights.  grad_scale multiplies the gradient first (1/world_size). */
+int exg_adamw(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+              long n, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+              float grad_scale, void* stream);
+/* target = m*target + (1-m)*online   (TwinTemporalAligner._momentum_update, tan_model.py:334-338) */
+int exg_ema(float* target, const float* online, long n, float m, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EXG_H_ */
