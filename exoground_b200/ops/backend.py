@@ -1,0 +1,255 @@
+"""Tensor-level op API on top of the C ABI (exoground_b200/ops/lib.py).
+
+Every method takes/returns torch CUDA tensors, extracts raw pointers / strides and enqueues the
+CUDA kernels of libexg.so on torch's current stream.  This is the only place tensors meet ctypes.
+The op *specifications* (shapes, dtypes, semantics) are documented here once; tests/fake_backend.py
+implements the same spec with plain torch ops on CPU to validate the host logic without a GPU.
+
+Conventions: "T" = compute dtype (torch.float32 or torch.bfloat16); rm = row map tuple
+(group, group_stride, offset) or None for contiguous rows (see exg_rowmap in include/exg.h).
+"""
+import ctypes as C
+
+import torch
+
+from . import lib as L
+
+_DT = {torch.float32: L.F32, torch.bfloat16: L.BF16}
+
+
+def _dt(t):
+    try:
+        return _DT[t]
+    except KeyError:
+        raise ValueError(f"exoground_b200: unsupported dtype {t} (float32 / bfloat16 only)")
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _rm(rm, rows):
+    if rm is None:
+        return L.RowMap(max(int(rows), 1), max(int(rows), 1), 0)
+    return L.RowMap(int(rm[0]), int(rm[1]), int(rm[2]))
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("exoground_b200 ops need CUDA tensors (there is no CPU fallback)")
+
+
+def _rows2d(t):
+    """(data tensor, leading dim) of a 2-D operand whose last dim is contiguous."""
+    if t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1):
+        raise ValueError(f"expected a 2-D operand with contiguous last dim, got {tuple(t.shape)} / {t.stride()}")
+    return t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1)
+
+
+class CudaBackend:
+    name = "cuda"
+
+    def __init__(self):
+        self.lib = L.load()
+
+    # ------------------------------------------------------------------ GEMM
+    def gemm(self, A, B, *, transA=False, transB=False, bias=None, epilogue=L.EPI_NONE, aux=None,
+             out_dtype=None, alpha=1.0, out=None, want_preact=False, impl=L.GEMM_AUTO):
+        """C = epi(alpha * op(A) @ op(B) (+ bias)).
+
+        A: [M,K] (transA=False) or [K,M] (transA=True); B: [N,K] (transB=False, nn.Linear layout) or
+        [K,N] (transB=True).  Either may carry a leading batch dim; a 2-D operand is broadcast over the
+        batch.  bias fp32 [N].  aux: RESID -> fp32 [.., M, N]; *_BWD -> T [.., M, N].
+        Returns C [.., M, N] of out_dtype (default: input dtype), plus the pre-activation if want_preact."""
+        _cuda(A, B, bias, aux, out)
+        if A.dtype != B.dtype:
+            raise ValueError("gemm: A and B dtypes differ")
+        batch = A.shape[0] if A.dim() == 3 else (B.shape[0] if B.dim() == 3 else 1)
+        a2 = A[0] if A.dim() == 3 else A
+        b2 = B[0] if B.dim() == 3 else B
+        M, K = (a2.shape[1], a2.shape[0]) if transA else (a2.shape[0], a2.shape[1])
+        N, Kb = (b2.shape[1], b2.shape[0]) if transB else (b2.shape[0], b2.shape[1])
+        if K != Kb:
+            raise ValueError(f"gemm: inner dims differ ({K} vs {Kb})")
+        out_dtype = out_dtype or A.dtype
+        batched = A.dim() == 3 or B.dim() == 3
+        if out is None:
+            out = torch.empty((batch, M, N) if batched else (M, N), dtype=out_dtype, device=A.device)
+        c2 = out[0] if out.dim() == 3 else out
+        pre = torch.empty_like(out) if want_preact else None
+        p = L.GemmParams()
+        p.A, p.B, p.C = A.data_ptr(), B.data_ptr(), out.data_ptr()
+        p.M, p.N, p.K = M, N, K
+        p.lda, p.ldb, p.ldc = _rows2d(a2), _rows2d(b2), _rows2d(c2)
+        p.transA, p.transB = int(transA), int(transB)
+        p.batch = batch
+        p.strideA = A.stride(0) if A.dim() == 3 else 0
+        p.strideB = B.stride(0) if B.dim() == 3 else 0
+        p.strideC = out.stride(0) if out.dim() == 3 else 0
+        p.in_dtype, p.out_dtype, p.epilogue = _dt(A.dtype), _dt(out.dtype), epilogue
+        p.bias = bias.data_ptr() if bias is not None else None
+        if aux is not None:
+            x2 = aux[0] if aux.dim() == 3 else aux
+            p.aux, p.ldaux = aux.data_ptr(), _rows2d(x2)
+            p.strideAux = aux.stride(0) if aux.dim() == 3 else 0
+        p.aux_out = pre.data_ptr() if pre is not None else None
+        p.alpha, p.impl = float(alpha), impl
+        L.check(self.lib.exg_gemm(C.byref(p), _stream()), "exg_gemm")
+        return (out, pre) if want_preact else out
+
+    # ------------------------------------------------------------------ row-wise
+    def layernorm_fwd(self, x, gamma, beta, *, out_dtype, out=None, out_map=None, y2_dtype=None, add=None,
+                      add_period=0, eps=1e-5):
+        """y[map(r)] = LN(x[r]) (+ add[r % add_period]); x [rows,C] contiguous.  `out` may be a larger
+        buffer addressed through out_map.  Returns (y, y2) with y2 an optional contiguous second copy."""
+        _cuda(x, gamma, beta, out, add)
+        rows, Cn = x.shape
+        if out is None:
+            out = torch.empty((rows, Cn), dtype=out_dtype, device=x.device)
+        y2 = torch.empty((rows, Cn), dtype=y2_dtype, device=x.device) if y2_dtype is not None else None
+        L.check(self.lib.exg_layernorm_fwd(_p(x), _dt(x.dtype), _p(gamma), _p(beta), _p(out), _dt(out.dtype),
+                                           _rm(out_map, rows), _p(y2), _dt(y2.dtype) if y2 is not None else 0,
+                                           _p(add), int(add_period), None, None, rows, Cn, float(eps),
+                                           _stream()), "exg_layernorm_fwd")
+        return out, y2
+
+    def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
+                      want_dx=True):
+        """Backward of y = LN(x)*gamma+beta with dy = dy1[map1] (+ dy2[map2]).
+        Returns (dx fp32 [rows,C] = dres + LN'(dy), dxT copy or None, dgamma fp32 [C], dbeta fp32 [C])."""
+        _cuda(dy1, x, gamma, dy2, dres)
+        rows, Cn = x.shape
+        dx = torch.empty((rows, Cn), dtype=torch.float32, device=x.device) if want_dx else None
+        dxT = torch.empty((rows, Cn), dtype=dxT_dtype, device=x.device) if dxT_dtype is not None else None
+        dg = torch.zeros(2, Cn, dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_layernorm_bwd(_p(dy1), _dt(dy1.dtype), _rm(map1, rows), _p(dy2),
+                                           _dt(dy2.dtype) if dy2 is not None else 0, _rm(map2, rows), _p(x),
+                                           _dt(x.dtype), _p(gamma), None, None, _p(dres), _p(dx), _p(dxT),
+                                           _dt(dxT.dtype) if dxT is not None else 0, _p(dg[0]), _p(dg[1]),
+                                           rows, Cn, _stream()), "exg_layernorm_bwd")
+        return dx, dxT, dg[0], dg[1]
+
+    def add_rows(self, x, rows, *, map_x=None, x2=None, map_x2=None, add=None, add_period=0, out=None,
+                 out_dtype=torch.float32, map_out=None, out2_dtype=None):
+        """out[map_out(r)] = x[map_x(r)] (+ x2[map_x2(r)]) (+ add[r % add_period]) for r < rows; x, x2, add fp32."""
+        _cuda(x, x2, add, out)
+        Cn = x.shape[-1]
+        if out is None:
+            out = torch.empty((rows, Cn), dtype=out_dtype, device=x.device)
+        out2 = torch.empty((rows, Cn), dtype=out2_dtype, device=x.device) if out2_dtype is not None else None
+        L.check(self.lib.exg_add_rows(_p(x), _rm(map_x, rows), _p(x2), _rm(map_x2, rows), _p(add),
+                                      int(add_period), _p(out), _dt(out.dtype), _rm(map_out, rows), _p(out2),
+                                      _dt(out2.dtype) if out2 is not None else 0, rows, Cn, _stream()),
+                "exg_add_rows")
+        return out, out2
+
+    def l2norm_fwd(self, x, rows, *, map_x=None, out_dtype=None):
+        """y[r] = x[map_x(r)] / ||.||  ->  (y [rows,C], inv_norm fp32 [rows])."""
+        _cuda(x)
+        Cn = x.shape[-1]
+        y = torch.empty((rows, Cn), dtype=out_dtype or x.dtype, device=x.device)
+        inv = torch.empty(rows, dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_l2norm_fwd(_p(x), _dt(x.dtype), _rm(map_x, rows), _p(y), _dt(y.dtype), _p(inv), rows,
+                                        Cn, _stream()), "exg_l2norm_fwd")
+        return y, inv
+
+    def l2norm_bwd(self, dy, y, inv, dx, *, map_dx=None, accumulate=False):
+        """dx[map_dx(r)] (+)= (dy[r] - y[r] <dy[r],y[r]>) * inv[r]; writes into the given dx buffer."""
+        _cuda(dy, y, inv, dx)
+        rows, Cn = y.shape
+        L.check(self.lib.exg_l2norm_bwd(_p(dy), _dt(dy.dtype), _p(y), _dt(y.dtype), _p(inv), _p(dx), _dt(dx.dtype),
+                                        _rm(map_dx, rows), int(accumulate), rows, Cn, _stream()), "exg_l2norm_bwd")
+        return dx
+
+    def colsum(self, x):
+        """fp32 [N] = sum over rows of x [M,N]."""
+        _cuda(x)
+        M, N = x.shape
+        out = torch.empty(N, dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_colsum(_p(x), _dt(x.dtype), M, N, _rows2d(x), _p(out), 0, _stream()), "exg_colsum")
+        return out
+
+    def cast(self, src, dtype, out=None):
+        _cuda(src)
+        if out is None:
+            out = torch.empty(src.shape, dtype=dtype, device=src.device)
+        L.check(self.lib.exg_cast(_p(src), _dt(src.dtype), _p(out), _dt(out.dtype), src.numel(), _stream()), "exg_cast")
+        return out
+
+    def stage_mean(self, x, *, outT_dtype=None):
+        """x [S, ...] contiguous -> (fp32 mean over S, optional T copy)."""
+        _cuda(x)
+        S, n = x.shape[0], x[0].numel()
+        out = torch.empty(x.shape[1:], dtype=torch.float32, device=x.device)
+        outT = torch.empty(x.shape[1:], dtype=outT_dtype, device=x.device) if outT_dtype is not None else None
+        L.check(self.lib.exg_stage_mean(_p(x), _dt(x.dtype), x.stride(0), S, _p(out), _p(outT),
+                                        _dt(outT.dtype) if outT is not None else 0, n, _stream()), "exg_stage_mean")
+        return out, outT
+
+    # ------------------------------------------------------------------ attention
+    def attn_fwd(self, q, k, v, key_pad, B, H, Sq, Sk, scale):
+        """q [B*Sq, H*64] / k,v [B*Sk, H*64] row-strided views (T); key_pad uint8 [B,Sk] or None.
+        Returns (o [B*Sq, H*64] T, lse fp32 [B,H,Sq])."""
+        _cuda(q, k, v, key_pad)
+        d = 64
+        o = torch.empty((B * Sq, H * d), dtype=q.dtype, device=q.device)
+        lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+        L.check(self.lib.exg_attn_fwd(_p(q), _p(k), _p(v), _dt(q.dtype), _rows2d(q), _rows2d(k), _rows2d(v),
+                                      _p(key_pad), _p(o), o.stride(0), _p(lse), B, H, Sq, Sk, d, float(scale),
+                                      _stream()), "exg_attn_fwd")
+        return o, lse
+
+    def attn_bwd(self, q, k, v, o, do, lse, key_pad, dq, dk, dv, B, H, Sq, Sk, scale):
+        """Writes dq/dk/dv (views with the same row strides as q/k/v)."""
+        _cuda(q, k, v, o, do, lse, key_pad, dq, dk, dv)
+        if (_rows2d(dq), _rows2d(dk), _rows2d(dv)) != (_rows2d(q), _rows2d(k), _rows2d(v)) or _rows2d(do) != _rows2d(o):
+            raise ValueError("attn_bwd: gradient views must use the strides of their primals")
+        delta = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+        L.check(self.lib.exg_attn_bwd(_p(q), _p(k), _p(v), _p(o), _p(do), _dt(q.dtype), _rows2d(q), _rows2d(k),
+                                      _rows2d(v), _rows2d(o), _p(key_pad), _p(lse), _p(delta), _p(dq), _p(dk),
+                                      _p(dv), B, H, Sq, Sk, 64, float(scale), _stream()), "exg_attn_bwd")
+
+    # ------------------------------------------------------------------ MIL-NCE
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp):
+        """logits [S, B*T, B*N] contiguous (T); tgt uint8 [B,N,T]; col_valid uint8 [B*N].
+        Returns fp32 (row_all [S,R], row_pos [S,R], col_all [S,Cc], col_pos [S,Cc]) exp-sums."""
+        _cuda(logits, tgt, col_valid)
+        S = logits.shape[0]
+        rows = torch.empty((2, S, B * T), dtype=torch.float32, device=logits.device)
+        cols = torch.zeros((2, S, B * N), dtype=torch.float32, device=logits.device)
+        L.check(self.lib.exg_nce_fwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(col_valid), _p(rows[0]), _p(rows[1]),
+                                     _p(cols[0]), _p(cols[1]), S, B, T, N, float(inv_temp), _stream()), "exg_nce_fwd")
+        return rows[0], rows[1], cols[0], cols[1]
+
+    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None):
+        """G [S,R,Cc] = d(sum_r wr*(log row_all-log row_pos) + sum_c wc*(log col_all-log col_pos)) / d logits."""
+        _cuda(logits, tgt, col_valid, wr, wc)
+        S = logits.shape[0]
+        G = torch.empty(logits.shape, dtype=g_dtype or logits.dtype, device=logits.device)
+        ra, rp, ca, cp = sums
+        L.check(self.lib.exg_nce_bwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(col_valid), _p(ra), _p(rp), _p(ca),
+                                     _p(cp), _p(wr), _p(wc), _p(G), _dt(G.dtype), S, B, T, N, float(inv_temp),
+                                     _stream()), "exg_nce_bwd")
+        return G
+
+    def own_max(self, logits, stage, B, T, N):
+        _cuda(logits)
+        out = torch.empty((B, N), dtype=torch.float32, device=logits.device)
+        L.check(self.lib.exg_own_max(_p(logits), _dt(logits.dtype), _p(out), int(stage), B, T, N, _stream()),
+                "exg_own_max")
+        return out
+
+    # ------------------------------------------------------------------ optimizer
+    def adamw(self, param, grad, m, v, shadow, lr, beta1, beta2, eps, wd, step, grad_scale=1.0):
+        _cuda(param, grad, m, v, shadow)
+        L.check(self.lib.exg_adamw(_p(param), _p(grad), _p(m), _p(v), _p(shadow), param.numel(), lr, beta1, beta2,
+                                   eps, wd, int(step), float(grad_scale), _stream()), "exg_adamw")
+
+    def ema(self, target, online, m):
+        _cuda(target, online)
+        L.check(self.lib.exg_ema(_p(target), _p(online), target.numel(), float(m), _stream()), "exg_ema")

@@ -1,0 +1,211 @@
+"""Plain-torch restatement of the op specs of exoground_b200/ops/backend.py.
+
+TEST INFRASTRUCTURE: (1) the per-kernel reference the GPU unit tests compare libexg.so against, and
+(2) injected with ops.set_backend() by the CPU tests so the host logic (buffer plumbing, manual
+backward chaining, row maps) can be validated against the oracle without a GPU.  Never shipped.
+All math is done in fp32 and rounded to the requested output dtype, like the kernels do.
+"""
+import torch
+
+from exoground_b200.ops import lib as L
+
+
+def _map_idx(rm, rows, device):
+    r = torch.arange(rows, device=device)
+    if rm is None:
+        return r
+    g, gs, off = rm
+    return (r // g) * gs + (r % g) + off
+
+
+def _qgelu(v):
+    return v * torch.sigmoid(1.702 * v)
+
+
+def _qgelu_grad(u):
+    s = torch.sigmoid(1.702 * u)
+    return s + 1.702 * u * s * (1 - s)
+
+
+class TorchBackend:
+    name = "fake-torch"
+
+    def gemm(self, A, B, *, transA=False, transB=False, bias=None, epilogue=L.EPI_NONE, aux=None,
+             out_dtype=None, alpha=1.0, out=None, want_preact=False, impl=0):
+        a = A.float().transpose(-1, -2) if transA else A.float()
+        b = B.float() if transB else B.float().transpose(-1, -2)
+        v = alpha * (a @ b)
+        if bias is not None:
+            v = v + bias.float()
+        pre = v
+        if epilogue == L.EPI_QGELU:
+            o = _qgelu(v)
+        elif epilogue == L.EPI_RESID:
+            o = aux.float() + v
+        elif epilogue == L.EPI_QGELU_BWD:
+            o = v * _qgelu_grad(aux.float())
+        elif epilogue == L.EPI_RELU:
+            o = v.clamp(min=0)
+        elif epilogue == L.EPI_RELU_BWD:
+            o = v * (aux.float() > 0)
+        else:
+            o = v
+        out_dtype = out_dtype or A.dtype
+        if out is not None:
+            out.copy_(o.to(out.dtype))
+        else:
+            out = o.to(out_dtype)
+        if want_preact:
+            return out, pre.to(out.dtype)
+        return out
+
+    def layernorm_fwd(self, x, gamma, beta, *, out_dtype, out=None, out_map=None, y2_dtype=None, add=None,
+                      add_period=0, eps=1e-5):
+        rows, C = x.shape
+        xf = x.float()
+        mu = xf.mean(-1, keepdim=True)
+        var = ((xf - mu) ** 2).mean(-1, keepdim=True)
+        y = (xf - mu) * torch.rsqrt(var + eps) * gamma + beta
+        if add is not None:
+            y = y + add[torch.arange(rows, device=x.device) % add_period]
+        if out is None:
+            out = torch.empty(rows, C, dtype=out_dtype, device=x.device)
+        out.view(-1, C)[_map_idx(out_map, rows, x.device)] = y.to(out.dtype)
+        y2 = y.to(y2_dtype) if y2_dtype is not None else None
+        return out, y2
+
+    def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
+                      want_dx=True):
+        rows, C = x.shape
+        dy = dy1.view(-1, C)[_map_idx(map1, rows, x.device)].float()
+        if dy2 is not None:
+            dy = dy + dy2.view(-1, C)[_map_idx(map2, rows, x.device)].float()
+        xf = x.float()
+        mu = xf.mean(-1, keepdim=True)
+        var = ((xf - mu) ** 2).mean(-1, keepdim=True)
+        rstd = torch.rsqrt(var + 1e-5)
+        xhat = (xf - mu) * rstd
+        dxh = dy * gamma
+        dx = (dxh - dxh.mean(-1, keepdim=True) - xhat * (dxh * xhat).mean(-1, keepdim=True)) * rstd
+        if dres is not None:
+            dx = dx + dres
+        dxT = dx.to(dxT_dtype) if dxT_dtype is not None else None
+        return (dx if want_dx else None), dxT, (dy * xhat).sum(0), dy.sum(0)
+
+    def add_rows(self, x, rows, *, map_x=None, x2=None, map_x2=None, add=None, add_period=0, out=None,
+                 out_dtype=torch.float32, map_out=None, out2_dtype=None):
+        C = x.shape[-1]
+        v = x.view(-1, C)[_map_idx(map_x, rows, x.device)].float()
+        if x2 is not None:
+            v = v + x2.view(-1, C)[_map_idx(map_x2, rows, x.device)].float()
+        if add is not None:
+            v = v + add[torch.arange(rows, device=x.device) % add_period]
+        if out is None:
+            out = torch.empty(rows, C, dtype=out_dtype, device=x.device)
+        out.view(-1, C)[_map_idx(map_out, rows, x.device)] = v.to(out.dtype)
+        out2 = v.to(out2_dtype) if out2_dtype is not None else None
+        return out, out2
+
+    def l2norm_fwd(self, x, rows, *, map_x=None, out_dtype=None):
+        C = x.shape[-1]
+        v = x.view(-1, C)[_map_idx(map_x, rows, x.device)].float()
+        inv = 1.0 / v.norm(dim=-1)
+        return (v * inv[:, None]).to(out_dtype or x.dtype), inv
+
+    def l2norm_bwd(self, dy, y, inv, dx, *, map_dx=None, accumulate=False):
+        rows, C = y.shape
+        g, yy = dy.float(), y.float()
+        d = (g - yy * (g * yy).sum(-1, keepdim=True)) * inv[:, None]
+        idx = _map_idx(map_dx, rows, y.device)
+        dv = dx.view(-1, C)
+        if accumulate:
+            d = d + dv[idx].float()
+        dv[idx] = d.to(dx.dtype)
+        return dx
+
+    def colsum(self, x):
+        return x.float().sum(0)
+
+    def cast(self, src, dtype, out=None):
+        if out is None:
+            return src.to(dtype)
+        out.copy_(src.to(out.dtype))
+        return out
+
+    def stage_mean(self, x, *, outT_dtype=None):
+        m = x.float().mean(0)
+        return m, (m.to(outT_dtype) if outT_dtype is not None else None)
+
+    def attn_fwd(self, q, k, v, key_pad, B, H, Sq, Sk, scale):
+        d = 64
+        qf = q.float().reshape(B, Sq, H, d).transpose(1, 2)
+        kf = k.float().reshape(B, Sk, H, d).transpose(1, 2)
+        vf = v.float().reshape(B, Sk, H, d).transpose(1, 2)
+        s = qf @ kf.transpose(-1, -2) * scale
+        if key_pad is not None:
+            s = s.masked_fill(key_pad.bool()[:, None, None, :], float("-inf"))
+        lse = torch.logsumexp(s, dim=-1)
+        p = torch.exp(s - lse[..., None])
+        o = (p @ vf).transpose(1, 2).reshape(B * Sq, H * d)
+        return o.to(q.dtype), lse
+
+    def attn_bwd(self, q, k, v, o, do, lse, key_pad, dq, dk, dv, B, H, Sq, Sk, scale):
+        d = 64
+        qf = q.float().reshape(B, Sq, H, d).transpose(1, 2)
+        kf = k.float().reshape(B, Sk, H, d).transpose(1, 2)
+        vf = v.float().reshape(B, Sk, H, d).transpose(1, 2)
+        dof = do.float().reshape(B, Sq, H, d).transpose(1, 2)
+        of = o.float().reshape(B, Sq, H, d).transpose(1, 2)
+        s = qf @ kf.transpose(-1, -2) * scale
+        if key_pad is not None:
+            s = s.masked_fill(key_pad.bool()[:, None, None, :], float("-inf"))
+        p = torch.exp(s - lse[..., None])
+        delta = (dof * of).sum(-1, keepdim=True)
+        dp = dof @ vf.transpose(-1, -2)
+        ds = p * (dp - delta) * scale
+        dq.copy_((ds @ kf).transpose(1, 2).reshape(B * Sq, H * d).to(dq.dtype))
+        dk.copy_((ds.transpose(-1, -2) @ qf).transpose(1, 2).reshape(B * Sk, H * d).to(dk.dtype))
+        dv.copy_((p.transpose(-1, -2) @ dof).transpose(1, 2).reshape(B * Sk, H * d).to(dv.dtype))
+
+    def _nce_common(self, logits, tgt, col_valid, B, T, N, inv_temp):
+        S = logits.shape[0]
+        e = torch.exp(logits.float() * inv_temp - inv_temp)                     # [S,R,Cc]
+        valid = col_valid.bool().view(1, 1, B * N)
+        e = torch.where(valid, e, torch.zeros_like(e))
+        eye = torch.eye(B, dtype=torch.bool, device=logits.device)
+        pos = (tgt.bool().permute(0, 2, 1)[:, :, None, :] & eye[:, None, :, None]).reshape(B * T, B * N)
+        pos = pos & col_valid.bool().view(1, B * N)
+        return e, pos
+
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp):
+        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp)
+        ep = e * pos[None]
+        return e.sum(-1), ep.sum(-1), e.sum(-2), ep.sum(-2)
+
+    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None):
+        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp)
+        ra, rp, ca, cp = sums
+        safe = lambda w, s: torch.where((w != 0) & (s > 0), w / s.clamp(min=1e-38), torch.zeros_like(s))
+        a_r = safe(wr[None, :].expand_as(ra), ra)[..., None]
+        b_r = safe(wr[None, :].expand_as(rp), rp)[..., None]
+        a_c = safe(wc[None, :].expand_as(ca), ca)[:, None, :]
+        b_c = safe(wc[None, :].expand_as(cp), cp)[:, None, :]
+        coef = a_r + a_c - pos[None].float() * (b_r + b_c)
+        return (inv_temp * e * coef).to(g_dtype or logits.dtype)
+
+    def own_max(self, logits, stage, B, T, N):
+        lg = logits[stage].float().view(B, T, B, N)
+        return torch.stack([lg[b, :, b, :].max(0).values for b in range(B)], 0)
+
+    def adamw(self, param, grad, m, v, shadow, lr, beta1, beta2, eps, wd, step, grad_scale=1.0):
+        g = grad * grad_scale
+        param.mul_(1 - lr * wd)
+        m.mul_(beta1).add_(g, alpha=1 - beta1)
+        v.mul_(beta2).addcmul_(g, g, value=1 - beta2)
+        bc1, bc2 = 1 - beta1 ** step, 1 - beta2 ** step
+        param.addcdiv_(m, v.sqrt() / (bc2 ** 0.5) + eps, value=-lr / bc1)
+        if shadow is not None:
+            shadow.copy_(param.to(shadow.dtype))
+
+    def ema(self, target, online, m):
+        target.mul_(m).add_(online, alpha=1 - m)
