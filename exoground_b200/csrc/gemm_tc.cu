@@ -28,6 +28,7 @@ struct TcArgs {
   void* aux_out;
   float alpha;
   int splits, kblocks_per_split, atomic;
+  int a_bcast, b_bcast;   // operand shared by all batches (batch stride 0): TMA z coordinate pinned to 0
 };
 
 template <int BN> struct Cfg {
@@ -79,17 +80,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint8_t* sb = sa + kABytes;
         const int k0 = (kb0 + i) * BK;
         mbar_arrive_expect_tx(&full[s], C_::kStageBytes);
+        const int za = p.a_bcast ? 0 : z, zb = p.b_bcast ? 0 : z;
         if (!p.a_mn) {
-          tma_load_3d(sa, &tmA, &full[s], k0, m0, z);
+          tma_load_3d(sa, &tmA, &full[s], k0, m0, za);
         } else {
 #pragma unroll
-          for (int j = 0; j < BM / 64; ++j) tma_load_3d(sa + j * 8192, &tmA, &full[s], m0 + j * 64, k0, z);
+          for (int j = 0; j < BM / 64; ++j) tma_load_3d(sa + j * 8192, &tmA, &full[s], m0 + j * 64, k0, za);
         }
         if (!p.b_mn) {
-          tma_load_3d(sb, &tmB, &full[s], k0, n0, z);
+          tma_load_3d(sb, &tmB, &full[s], k0, n0, zb);
         } else {
 #pragma unroll
-          for (int j = 0; j < BN / 64; ++j) tma_load_3d(sb + j * 8192, &tmB, &full[s], n0 + j * 64, k0, z);
+          for (int j = 0; j < BN / 64; ++j) tma_load_3d(sb + j * 8192, &tmB, &full[s], n0 + j * 64, k0, zb);
         }
       }
     }
@@ -297,11 +299,14 @@ int exg_gemm_tc(const exg_gemm_params* q, void* stream) {
 
   CUtensorMap ta, tb;
   int rc;
-  if (!q->transA) rc = make_tmap(&ta, q->A, q->K, q->M, q->batch, q->lda, q->strideA, BM);
-  else            rc = make_tmap(&ta, q->A, q->M, q->K, q->batch, q->lda, q->strideA, BK);
+  a.a_bcast = (q->batch > 1 && q->strideA == 0) ? 1 : 0;
+  a.b_bcast = (q->batch > 1 && q->strideB == 0) ? 1 : 0;
+  const int ba = a.a_bcast ? 1 : q->batch, bb = a.b_bcast ? 1 : q->batch;
+  if (!q->transA) rc = make_tmap(&ta, q->A, q->K, q->M, ba, q->lda, q->strideA, BM);
+  else            rc = make_tmap(&ta, q->A, q->M, q->K, ba, q->lda, q->strideA, BK);
   if (rc) return rc;
-  if (!q->transB) rc = make_tmap(&tb, q->B, q->K, q->N, q->batch, q->ldb, q->strideB, bn);
-  else            rc = make_tmap(&tb, q->B, q->N, q->K, q->batch, q->ldb, q->strideB, BK);
+  if (!q->transB) rc = make_tmap(&tb, q->B, q->K, q->N, bb, q->ldb, q->strideB, bn);
+  else            rc = make_tmap(&tb, q->B, q->N, q->K, bb, q->ldb, q->strideB, BK);
   if (rc) return rc;
   return bn == 256 ? launch<256>(ta, tb, a, q->batch, s) : launch<128>(ta, tb, a, q->batch, s);
 }

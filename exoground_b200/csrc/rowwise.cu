@@ -299,6 +299,23 @@ __global__ void colsum_kernel(const void* __restrict__ x, int xd, long M, long N
   }
 }
 
+// generic fallback (any N / ldx): one CTA per column
+__global__ void colsum_scalar_kernel(const void* __restrict__ x, int xd, long M, long N, long ldx,
+                                     float* __restrict__ out, int accumulate) {
+  __shared__ float sm[8];
+  const long n = blockIdx.x;
+  float a = 0.f;
+  for (long r = threadIdx.x; r < M; r += blockDim.x) a += load1(x, xd, r * ldx + n);
+  a = warp_sum(a);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += sm[w];
+    out[n] = accumulate ? out[n] + t : t;
+  }
+}
+
 __global__ void cast_kernel(const void* __restrict__ src, int sd, void* __restrict__ dst, int dd, long n) {
   const long n4 = n / 4;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x)
@@ -440,8 +457,14 @@ extern "C" int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y
 extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, float* out,
                           int accumulate, void* stream) {
   EXG_CHECK_ARG(x && out && exg_valid_dtype(x_dtype), "colsum: bad argument");
-  EXG_CHECK_ARG(N > 0 && N % 4 == 0 && ldx % 4 == 0, "colsum: N and ldx must be multiples of 4");
+  EXG_CHECK_ARG(N > 0, "colsum: N must be positive");
   cudaStream_t s = (cudaStream_t)stream;
+  if (N % 4 != 0 || ldx % 4 != 0) {
+    EXG_CHECK_ARG(N <= 65535, "colsum: unaligned N too large");
+    colsum_scalar_kernel<<<(unsigned)N, 256, 0, s>>>(x, x_dtype, M, N, ldx, out, accumulate);
+    EXG_LAUNCH_CHECK("colsum_scalar");
+    return 0;
+  }
   if (!accumulate) EXG_CUDA(cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), s));
   if (M <= 0) return 0;
   long strips = (N + 127) / 128;

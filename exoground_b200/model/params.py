@@ -1,0 +1,131 @@
+"""Parameter storage for the B200 path: one flat fp32 buffer per model (+ a flat bf16 shadow copy
+refreshed by one cast kernel, + a flat fp32 gradient buffer for the fused optimizer / all-reduce).
+
+`nn.Parameter`s stay ordinary parameters (same names as the reference, so reference checkpoints
+load and torch DDP / optimizers still work); only their `.data` is re-pointed at views of the flat
+buffer.  Offsets are padded to 64 elements so every view is 128-byte aligned (TMA needs 16 B).
+"""
+import os
+
+import torch
+
+from .. import ops
+
+ALIGN = 64
+
+
+def default_compute_dtype():
+    v = os.environ.get("EXG_COMPUTE_DTYPE", "bf16").lower()
+    return torch.float32 if v in ("fp32", "float32", "f32") else torch.bfloat16
+
+
+def is_no_decay(name):
+    """The reference's optimiser policy (train/main.py:352): no weight decay for LayerNorms and biases."""
+    name = "." + name
+    return any(k in name for k in (".ln_", ".bias", ".logit_scale", ".entropy_scale"))
+
+
+class FlatParams:
+    def __init__(self, module):
+        self.module = module
+        self.flat = None
+        self.shadow = None
+        self.grad = None
+        self.index = {}          # name -> (offset, numel, shape)
+        self.n_no_decay = 0      # elements [0, n_no_decay) take no weight decay
+        self._ptr_check = []
+
+    def _layout(self):
+        named = [(n, p) for n, p in self.module.named_parameters()]
+        named.sort(key=lambda np_: (0 if is_no_decay(np_[0]) else 1))
+        off = 0
+        index = {}
+        n_no_decay = 0
+        for n, p in named:
+            index[n] = (off, p.numel(), tuple(p.shape))
+            off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
+            if is_no_decay(n):
+                n_no_decay = off
+        return named, index, off, n_no_decay
+
+    def ensure(self):
+        """(Re)build the flat buffer if parameters were moved / replaced since the last call."""
+        if self.flat is not None and all(p.data_ptr() == ptr for p, ptr in self._ptr_check):
+            return False
+        named, index, total, n_no_decay = self._layout()
+        dev = named[0][1].device
+        flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self._ptr_check = []
+        for n, p in named:
+            off, numel, shape = index[n]
+            view = flat[off:off + numel].view(shape)
+            view.copy_(p.data)
+            p.data = view
+            self._ptr_check.append((p, p.data_ptr()))
+        self.flat, self.index, self.n_no_decay = flat, index, n_no_decay
+        self.shadow = None
+        self.grad = None
+        return True
+
+    def refresh_shadow(self):
+        """bf16 copy of every weight: one cast kernel over the flat buffer."""
+        self.ensure()
+        if self.shadow is None:
+            self.shadow = torch.empty(self.flat.numel(), dtype=torch.bfloat16, device=self.flat.device)
+        ops.get().cast(self.flat, torch.bfloat16, out=self.shadow)
+        return self.shadow
+
+    def shadow_view(self, name):
+        off, numel, shape = self.index[name]
+        return self.shadow[off:off + numel].view(shape)
+
+    def grad_buffer(self):
+        self.ensure()
+        if self.grad is None:
+            self.grad = torch.zeros_like(self.flat)
+        return self.grad
+
+    def grad_views(self):
+        g = self.grad_buffer()
+        return {n: g[off:off + numel].view(shape) for n, (off, numel, shape) in self.index.items()}
+
+
+class ExgModule(torch.nn.Module):
+    """Base of the drop-in model classes: owns the FlatParams and the compute dtype."""
+
+    def _exg_init(self, compute_dtype=None):
+        object.__setattr__(self, "_flat", FlatParams(self))
+        self.compute_dtype = compute_dtype or default_compute_dtype()
+        self._shadow_stale = True
+
+    def set_compute_dtype(self, dtype):
+        if dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("compute dtype must be torch.float32 or torch.bfloat16")
+        self.compute_dtype = dtype
+        return self
+
+    def flat_params(self):
+        self._flat.ensure()
+        return self._flat
+
+    def _weights(self):
+        """Returns wT(name) -> weight tensor in compute dtype.  Refreshes the bf16 shadow when training
+        (weights change every step) or when it has never been built."""
+        T = self.compute_dtype
+        fp = self._flat
+        rebuilt = fp.ensure()
+        if T == torch.float32:
+            params = dict(self.named_parameters())
+            return lambda name: params[name]
+        if rebuilt or fp.shadow is None or self.training or self._shadow_stale or torch.is_grad_enabled():
+            fp.refresh_shadow()
+            self._shadow_stale = False
+        return fp.shadow_view
+
+    def load_state_dict(self, state_dict, strict=True, **kw):
+        # accept checkpoints saved from a DDP wrapper (keys carry "module.":
+        # train/main_egoexo4d_distributed.py:716-717,870)
+        if state_dict and all(k.startswith("module.") for k in state_dict):
+            state_dict = {k[len("module."):]: v for k, v in state_dict.items()}
+        self._shadow_stale = True
+        return super().load_state_dict(state_dict, strict=strict, **kw)

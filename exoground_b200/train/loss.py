@@ -1,0 +1,172 @@
+"""Drop-in replacement of the reference's train/loss.py: get_loss / get_mask_from_time / get_text_pos.
+
+The logits-sized work (the masked bidirectional MIL-NCE of loss.py:234-278 and its gradient, the
+per-text max of loss.py:283-286) runs in libexg.so kernels (exg_nce_fwd / exg_nce_bwd / exg_own_max);
+the remaining arithmetic touches vectors of at most B*T or B*N elements and is written with
+static-shape masked torch ops (no boolean indexing, no .item()), so the whole step stays
+CUDA-graph capturable.  `logits` may come from exoground_b200's TemporalAligner (zero-copy
+stage-major storage) or from the reference model (copied once into stage-major layout).
+"""
+import torch
+import torch.nn.functional as F
+from torch.nn.utils.rnn import pad_sequence
+
+from .. import ops
+from ..model.functional import NceLossFn
+
+INV_TEMP = 1.0 / 0.07      # train/loss.py:68-69 (logits / 0.07 for args.sim == 'cos')
+
+
+def get_mask_from_time(start_list, end_list, num_timestamp, num_text, device='cuda'):
+    """bool [B, num_text, T]: 1 where start <= t < end (reference train/loss.py:26-43, minus its prints).
+    Built on the host from the python lists and copied once."""
+    start = pad_sequence([torch.FloatTensor(i) for i in start_list], batch_first=True,
+                         padding_value=num_timestamp + 1e2)
+    end = pad_sequence([torch.FloatTensor(i) for i in end_list], batch_first=True, padding_value=-1e2)
+    if start.shape[1] != num_text:
+        # the reference broadcasts a [B, max_len] tensor against num_text and fails when they differ
+        raise RuntimeError(f"get_mask_from_time: longest start list has {start.shape[1]} entries but "
+                           f"num_text={num_text} (reference train/loss.py:32-42 requires them equal)")
+    steps = torch.arange(num_timestamp, dtype=torch.float32)[None, None, :]
+    mask = (start[:, :, None] <= steps) & (steps < end[:, :, None])
+    return (mask.to(device, non_blocking=True), start.to(device, non_blocking=True),
+            end.to(device, non_blocking=True))
+
+
+def get_text_pos(start_list, end_list, device='cuda'):
+    """[B, N, 2] padded (start, end) (reference train/loss.py:46-54)."""
+    start = pad_sequence([torch.FloatTensor(i) for i in start_list], batch_first=True, padding_value=0)
+    end = pad_sequence([torch.FloatTensor(i) for i in end_list], batch_first=True, padding_value=0)
+    return torch.stack((start, end), dim=-1).to(device, non_blocking=True)
+
+
+def _stage_major(lg):
+    """[B,S,T,B,N] (any strides) -> contiguous [S, B*T, B*N]; zero-copy for exoground_b200 outputs."""
+    B, S, T, _, N = lg.shape
+    x = lg.permute(1, 0, 2, 3, 4)
+    if not x.is_contiguous():
+        x = x.contiguous()
+    return x.view(S, B * T, B * N)
+
+
+def _nce_value(sums, wr, wc):
+    ra, rp, ca, cp = sums
+    tiny = 1e-38
+    v = torch.log(ra) - torch.log(rp.clamp(min=tiny))
+    t = torch.log(ca.clamp(min=tiny)) - torch.log(cp.clamp(min=tiny))
+    z = torch.zeros((), device=ra.device)
+    return torch.where(wr != 0, v * wr, z).sum() + torch.where(wc != 0, t * wc, z).sum()
+
+
+def _weights(row_mask, col_mask, S):
+    """wr/wc such that sum_s,r wr*v + sum_s,c wc*t == (v[:, rows].mean() + t[:, cols].mean()) / 2."""
+    rm, cm = row_mask.float(), col_mask.float()
+    return rm / (2.0 * S * rm.sum()), cm / (2.0 * S * cm.sum())
+
+
+def _masked_quantile(x, mask, q):
+    return torch.nanquantile(torch.where(mask, x, torch.full_like(x, float('nan'))), q)
+
+
+def _masked_standardise(x, mask):
+    n = mask.float().sum()
+    mean = torch.where(mask, x, torch.zeros_like(x)).sum() / n
+    var = torch.where(mask, (x - mean) ** 2, torch.zeros_like(x)).sum() / (n - 1)      # unbiased, as Tensor.std
+    return (x - mean) / var.sqrt()
+
+
+def get_loss(input_data, video_seq, text_embed, video_padding_mask, text_padding_mask, logits, args,
+             abs_text_pos=None):
+    """Same contract as reference train/loss.py::get_loss for args.model == 'init'
+    (returns the loss dict; 'loss' is differentiable)."""
+    if args.model not in ('init',):
+        raise NotImplementedError("get_loss: only args.model='init' is implemented on the CUDA path "
+                                  "(cotrain / learn_agreement: see exoground_b200.train.agreement)")
+    if getattr(args, 'learn_agreement', 0):
+        raise NotImplementedError("learn_agreement branch not built yet")
+    if args.sim != 'cos':
+        raise NotImplementedError("only args.sim == 'cos' is supported")
+    K = ops.get()
+    ld_raw, lj_raw = logits['logits_dual'], logits['logits_joint']
+    device = ld_raw.device
+    B, T, _ = video_seq.shape
+    N = text_embed.shape[1]
+    ld, lj = _stage_major(ld_raw), _stage_major(lj_raw)
+    E, D = ld.shape[0], lj.shape[0]
+    loss_dict = {}
+
+    tgt, _, _ = get_mask_from_time(input_data['start'], input_data['end'], num_timestamp=T, num_text=N,
+                                   device=device)                                   # bool [B,N,T]
+    valid = ~text_padding_mask.bool()                                               # [B,N]
+    tgt = tgt & valid[:, :, None]
+    tgt_u8 = tgt.to(torch.uint8).contiguous()
+    col_valid = valid.reshape(-1).to(torch.uint8).contiguous()
+    rowp = tgt.any(dim=1).reshape(-1)                                               # [B*T]
+    colp = tgt.any(dim=2).reshape(-1)                                               # [B*N]
+
+    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP)
+    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP)
+    wr_d, wc_d = _weights(rowp, colp, E)
+    wr_j, wc_j = _weights(rowp, colp, D)
+    use_th = args.loss_threshold > 0
+    use_head = bool(args.use_alignability_head)
+
+    if not use_th:
+        loss_dual = NceLossFn.apply(ld, sums_d, tgt_u8, col_valid, wr_d, wc_d, (B, T, N), INV_TEMP)
+        loss_joint = NceLossFn.apply(lj, sums_j, tgt_u8, col_valid, wr_j, wc_j, (B, T, N), INV_TEMP)
+    else:
+        with torch.no_grad():
+            loss_dual = _nce_value(sums_d, wr_d, wc_d)
+            loss_joint = _nce_value(sums_j, wr_j, wc_j)
+    loss_dict['loss-dual'] = loss_dual.detach()
+    loss_dict['loss-joint'] = loss_joint.detach()
+
+    if use_th or use_head:
+        with torch.no_grad():
+            vflat = valid.reshape(-1)
+            # the reference indexes per-text vectors compacted over *valid* columns with masks compacted over
+            # columns *with positives* (loss.py:298,304,337-347): only consistent when they coincide.
+            md = K.own_max(ld.detach(), E - 1, B, T, N).reshape(-1) * INV_TEMP         # loss.py:283
+            mj = K.own_max(lj.detach(), D - 1, B, T, N).reshape(-1) * INV_TEMP         # loss.py:285
+            metric = -(_masked_standardise(md, vflat) + _masked_standardise(mj, vflat))
+            keep = vflat & (metric <= _masked_quantile(metric, vflat, args.loss_threshold))
+            rowp_th = (tgt & keep.view(B, N, 1)).any(dim=1).reshape(-1)
+        if use_th:
+            loss_dict['loss-dual-all'] = loss_dual.detach()
+            loss_dict['loss-joint-all'] = loss_joint.detach()
+            wr_dt, wc_dt = _weights(rowp_th, keep, E)
+            wr_jt, wc_jt = _weights(rowp_th, keep, D)
+            loss_dual_th = NceLossFn.apply(ld, sums_d, tgt_u8, col_valid, wr_dt, wc_dt, (B, T, N), INV_TEMP)
+            loss_joint_th = NceLossFn.apply(lj, sums_j, tgt_u8, col_valid, wr_jt, wc_jt, (B, T, N), INV_TEMP)
+            loss_dict['loss-dual'] = loss_dual_th.detach()
+            loss_dict['loss-joint'] = loss_joint_th.detach()
+        if use_head:
+            with torch.no_grad():
+                qd, qj = _masked_quantile(md, vflat, 0.5), _masked_quantile(mj, vflat, 0.5)
+                lab = torch.full_like(metric, 2.0)
+                lab = torch.where((md > qd) & (mj > qj), torch.ones_like(lab), lab)
+                lab = torch.where((md < qd) & (mj < qj), torch.zeros_like(lab), lab)
+                if abs_text_pos is not None:
+                    c = abs_text_pos.reshape(B * N, -1).float().mean(-1)
+                    lab = torch.where((c < 0.2) | (c > 0.8), torch.zeros_like(lab), lab)
+                sel = vflat & (lab != 2)
+                selw = sel.float()
+                y = torch.where(sel, lab, torch.zeros_like(lab))
+                n_sel = selw.sum()
+                pos_weight = n_sel / y.sum() - 1.0                                    # 1/mean(y) - 1
+            la_j = logits['joint_logits_alignability'][:, 2, :, 0].reshape(-1).float()   # 3rd stage hard-coded (:344)
+            bce = F.binary_cross_entropy_with_logits(la_j, y, pos_weight=pos_weight, reduction='none')
+            loss_bce_joint = (bce * selw).sum() / n_sel
+            loss_dict['loss-joint-bce'] = loss_bce_joint.detach()
+            loss_dict['alignability_top1'] = ((((la_j > 0).float() == y).float() * selw).sum() / n_sel).detach()
+
+    nce_weight = 0 if args.optim_policy == 'bce' else 1
+    if use_th:
+        loss_dict['loss-total'] = ((loss_dual + loss_joint) / 2).detach()
+        loss = (loss_dual_th + loss_joint_th) / 2
+    else:
+        loss = (loss_dual + loss_joint) / 2
+    if use_head:
+        loss = loss * nce_weight + loss_bce_joint
+    loss_dict['loss'] = loss
+    return loss_dict
