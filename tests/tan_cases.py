@@ -1,0 +1,101 @@
+"""Shared TAN parity case: drop-in TemporalAligner + get_loss + backward against a golden fixture of
+the reference (tests/golden/*.npz).  Used by the CPU host-logic test (fake backend, fp32) and by the
+GPU parity tests (CUDA kernels, fp32 and bf16)."""
+import os
+
+import numpy as np
+import torch
+
+from exoground_b200.model import TemporalAligner
+from exoground_b200.train import loss as exg_loss
+from exoground_b200.utils import synth
+from tests.shapes import tan_shapes
+
+SUB = 997
+
+
+def load_golden(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name + ".npz")))
+
+
+def rel_l2(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).norm() / b.norm().clamp(min=1e-30)).item()
+
+
+def close(a, b, rtol, atol, what=""):
+    a = torch.as_tensor(np.asarray(a.detach().cpu() if torch.is_tensor(a) else a), dtype=torch.float32)
+    b = torch.as_tensor(np.asarray(b), dtype=torch.float32)
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    assert torch.isfinite(a).all(), f"{what}: non-finite"
+    assert torch.allclose(a, b, rtol=rtol, atol=atol), \
+        f"{what}: max abs err {(a - b).abs().max().item():.3e} (ref max {b.abs().max().item():.3e})"
+
+
+def run_tan_case(g, losses_cfg, device, compute_dtype, sub=None, check_grads=True):
+    """Tolerances (BASELINE.json north star): fp32 -> logits/loss rel 1e-4, grads rel-L2 1e-3;
+    bf16 -> logits/loss 2e-2 (relative to the tensor's scale), grads rel-L2 5e-2."""
+    fp32 = compute_dtype == torch.float32
+    E, D, B, T, N, d_in, np_seed = [int(x) for x in g["meta"]]
+    m = TemporalAligner(E, D, use_alignability_head=1, video_embed_dim=d_in, text_embed_dim=d_in,
+                        compute_dtype=compute_dtype)
+    m.load_state_dict(synth.fill_state_dict(tan_shapes(E, D, d_in, head=1)))
+    m = m.to(device)
+    b = synth.tan_batch(B=B, T=T, N=N, d_video=d_in, d_text=d_in)
+    video, text = b["video"].to(device), b["text"].to(device)
+    vmask, tmask = b["video_padding_mask"].to(device), b["text_padding_mask"].to(device)
+    gen = torch.Generator().manual_seed(1234)
+    abs_pos = torch.rand(B, N, 2, generator=gen).to(device)
+    valid = ~b["text_padding_mask"]
+    inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
+    for i, (th, al, use_abs) in enumerate(losses_cfg):
+        m.zero_grad()
+        np.random.seed(np_seed)
+        out = m(video, text, vmask, tmask, None)
+        args = synth.tan_args(loss_threshold=th, use_alignability_head=al)
+        L = exg_loss.get_loss(inp, video, text, vmask, tmask, out, args, abs_pos if use_abs else None)
+        for k, v in L.items():
+            if not fp32 and k == "alignability_top1":
+                continue          # a thresholded count: not a smooth quantity
+            close(v, g[f"loss{i}/{k}"], rtol=1e-4 if fp32 else 2e-2, atol=1e-5 if fp32 else 2e-3, what=f"loss{i}/{k}")
+    L["loss"].backward()
+    for k, v in out.items():
+        a = v.detach().float().cpu()
+        ref = torch.as_tensor(g[f"out/{k}"])
+        if k.startswith("logits_"):
+            if sub:
+                a = a[:, :, ::sub[0], :, ::sub[1]]
+            vm = valid[:, ::sub[1]] if sub else valid
+            a, ref = a[:, :, :, vm], ref[:, :, :, vm]
+        elif k == "dual_feature_text":
+            a, ref = a[valid], ref[valid]
+        elif k == "dual_feature_video" and sub:
+            a = a[:, :, ::sub[0], ::16]
+        scale = ref.abs().max().item()
+        if fp32:
+            close(a, ref, rtol=1e-4, atol=1e-4 * scale, what=k)
+        else:
+            assert (a - ref).abs().max().item() <= 2e-2 * scale + 1e-3, f"{k}: {(a - ref).abs().max().item()} vs scale {scale}"
+    if fp32:
+        sim = (out["logits_dual"][:, -1] + out["logits_joint"][:, -1]).float().cpu() / 2
+        own = torch.stack([sim[bb, :, bb, :] for bb in range(B)], 0)
+        assert torch.equal(own.argmax(dim=1)[valid], torch.as_tensor(g["argmax_t"])[valid]), \
+            f"argmax-over-time differs (min top-2 gap of the fixture: {float(g['top2_gap_min']):.3e})"
+    if not check_grads:
+        return m
+    worst = ("", 0.0)
+    for name, p in m.named_parameters():
+        if f"grad/{name}" not in g:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, name
+            continue
+        gr = p.grad.detach().float().cpu().reshape(-1)
+        gr = gr if gr.numel() <= 4096 else gr[::SUB]
+        ref = torch.as_tensor(g[f"grad/{name}"])
+        e = rel_l2(gr, ref)
+        if e > worst[1]:
+            worst = (name, e)
+        tol = 1e-3 if fp32 else 5e-2
+        if "pos_embed" in name:
+            tol *= 4     # a handful of rows with tiny gradients
+        assert e <= tol, f"grad {name}: rel-L2 {e:.3e} > {tol}"
+    return m

@@ -14,6 +14,7 @@ from exoground_b200.train import loss as exg_loss
 from exoground_b200.utils import synth
 from tests.fake_backend import TorchBackend
 from tests.shapes import tan_shapes
+from tests.tan_cases import run_tan_case
 
 SUB = 997
 
@@ -36,50 +37,9 @@ def _close(a, b, rtol=1e-4, atol=2e-5, what=""):
     assert torch.allclose(a, b, rtol=rtol, atol=atol), f"{what}: max abs err {(a - b).abs().max().item()}"
 
 
-def _run_tan(g, losses_cfg, sub=None):
-    E, D, B, T, N, d_in, np_seed = [int(x) for x in g["meta"]]
-    m = TemporalAligner(E, D, use_alignability_head=1, video_embed_dim=d_in, text_embed_dim=d_in,
-                        compute_dtype=torch.float32)
-    m.load_state_dict(synth.fill_state_dict(tan_shapes(E, D, d_in, head=1)))
-    b = synth.tan_batch(B=B, T=T, N=N, d_video=d_in, d_text=d_in)
-    gen = torch.Generator().manual_seed(1234)
-    abs_pos = torch.rand(B, N, 2, generator=gen)
-    valid = ~b["text_padding_mask"]
-    inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
-    for i, (th, al, use_abs) in enumerate(losses_cfg):
-        m.zero_grad()
-        np.random.seed(np_seed)
-        out = m(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
-        args = synth.tan_args(loss_threshold=th, use_alignability_head=al)
-        L = exg_loss.get_loss(inp, b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], out,
-                              args, abs_pos if use_abs else None)
-        for k, v in L.items():
-            _close(float(v), g[f"loss{i}/{k}"], rtol=1e-4, atol=1e-5, what=f"loss{i}/{k}")
-    L["loss"].backward()
-    for k, v in out.items():
-        a = v.detach()
-        ref = g[f"out/{k}"]
-        if k.startswith("logits_"):
-            if sub:
-                a = a[:, :, ::sub[0], :, ::sub[1]]
-            vm = valid[:, ::sub[1]] if sub else valid
-            _close(a[:, :, :, vm], ref[:, :, :, vm.numpy()], what=k)
-        elif k == "dual_feature_text":
-            _close(a[valid], ref[valid.numpy()], what=k)
-        elif k == "dual_feature_video" and sub:
-            _close(a[:, :, ::sub[0], ::16], ref, atol=5e-5, what=k)
-        else:
-            _close(a, ref, atol=5e-5, what=k)
-    for name, p in m.named_parameters():
-        if f"grad/{name}" not in g:
-            assert p.grad is None or float(p.grad.abs().max()) == 0.0, name
-            continue
-        gr = p.grad.reshape(-1)
-        _close(gr if gr.numel() <= 4096 else gr[::SUB], g[f"grad/{name}"], rtol=2e-3, atol=2e-6, what=f"grad/{name}")
-
-
 def test_tan_small_host_logic(golden_dir):
-    _run_tan(_load(golden_dir, "tan_small"), [(0.0, 0, 0), (0.3, 0, 0), (0.0, 1, 1), (0.5, 1, 0)])
+    run_tan_case(_load(golden_dir, "tan_small"), [(0.0, 0, 0), (0.3, 0, 0), (0.0, 1, 1), (0.5, 1, 0)], "cpu",
+                 torch.float32)
 
 
 def test_tan_sim_helpers(golden_dir):

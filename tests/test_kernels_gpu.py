@@ -1,0 +1,298 @@
+"""GPU unit tests: every libexg.so kernel (through the C ABI, via exoground_b200.ops.backend) against
+the torch restatement of its op spec (tests/fake_backend.py) on the same seeded inputs.
+Tolerances: fp32 paths rel 1e-4 (north star); bf16 paths 2e-2 relative to the output scale."""
+import math
+
+import pytest
+import torch
+
+from exoground_b200 import ops
+from exoground_b200.ops import lib as L
+from tests.fake_backend import TorchBackend
+
+pytestmark = pytest.mark.gpu
+REF = TorchBackend()
+DEV = "cuda"
+
+
+@pytest.fixture(scope="module")
+def K():
+    assert torch.cuda.is_available()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    b = ops.get()
+    assert b.name == "cuda"
+    return b
+
+
+def _g(seed):
+    return torch.Generator(device="cpu").manual_seed(seed)
+
+
+def _rand(shape, dtype, seed, scale=1.0):
+    return (torch.randn(shape, generator=_g(seed)) * scale).to(dtype).to(DEV)
+
+
+def _check(got, ref, dtype, what="", scale=None):
+    got, ref = got.float(), ref.float()
+    assert got.shape == ref.shape, (what, got.shape, ref.shape)
+    assert torch.isfinite(got).all(), f"{what}: non-finite output"
+    s = scale if scale is not None else max(ref.abs().max().item(), 1e-6)
+    err = (got - ref).abs().max().item() / s
+    tol = 2e-4 if dtype == torch.float32 else 2e-2
+    assert err <= tol, f"{what}: rel-to-scale err {err:.3e} > {tol}"
+
+
+# ------------------------------------------------------------------------------------------- GEMM
+def _gemm_case(K, M, N, Kd, tA, tB, dtype, impl, epilogue=L.EPI_NONE, bias=False, batch=0, bcast_b=False,
+               out_dtype=None, seed=0):
+    sa = (Kd, M) if tA else (M, Kd)
+    sb = (Kd, N) if tB else (N, Kd)
+    if batch:
+        sa = (batch,) + sa
+        if not bcast_b:
+            sb = (batch,) + sb
+    A = _rand(sa, dtype, seed + 1)
+    B = _rand(sb, dtype, seed + 2)
+    bs = _rand((N,), torch.float32, seed + 3) if bias else None
+    cs = ((batch, M, N) if batch else (M, N))
+    aux = None
+    if epilogue == L.EPI_RESID:
+        aux = _rand(cs, torch.float32, seed + 4)
+        out_dtype = torch.float32
+    elif epilogue in (L.EPI_QGELU_BWD, L.EPI_RELU_BWD):
+        aux = _rand(cs, dtype, seed + 4)
+    kw = dict(transA=tA, transB=tB, bias=bs, epilogue=epilogue, aux=aux, out_dtype=out_dtype)
+    want_pre = epilogue == L.EPI_QGELU
+    got = K.gemm(A, B, impl=impl, want_preact=want_pre, **kw)
+    ref = REF.gemm(A, B, want_preact=want_pre, **kw)
+    torch.cuda.synchronize()
+    scale = math.sqrt(Kd)
+    if want_pre:
+        _check(got[0], ref[0], dtype, "gemm out", scale)
+        _check(got[1], ref[1], dtype, "gemm preact", scale)
+    else:
+        _check(got, ref, dtype, f"gemm M{M} N{N} K{Kd} tA{tA} tB{tB} epi{epilogue}", scale)
+
+
+@pytest.mark.parametrize("tA,tB", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("shape", [(128, 128, 64), (256, 512, 512), (200, 72, 136), (64, 8, 40), (1, 16, 8)])
+def test_gemm_simt_fp32(K, tA, tB, shape):
+    _gemm_case(K, *shape, tA, tB, torch.float32, L.GEMM_SIMT, bias=True)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("epi", [L.EPI_NONE, L.EPI_QGELU, L.EPI_RESID, L.EPI_QGELU_BWD, L.EPI_RELU, L.EPI_RELU_BWD])
+def test_gemm_simt_epilogues(K, dtype, epi):
+    _gemm_case(K, 192, 136, 96, False, False, dtype, L.GEMM_SIMT, epilogue=epi, bias=True)
+
+
+def test_gemm_simt_small_n_and_batch(K):
+    _gemm_case(K, 100, 1, 512, False, False, torch.float32, L.GEMM_SIMT, bias=True)
+    _gemm_case(K, 100, 2, 512, False, False, torch.bfloat16, L.GEMM_SIMT, bias=True, out_dtype=torch.float32)
+    _gemm_case(K, 96, 40, 64, False, False, torch.float32, L.GEMM_SIMT, batch=3)
+    _gemm_case(K, 96, 40, 64, False, False, torch.float32, L.GEMM_SIMT, batch=3, bcast_b=True)
+
+
+@pytest.mark.parametrize("tA,tB", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("shape", [(128, 128, 64), (256, 256, 512), (384, 512, 2048), (8192, 1536, 512),
+                                   (200, 72, 136), (130, 264, 72), (64, 8, 64)])
+def test_gemm_tc_layouts(K, tA, tB, shape):
+    _gemm_case(K, *shape, tA, tB, torch.bfloat16, L.GEMM_TC)
+
+
+@pytest.mark.parametrize("epi", [L.EPI_NONE, L.EPI_QGELU, L.EPI_RESID, L.EPI_QGELU_BWD, L.EPI_RELU, L.EPI_RELU_BWD])
+def test_gemm_tc_epilogues(K, epi):
+    _gemm_case(K, 300, 520, 512, False, False, torch.bfloat16, L.GEMM_TC, epilogue=epi, bias=True)
+
+
+def test_gemm_tc_fp32_out_splitk_batch(K):
+    # weight-gradient shape: tiny M x N, long K -> split-K with fp32 atomics
+    _gemm_case(K, 512, 512, 8192, True, True, torch.bfloat16, L.GEMM_TC, out_dtype=torch.float32)
+    _gemm_case(K, 1536, 512, 12288, True, True, torch.bfloat16, L.GEMM_TC, out_dtype=torch.float32)
+    _gemm_case(K, 256, 264, 512, False, False, torch.bfloat16, L.GEMM_TC, batch=3)
+    _gemm_case(K, 256, 264, 512, False, False, torch.bfloat16, L.GEMM_TC, batch=3, bcast_b=True)
+    _gemm_case(K, 192, 136, 520, False, True, torch.bfloat16, L.GEMM_TC, batch=2)
+    _gemm_case(K, 264, 64, 520, True, True, torch.bfloat16, L.GEMM_TC, batch=2, out_dtype=torch.float32)
+
+
+def test_gemm_auto_dispatch(K):
+    _gemm_case(K, 256, 512, 512, False, False, torch.bfloat16, L.GEMM_AUTO, bias=True)
+    _gemm_case(K, 100, 1, 512, False, False, torch.bfloat16, L.GEMM_AUTO, bias=True, out_dtype=torch.float32)
+    _gemm_case(K, 256, 512, 512, False, False, torch.float32, L.GEMM_AUTO, bias=True)
+
+
+# ------------------------------------------------------------------------------------------- row-wise
+@pytest.mark.parametrize("xd,yd", [(torch.float32, torch.float32), (torch.float32, torch.bfloat16),
+                                   (torch.bfloat16, torch.float32)])
+@pytest.mark.parametrize("C", [512, 768, 4096])
+def test_layernorm_fwd_bwd(K, xd, yd, C):
+    rows = 77
+    x = _rand((rows, C), xd, 1, 2.0)
+    g = 1 + 0.1 * _rand((C,), torch.float32, 2)
+    b = 0.1 * _rand((C,), torch.float32, 3)
+    add = _rand((7, C), torch.float32, 4)
+    y, y2 = K.layernorm_fwd(x, g, b, out_dtype=yd, y2_dtype=torch.float32, add=add, add_period=7)
+    yr, y2r = REF.layernorm_fwd(x, g, b, out_dtype=yd, y2_dtype=torch.float32, add=add, add_period=7)
+    _check(y, yr, yd, "ln fwd")
+    _check(y2, y2r, torch.float32, "ln fwd y2")
+    dy1 = _rand((rows, C), yd, 5)
+    dy2 = _rand((rows, C), yd, 6)
+    dres = _rand((rows, C), torch.float32, 7)
+    got = K.layernorm_bwd(dy1, x, g, dy2=dy2, dres=dres, dxT_dtype=torch.bfloat16)
+    ref = REF.layernorm_bwd(dy1, x, g, dy2=dy2, dres=dres, dxT_dtype=torch.bfloat16)
+    _check(got[0], ref[0], torch.float32 if xd == torch.float32 and yd == torch.float32 else torch.bfloat16, "ln dx")
+    _check(got[1], ref[1], torch.bfloat16, "ln dxT")
+    _check(got[2], ref[2], torch.float32 if yd == torch.float32 and xd == torch.float32 else torch.bfloat16, "ln dgamma")
+    _check(got[3], ref[3], torch.float32 if yd == torch.float32 else torch.bfloat16, "ln dbeta")
+
+
+def test_layernorm_rowmaps(K):
+    B, T, N, C = 3, 5, 2, 512
+    x = _rand((B * T, C), torch.float32, 1)
+    g = 1 + 0.1 * _rand((C,), torch.float32, 2)
+    b = 0.1 * _rand((C,), torch.float32, 3)
+    out = torch.zeros(B * (T + N), C, device=DEV)
+    outr = torch.zeros(B * (T + N), C, device=DEV)
+    K.layernorm_fwd(x, g, b, out_dtype=torch.float32, out=out, out_map=(T, T + N, 0))
+    REF.layernorm_fwd(x, g, b, out_dtype=torch.float32, out=outr, out_map=(T, T + N, 0))
+    _check(out, outr, torch.float32, "ln fwd map")
+    dy = _rand((B * (T + N), C), torch.float32, 4)
+    got = K.layernorm_bwd(dy, x, g, map1=(T, T + N, 0))
+    ref = REF.layernorm_bwd(dy, x, g, map1=(T, T + N, 0))
+    for a, r, n in zip(got, ref, ("dx", "dxT", "dg", "db")):
+        if r is not None:
+            _check(a, r, torch.float32, "ln bwd map " + n)
+
+
+def test_add_rows_and_l2norm(K):
+    B, T, N, C = 4, 6, 3, 512
+    xv = _rand((B * T, C), torch.float32, 1)
+    xt = _rand((B * N, C), torch.float32, 2)
+    pos = _rand((T, C), torch.float32, 3)
+    out = torch.zeros(B * (T + N), C, device=DEV)
+    outr = torch.zeros_like(out)
+    for Kb, o in ((K, out), (REF, outr)):
+        Kb.add_rows(xv, B * T, add=pos, add_period=T, out=o, map_out=(T, T + N, 0))
+        Kb.add_rows(xt, B * N, out=o, map_out=(N, T + N, T))
+    _check(out, outr, torch.float32, "concat")
+    g1, _ = K.add_rows(out, B * N, map_x=(N, T + N, T), out_dtype=torch.bfloat16)
+    g2, _ = REF.add_rows(out, B * N, map_x=(N, T + N, T), out_dtype=torch.bfloat16)
+    _check(g1, g2, torch.bfloat16, "gather")
+    for dt in (torch.float32, torch.bfloat16):
+        st = _rand((2, B * (T + N), C), dt, 5)
+        y, inv = K.l2norm_fwd(st.view(-1, C), 2 * B * T, map_x=(T, T + N, 0))
+        yr, invr = REF.l2norm_fwd(st.view(-1, C), 2 * B * T, map_x=(T, T + N, 0))
+        _check(y, yr, dt, "l2 fwd")
+        _check(inv, invr, dt, "l2 inv")
+        dy = _rand(tuple(y.shape), dt, 6)
+        dx, dxr = torch.zeros_like(st), torch.zeros_like(st)
+        K.l2norm_bwd(dy, yr, invr, dx.view(-1, C), map_dx=(T, T + N, 0))
+        REF.l2norm_bwd(dy, yr, invr, dxr.view(-1, C), map_dx=(T, T + N, 0))
+        _check(dx, dxr, dt, "l2 bwd")
+
+
+@pytest.mark.parametrize("shape", [(12288, 512), (777, 1536), (300, 2), (300, 1), (5, 2048)])
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_colsum(K, shape, dt):
+    x = _rand(shape, dt, 1)
+    _check(K.colsum(x), REF.colsum(x), torch.float32, "colsum", scale=math.sqrt(shape[0]) * 3)
+
+
+def test_cast_and_stage_mean(K):
+    x = _rand((1000003,), torch.float32, 1)
+    assert torch.equal(K.cast(x, torch.bfloat16), x.to(torch.bfloat16))
+    assert torch.equal(K.cast(x.to(torch.bfloat16), torch.float32), x.to(torch.bfloat16).float())
+    st = _rand((6, 40, 512), torch.bfloat16, 2)
+    m, mT = K.stage_mean(st, outT_dtype=torch.bfloat16)
+    mr, mTr = REF.stage_mean(st, outT_dtype=torch.bfloat16)
+    _check(m, mr, torch.float32, "stage_mean")
+    _check(mT, mTr, torch.bfloat16, "stage_mean T")
+
+
+# ------------------------------------------------------------------------------------------- attention
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,Sq,Sk,masked", [(2, 64, 64, True), (3, 96, 96, True), (2, 100, 100, True),
+                                            (2, 8, 200, True), (1, 300, 300, False)])
+def test_attention(K, dt, B, Sq, Sk, masked):
+    H, d = 8, 64
+    self_attn = Sq == Sk
+    if self_attn:
+        qkv = _rand((B * Sq, 3 * H * d), dt, 1)
+        q, k, v = qkv[:, :512], qkv[:, 512:1024], qkv[:, 1024:]
+    else:
+        q = _rand((B * Sq, H * d), dt, 1)
+        kv = _rand((B * Sk, 2 * H * d), dt, 2)
+        k, v = kv[:, :512], kv[:, 512:]
+    pad = None
+    if masked:
+        pad = torch.zeros(B, Sk, dtype=torch.uint8, device=DEV)
+        for b in range(B):
+            pad[b, Sk - 1 - 3 * b - (Sk // 3 if b == 0 else 0):] = 1
+    scale = d ** -0.5
+    o, lse = K.attn_fwd(q, k, v, pad, B, H, Sq, Sk, scale)
+    orf, lser = REF.attn_fwd(q, k, v, pad, B, H, Sq, Sk, scale)
+    _check(o, orf, dt, "attn o")
+    _check(lse, lser, dt, "attn lse")
+    do = _rand((B * Sq, H * d), dt, 3)
+    if self_attn:
+        dqkv, dqkvr = torch.zeros_like(qkv), torch.zeros_like(qkv)
+        K.attn_bwd(q, k, v, orf, do, lser, pad, dqkv[:, :512], dqkv[:, 512:1024], dqkv[:, 1024:], B, H, Sq, Sk, scale)
+        REF.attn_bwd(q, k, v, orf, do, lser, pad, dqkvr[:, :512], dqkvr[:, 512:1024], dqkvr[:, 1024:], B, H, Sq, Sk, scale)
+        _check(dqkv, dqkvr, dt, "attn dqkv")
+    else:
+        dq, dkv = torch.zeros_like(q), torch.zeros_like(kv)
+        dqr, dkvr = torch.zeros_like(q), torch.zeros_like(kv)
+        K.attn_bwd(q, k, v, orf, do, lser, pad, dq, dkv[:, :512], dkv[:, 512:], B, H, Sq, Sk, scale)
+        REF.attn_bwd(q, k, v, orf, do, lser, pad, dqr, dkvr[:, :512], dkvr[:, 512:], B, H, Sq, Sk, scale)
+        _check(dq, dqr, dt, "attn dq")
+        _check(dkv, dkvr, dt, "attn dkv")
+
+
+# ------------------------------------------------------------------------------------------- NCE
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("S,B,T,N", [(2, 3, 16, 8), (3, 5, 24, 4), (6, 16, 64, 32)])
+def test_nce(K, dt, S, B, T, N):
+    Lg = (torch.rand((S, B * T, B * N), generator=_g(1)) * 2 - 1).to(dt).to(DEV)
+    tgt = (torch.rand((B, N, T), generator=_g(2)) < 0.15).to(torch.uint8).to(DEV)
+    cv = (torch.rand((B * N,), generator=_g(3)) < 0.8).to(torch.uint8).to(DEV)
+    tgt = tgt * cv.view(B, N, 1)
+    it = 1 / 0.07
+    got = K.nce_fwd(Lg, tgt, cv, B, T, N, it)
+    ref = REF.nce_fwd(Lg, tgt, cv, B, T, N, it)
+    for a, r, n in zip(got, ref, ("row_all", "row_pos", "col_all", "col_pos")):
+        _check(a, r, torch.float32, "nce " + n)
+    wr = (torch.rand((B * T,), generator=_g(4)) * (torch.rand((B * T,), generator=_g(5)) < 0.7)).to(DEV)
+    wc = (torch.rand((B * N,), generator=_g(6)) * (torch.rand((B * N,), generator=_g(7)) < 0.7)).to(DEV)
+    wr = wr * (ref[1][0] > 0)
+    wc = wc * (ref[3][0] > 0)
+    G = K.nce_bwd(Lg, tgt, cv, ref, wr, wc, B, T, N, it)
+    Gr = REF.nce_bwd(Lg, tgt, cv, ref, wr, wc, B, T, N, it)
+    _check(G, Gr, dt, "nce G")
+    _check(K.own_max(Lg, S - 1, B, T, N), REF.own_max(Lg, S - 1, B, T, N), torch.float32, "own_max")
+
+
+# ------------------------------------------------------------------------------------------- optimizer
+def test_adamw_and_ema(K):
+    n = 100003
+    p, g = _rand((n + 1,), torch.float32, 1)[:n], _rand((n + 1,), torch.float32, 2)[:n]
+    m, v = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    sh = torch.zeros(n, dtype=torch.bfloat16, device=DEV)
+    pr, mr, vr, shr = p.clone(), m.clone(), v.clone(), sh.clone()
+    for step in (1, 2, 3):
+        K.adamw(p, g, m, v, sh, 1e-3, 0.9, 0.999, 1e-8, 1e-2, step, 0.5)
+        REF.adamw(pr, g, mr, vr, shr, 1e-3, 0.9, 0.999, 1e-8, 1e-2, step, 0.5)
+    _check(p, pr, torch.float32, "adamw p")
+    _check(m, mr, torch.float32, "adamw m")
+    _check(v, vr, torch.float32, "adamw v")
+    _check(sh, shr, torch.bfloat16, "adamw shadow")
+    opt_p = torch.nn.Parameter(_rand((n + 1,), torch.float32, 1)[:n].clone())
+    opt = torch.optim.AdamW([opt_p], lr=1e-3, weight_decay=1e-2)
+    for _ in range(3):
+        opt_p.grad = g * 0.5
+        opt.step()
+    _check(p, opt_p.detach(), torch.float32, "adamw vs torch.optim.AdamW")
+    t, o = _rand((n,), torch.float32, 3), _rand((n,), torch.float32, 4)
+    tr = t.clone()
+    K.ema(t, o, 0.999)
+    REF.ema(tr, o, 0.999)
+    _check(t, tr, torch.float32, "ema")

@@ -1,0 +1,42 @@
+"""GPU parity tests proper: the drop-in TemporalAligner + get_loss + backward, running on the CUDA
+kernels through the C ABI, against golden fixtures produced by the unmodified reference."""
+import numpy as np
+import pytest
+import torch
+
+from exoground_b200 import ops
+from tests.tan_cases import load_golden, run_tan_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _cuda_backend():
+    assert torch.cuda.is_available()
+    assert ops.get().name == "cuda"
+
+
+def test_tan_small_fp32(golden_dir):
+    run_tan_case(load_golden(golden_dir, "tan_small"), [(0.0, 0, 0), (0.3, 0, 0), (0.0, 1, 1), (0.5, 1, 0)],
+                 "cuda", torch.float32)
+
+
+def test_tan_small_bf16(golden_dir):
+    run_tan_case(load_golden(golden_dir, "tan_small"), [(0.0, 0, 0), (0.3, 0, 0), (0.0, 1, 1), (0.5, 1, 0)],
+                 "cuda", torch.bfloat16)
+
+
+def test_tan_cfg1_fp32(golden_dir):
+    """BASELINE.json configs[0]: TAN E6D6, B=8, T=64, N=32 (D_in=1024), fp32."""
+    run_tan_case(load_golden(golden_dir, "tan_cfg1"), [(0.0, 0, 0), (0.5, 1, 0)], "cuda", torch.float32, sub=(8, 4))
+
+
+def test_tan_cfg1_bf16(golden_dir):
+    run_tan_case(load_golden(golden_dir, "tan_cfg1"), [(0.0, 0, 0), (0.5, 1, 0)], "cuda", torch.bfloat16, sub=(8, 4))
+
+
+def test_launches_counted():
+    before = ops.lib.launch_count()
+    x = torch.randn(8, 512, device="cuda")
+    ops.get().cast(x, torch.bfloat16)
+    assert ops.lib.launch_count() == before + 1
