@@ -79,7 +79,7 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
               float* __restrict__ dgamma, float* __restrict__ dbeta, long rows, int C, float eps) {
   extern __shared__ float red[];  // [warps][2*C]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int nwarps = kLnBwdThreads / 32;
+  const int nwarps = blockDim.x / 32;
   float4 ag[NCH], ab[NCH];
 #pragma unroll
   for (int j = 0; j < NCH; ++j) ag[j] = ab[j] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -173,7 +173,7 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += kLnBwdThreads) {
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
     float t = 0.f;
     for (int w = 0; w < nwarps; ++w) t += red[(size_t)w * 2 * C + i];
     if (i < C) { if (dgamma) atomicAdd(dgamma + i, t); }
@@ -391,7 +391,8 @@ extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1
   EXG_CHECK_ARG(rowmap_ok(map1) && (!dy2 || rowmap_ok(map2)), "layernorm_bwd: bad row map");
   if (rows <= 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
-  const int nwarps = kLnBwdThreads / 32;
+  const int threads = C > 2048 ? 128 : kLnBwdThreads;   // keeps the [warps][2C] reduction buffer under 227 KB
+  const int nwarps = threads / 32;
   long want = (rows + nwarps - 1) / nwarps;
   int blocks = (int)(want < 2L * exg_num_sms() ? want : 2L * exg_num_sms());
   size_t smem = (size_t)nwarps * 2 * C * sizeof(float);
@@ -400,7 +401,7 @@ extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1
   do {                                                                                            \
     auto kfn = ln_bwd_kernel<NCH>;                                                                \
     if (smem > 48 * 1024) cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    kfn<<<blocks, kLnBwdThreads, smem, s>>>(dy1, dy1_dtype, map1, dy2, dy2_dtype, map2, x, x_dtype, \
+    kfn<<<blocks, threads, smem, s>>>(dy1, dy1_dtype, map1, dy2, dy2_dtype, map2, x, x_dtype, \
                                             gamma, mean, rstd, dres, dx, dxT, dxT_dtype, dgamma,  \
                                             dbeta, rows, C, eps);                                 \
   } while (0)

@@ -66,7 +66,12 @@ def _gemm_case(K, M, N, Kd, tA, tB, dtype, impl, epilogue=L.EPI_NONE, bias=False
     got = K.gemm(A, B, impl=impl, want_preact=want_pre, **kw)
     ref = REF.gemm(A, B, want_preact=want_pre, **kw)
     torch.cuda.synchronize()
+    # fp32: error relative to the typical magnitude sqrt(K); bf16 outputs: one bf16 ulp (2^-8) of the largest
+    # output on each side of the comparison, i.e. relative to max |ref|
     scale = math.sqrt(Kd)
+    if (out_dtype or dtype) == torch.bfloat16:
+        r0 = ref[0] if want_pre else ref
+        scale = max(scale, r0.float().abs().max().item() / 2)
     if want_pre:
         _check(got[0], ref[0], dtype, "gemm out", scale)
         _check(got[1], ref[1], dtype, "gemm preact", scale)
@@ -97,6 +102,14 @@ def test_gemm_simt_small_n_and_batch(K):
 @pytest.mark.parametrize("shape", [(128, 128, 64), (256, 256, 512), (384, 512, 2048), (8192, 1536, 512),
                                    (200, 72, 136), (130, 264, 72), (64, 8, 64)])
 def test_gemm_tc_layouts(K, tA, tB, shape):
+    M, N, _ = shape
+    if (tA and M % 8) or (tB and N % 8):
+        # an MN-major operand whose leading dimension is not a multiple of 16 bytes cannot be described to TMA:
+        # the forced tensor-core path must refuse it loudly (AUTO dispatch falls back to the SIMT kernel)
+        with pytest.raises(L.ExgError):
+            _gemm_case(K, *shape, tA, tB, torch.bfloat16, L.GEMM_TC)
+        _gemm_case(K, *shape, tA, tB, torch.bfloat16, L.GEMM_AUTO)
+        return
     _gemm_case(K, *shape, tA, tB, torch.bfloat16, L.GEMM_TC)
 
 
