@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py — training clips/sec of the TAN E6D6 alignment hot path on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Own arm: one process per GPU (torchrun for N>1), per-GPU batch fixed (weak scaling).  A step is one full
+training step of TemporalAligner E6D6 (T=64, N=32 sentences, 4096-d features, bf16 compute, fp32 master
+weights): forward -> MIL-NCE + alignability loss -> backward -> gradient all-reduce -> fused AdamW.
+  value : device-resident inputs, K steps between barrier+synchronize, CUDA events, max over ranks;
+  e2e   : the same K steps through TanTrainStep.step(batch) with pinned-host inputs (H2D copies, host-built
+          target masks and the loss read-back inside the timed region).
+  roofline / breakdown : per-kernel-class CUDA-event timings of one profiled step (exg_profile_*).
+  cpu_baseline : the CPU oracle port (oracle/, fp32 torch restatement of the reference) fwd+loss+bwd on a
+          bounded sample of the same workload, all host threads (rank 0, N=1 only).
+Reference arm (--impl reference): the reference's own CPU path for this step.  /root/reference does not travel
+to the GPU box, so it times the oracle port (kind "port") with every host thread; when the reference tree is
+present (build container) it times the unmodified reference modules instead (kind "reference").
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+E_LAYERS, D_LAYERS, T, N, D_IN = 6, 6, 64, 32, 4096
+PER_GPU_BATCH = 128
+CPU_SAMPLE_BATCH = 8
+METRIC = "train clips/sec (fwd+bwd) TAN E6D6 T=64"
+
+
+def train_gflop_per_clip(B):
+    """Algorithmic-minimum FLOPs of one training clip: fwd = pre-proj (T+N)*2*D*C +
+    video encoder + joint encoder + similarity head (quadratic in B); train = 3x fwd."""
+    C, F = 512, 2048
+    per_tok = lambda S: 2 * C * 3 * C + 2 * C * C + 4 * C * F + 4 * S * C
+    pre = (T + N) * 2 * D_IN * C
+    enc = E_LAYERS * T * per_tok(T)
+    joint = D_LAYERS * (T + N) * per_tok(T + N)
+    sim = (E_LAYERS + D_LAYERS) * T * B * N * 2 * C
+    return 3 * (pre + enc + joint + sim) / 1e9
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        busy = [x for x in sm if mx and x > 0.5 * mx] or sm
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ CPU arms
+def cpu_step_fn(B, kind_pref="auto"):
+    """Returns (kind, cores, callable) timing one fwd+loss+bwd of the CPU path at batch B, fp32."""
+    import numpy as np
+    import torch
+    from exoground_b200.utils import synth
+    from exoground_b200.model import TemporalAligner
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    b = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, zero_pad_text=False)
+    args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
+    shapes = {k: tuple(v.shape) for k, v in TemporalAligner(E_LAYERS, D_LAYERS, use_alignability_head=1,
+                                                            video_embed_dim=D_IN, text_embed_dim=D_IN).state_dict().items()}
+    sd = synth.fill_state_dict(shapes)
+    from oracle import ref_import
+    if kind_pref != "port" and ref_import.available():
+        r = ref_import.load()
+        with ref_import.quiet():
+            m = r.tan_model.TemporalAligner(E_LAYERS, D_LAYERS, use_alignability_head=1)
+        m.load_state_dict(sd)
+        inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
+
+        def step():
+            m.zero_grad()
+            np.random.seed(0)
+            out = m(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
+            with ref_import.quiet():
+                L = r.loss.get_loss(inp, b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"],
+                                    out, args, None)
+            L["loss"].backward()
+            return float(L["loss"])
+        return "reference", cores, step
+    from oracle import tan_oracle, loss_oracle
+    sd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+
+    def step():
+        for v in sd.values():
+            v.grad = None
+        np.random.seed(0)
+        ps = tan_oracle.draw_pos_starts(T, N)
+        out = tan_oracle.tan_forward(sd, E_LAYERS, D_LAYERS, b["video"], b["text"], b["video_padding_mask"],
+                                     b["text_padding_mask"], ps, use_alignability_head=1)
+        L = loss_oracle.tan_loss(out, b["start"], b["end"], b["text_padding_mask"], T, N, 0.5, 1)
+        L["loss"].backward()
+        return float(L["loss"])
+    return "port", cores, step
+
+
+def time_cpu(B, steps, warmup, kind_pref="auto"):
+    kind, cores, step = cpu_step_fn(B, kind_pref)
+    for _ in range(warmup):
+        step()
+    ts = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        step()
+        ts.append(time.perf_counter() - t0)
+    sec = sum(ts) / len(ts)
+    return {"value": B / sec, "unit": "clips/s", "cores": cores, "kind": kind,
+            "sample": f"TAN E6D6 fwd+loss+bwd fp32, batch {B} of the {PER_GPU_BATCH}-clip step (T={T}, N={N}, "
+                      f"D_in={D_IN}), {steps} timed + {warmup} warm-up steps, torch CPU {cores} threads",
+            "ms_per_step": sec * 1e3}
+
+
+def workload_config(n_gpus):
+    return {"workload": f"TAN E6D6 full train step (fwd + MIL-NCE/alignability loss + bwd + AdamW), T={T}, "
+                        f"N={N} sentences, D_in={D_IN}, batch {PER_GPU_BATCH}/GPU (BASELINE.json configs[1])",
+            "global_batch": PER_GPU_BATCH * n_gpus, "per_gpu_batch": PER_GPU_BATCH, "seq_len": T,
+            "parallelism": f"dp{n_gpus}", "loss": "loss_threshold=0.5, use_alignability_head=1",
+            "l2": "no flush: per-step working set (2 x 403 MB bf16 logits + saved activations, > 3 GB) exceeds the 126 MB L2"}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    r = time_cpu(CPU_SAMPLE_BATCH, max(1, a.steps), max(1, min(a.warmup, 2)))
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": "clips/s", "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(a.gpus),
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def run_ours(a):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from exoground_b200 import ops
+    from exoground_b200.ops import lib
+    from exoground_b200.model import TemporalAligner
+    from exoground_b200.train.step import TanTrainStep
+    from exoground_b200.utils import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (exoground_b200 has no CPU fallback; use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    pg = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+        pg = dist.group.WORLD
+    assert ops.get().name == "cuda"
+    B = PER_GPU_BATCH
+
+    torch.manual_seed(888)
+    np.random.seed(888 + rank)
+    model = TemporalAligner(E_LAYERS, D_LAYERS, use_alignability_head=1, video_embed_dim=D_IN,
+                            text_embed_dim=D_IN, compute_dtype=torch.bfloat16)
+    args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
+    tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg)
+    # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
+    # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
+    batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
+    for k in ("video", "text", "video_padding_mask", "text_padding_mask"):
+        batch[k] = batch[k].pin_memory()
+    h2d = tr.load_batch(batch)
+    c0 = lib.launch_count()
+    tr.prepare()
+    torch.cuda.synchronize()
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- launches per step: one eager (un-captured) step goes through every C-ABI entry
+    # ---- device-resident timing
+    for _ in range(a.warmup):
+        tr.run()
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        tr.run()
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1) / a.steps
+    # ---- end-to-end timing through the public step() call
+    for _ in range(min(a.warmup, 3)):
+        tr.step(batch)
+    sync_all()
+    t0 = time.perf_counter()
+    e0.record()
+    last = 0.0
+    for _ in range(a.steps):
+        last = tr.step(batch)
+    e1.record()
+    sync_all()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+
+    # ---- one profiled eager step: per-kernel-class CUDA-event timings + launch count
+    graph, tr.graph = tr.graph, None
+    tr.run(); torch.cuda.synchronize()
+    c1 = lib.launch_count()
+    lib.profile_begin()
+    tr.run()
+    prof = lib.profile_end()
+    launches_per_step = lib.launch_count() - c1
+    tr.graph = graph
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
+        breakdown = {}
+        tot = sum(v["ms"] for v in prof.values())
+        for k, v in prof.items():
+            tensor = k.startswith("gemm") or k.startswith("attn")
+            rate = v["work"] / (v["ms"] * 1e-3) / (1e12 if tensor else 1e9) if v["ms"] > 0 else 0.0
+            breakdown[k] = {"ms": round(v["ms"], 4), "launches": v["launches"], "share": round(v["ms"] / tot, 4),
+                            ("tflops" if tensor else "gbs"): round(rate, 1)}
+        top = max(prof, key=lambda k: prof[k]["ms"])
+        tv = prof[top]
+        tensor = top.startswith("gemm") or top.startswith("attn")
+        ach = tv["work"] / (tv["ms"] * 1e-3) / (1e12 if tensor else 1e9)
+        roof = {"kernel": top, "bound": "tensor" if tensor else "hbm", "achieved": round(ach, 2),
+                "peak": tf_peak if tensor else hbm_peak, "unit": "TFLOP/s" if tensor else "GB/s",
+                "frac": round(ach / (tf_peak if tensor else hbm_peak), 4), "traffic": None, "peak_source": src,
+                "launches": tv["launches"], "avg_launch_ms": round(tv["ms"] / tv["launches"], 5),
+                "how": "sum of algorithmic work / sum of CUDA-event durations of every launch of this kernel "
+                       "class in one profiled eager step"}
+        gb = B * world
+        value = gb / (ms * 1e-3)
+        gf = train_gflop_per_clip(B)
+        line = {"metric": METRIC, "value": round(value, 1), "unit": "clips/s", "n_gpus": world, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world),
+                "e2e": {"value": round(gb / (ms_e2e * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_e2e, 4),
+                        "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last},
+                "gpu_launches": int(launches_per_step * a.steps),
+                "launches_per_step": int(launches_per_step), "cuda_graph": not a.no_graph,
+                "model_tflops": round(value / world * gf / 1e3, 1),
+                "model_tflops_frac_of_peak": round(value / world * gf / 1e3 / tf_peak, 4),
+                "train_gflop_per_clip": round(gf, 2),
+                "roofline": roof, "breakdown": breakdown, "clocks": clocks}
+        if world == 1 and not a.no_cpu:
+            r = time_cpu(CPU_SAMPLE_BATCH, 3, 1, "port")
+            line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -311,6 +311,7 @@ extern "C" int exg_attn_fwd(const void* q, const void* k, const void* v, int dty
   static bool once = false;
   if (!once) { rc = set_smem(attn_fwd_kernel, smem, "attn_fwd"); if (rc) return rc; once = true; }
   dim3 grid((Sq + BT - 1) / BT, H, B);
+  ExgProfScope prof(EXG_PC_ATTN_FWD, 4.0 * B * H * Sq * Sk * d, stream);
   attn_fwd_kernel<<<grid, NTHREADS, smem, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("attn_fwd");
   return 0;
@@ -335,6 +336,7 @@ extern "C" int exg_attn_bwd(const void* q, const void* k, const void* v, const v
     once = true;
   }
   cudaStream_t s = (cudaStream_t)stream;
+  ExgProfScope prof(EXG_PC_ATTN_BWD, 10.0 * B * H * Sq * Sk * d, stream);
   attn_bwd_dq_kernel<<<dim3((Sq + BT - 1) / BT, H, B), NTHREADS, smem_dq, s>>>(a);
   EXG_LAUNCH_CHECK("attn_bwd_dq");
   attn_bwd_dkv_kernel<<<dim3((Sk + BT - 1) / BT, H, B), NTHREADS, smem_dkv, s>>>(a);

@@ -40,6 +40,24 @@ void exg_count_launch(int n = 1);
     }                                                                            \
   } while (0)
 
+// ---------------------------------------------------------------- per-class launch profiling
+// exg_profile_begin()/exg_profile_end(): while active, every launch site brackets its kernel with a CUDA
+// event pair on the launching stream (bench.py's roofline numbers come from these).
+enum ExgProfClass {
+  EXG_PC_GEMM_TC = 0, EXG_PC_GEMM_SIMT, EXG_PC_ATTN_FWD, EXG_PC_ATTN_BWD, EXG_PC_LN_FWD, EXG_PC_LN_BWD,
+  EXG_PC_ROWWISE, EXG_PC_NCE_FWD, EXG_PC_NCE_BWD, EXG_PC_OPTIM, EXG_PC_COUNT
+};
+bool exg_profiling();
+void exg_prof_open(int cls, double work, cudaStream_t s);
+void exg_prof_close(cudaStream_t s);
+struct ExgProfScope {
+  cudaStream_t s; bool on;
+  ExgProfScope(int cls, double work, void* stream) : s((cudaStream_t)stream), on(exg_profiling()) {
+    if (on) exg_prof_open(cls, work, s);
+  }
+  ~ExgProfScope() { if (on) exg_prof_close(s); }
+};
+
 static inline bool exg_valid_dtype(int d) { return d == EXG_F32 || d == EXG_BF16; }
 static inline size_t exg_dtype_size(int d) { return d == EXG_F32 ? 4 : 2; }
 

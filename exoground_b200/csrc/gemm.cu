@@ -26,5 +26,7 @@ extern "C" int exg_gemm(const exg_gemm_params* p, void* stream) {
       return EXG_EUNSUPPORTED;
     }
   }
+  ExgProfScope prof(impl == EXG_GEMM_TC ? EXG_PC_GEMM_TC : EXG_PC_GEMM_SIMT,
+                    2.0 * p->M * p->N * p->K * p->batch, stream);
   return impl == EXG_GEMM_TC ? exg_gemm_tc(p, stream) : exg_gemm_simt(p, stream);
 }

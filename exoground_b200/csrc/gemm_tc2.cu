@@ -1,0 +1,430 @@
+// gemm_tc2.cu — persistent, warp-specialised bf16 GEMM for sm_100a.
+//
+//   warp 0      : TMA producer   (global -> 128B-swizzled smem ring, mbarrier complete_tx)
+//   warp 1      : MMA issuer     (one elected lane, tcgen05.mma cta_group::1, 128 x BN x 16 per instruction)
+//   warps 2..5  : epilogue       (tcgen05.ld TMEM -> registers -> bias / QuickGELU / ReLU -> 128B-swizzled smem
+//                                 staging -> TMA store, or TMA reduce-add for split-K partial sums)
+//
+// One CTA per SM loops over output tiles (static round-robin).  The fp32 accumulator is double-buffered in
+// TMEM (2 x BN columns), so the epilogue of tile i overlaps the MMAs of tile i+1, and every global access is a
+// TMA transfer (no per-thread global loads or stores in the kernel).  Operands may be K-major or MN-major in
+// global memory (MN-major tiles are fetched as 64-wide column blocks and flagged in the instruction
+// descriptor), so the backward GEMMs need no transposes; weight gradients (short M x N, long K) are split
+// along K and accumulated in fp32 with TMA reduce-add.
+#include "common.cuh"
+#include "sm100.cuh"
+
+using namespace sm100;
+
+namespace {
+
+constexpr int BM = 128, BK = 64, UK = 16;
+constexpr int kEpiWarps = 4;
+constexpr int kThreads = 32 * (2 + kEpiWarps);
+constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
+constexpr int kStageBufs = 4;                      // staging ring per epilogue warp
+constexpr uint32_t kStageBufBytes = 32 * 128;      // 32 rows x 128 B
+
+struct Tc2Args {
+  int M, N, K;
+  int a_mn, b_mn;
+  int out_f32, epilogue;
+  const float* bias;
+  float alpha;
+  int tiles_m, tiles_n, splits, kblocks_per_split, batch;
+  int a_bcast, b_bcast;
+  int has_aux_out;
+};
+
+template <int BN> struct Cfg2 {
+  static constexpr uint32_t kBBytes = BN * BK * 2;
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 3 : 4;
+  static constexpr uint32_t kEpiBytes = kEpiWarps * kStageBufs * kStageBufBytes;     // 64 KB
+  static constexpr uint32_t kSmem = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1,
+                                                  int c2) {
+  asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+struct TileCoord { int m0, n0, z, kb0, nkb; };
+
+__device__ __forceinline__ TileCoord tile_coord(const Tc2Args& p, int tile, int BN) {
+  // order: n fastest, then m, then split, then batch -> CTAs running concurrently share A row blocks in L2
+  TileCoord t;
+  const int tn = tile % p.tiles_n; tile /= p.tiles_n;
+  const int tm = tile % p.tiles_m; tile /= p.tiles_m;
+  const int sp = tile % p.splits;
+  t.z = tile / p.splits;
+  t.m0 = tm * BM; t.n0 = tn * BN;
+  const int kbt = (p.K + BK - 1) / BK;
+  t.kb0 = sp * p.kblocks_per_split;
+  const int kb1 = min(kbt, t.kb0 + p.kblocks_per_split);
+  t.nkb = kb1 - t.kb0;
+  return t;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux, Tc2Args p) {
+  using C_ = Cfg2<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* epi_smem = smem + C_::kStages * C_::kStageBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C_::kEpiBytes);
+  uint64_t* empty = full + C_::kStages;
+  uint64_t* tmem_full = empty + C_::kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;          // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.tiles_m * p.tiles_n * p.splits * p.batch;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C_::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], kEpiWarps); }
+    fence_barrier_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); tma_prefetch_desc(&tmC);
+    if (p.has_aux_out) tma_prefetch_desc(&tmAux);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord t = tile_coord(p, tile, BN);
+        const int za = p.a_bcast ? 0 : t.z, zb = p.b_bcast ? 0 : t.z;
+        for (int i = 0; i < t.nkb; ++i, ++it) {
+          const int s = it % C_::kStages;
+          const uint32_t ph = (it / C_::kStages) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* sa = smem + (size_t)s * C_::kStageBytes;
+          uint8_t* sb = sa + kABytes;
+          const int k0 = (t.kb0 + i) * BK;
+          mbar_arrive_expect_tx(&full[s], C_::kStageBytes);
+          if (!p.a_mn) {
+            tma_load_3d(sa, &tmA, &full[s], k0, t.m0, za);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j) tma_load_3d(sa + j * 8192, &tmA, &full[s], t.m0 + j * 64, k0, za);
+          }
+          if (!p.b_mn) {
+            tma_load_3d(sb, &tmB, &full[s], k0, t.n0, zb);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_3d(sb + j * 8192, &tmB, &full[s], t.n0 + j * 64, k0, zb);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+      const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
+      const uint32_t a_kstep = p.a_mn ? (UK * 128u) : (UK * 2u);
+      const uint32_t b_kstep = p.b_mn ? (UK * 128u) : (UK * 2u);
+      uint32_t it = 0, ti = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
+        const TileCoord t = tile_coord(p, tile, BN);
+        const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue has drained this accumulator stage
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int i = 0; i < t.nkb; ++i, ++it) {
+          const int s = it % C_::kStages;
+          const uint32_t ph = (it / C_::kStages) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + (size_t)s * C_::kStageBytes);
+          const uint32_t sb = sa + kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UK; ++k) {
+            const uint64_t ad = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024u);
+            const uint64_t bd = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
+            umma_bf16(d_tmem, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[s]);
+        }
+        umma_commit(&tmem_full[as]);
+      }
+    }
+  } else {
+    // ===================== epilogue =====================
+    const int ew = warp - 2;                      // staging slot
+    const int lg = warp & 3;                      // TMEM lane group this warp may access
+    uint8_t* stage = epi_smem + (size_t)ew * kStageBufs * kStageBufBytes;
+    uint32_t sbuf = 0;                            // next staging buffer (ring)
+    uint32_t ti = 0;
+    const int cols_per_chunk = p.out_f32 ? 32 : 64;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
+      const TileCoord t = tile_coord(p, tile, BN);
+      const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
+      mbar_wait(&tmem_full[as], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(lg * 32) << 16);
+      const int row0 = t.m0 + lg * 32;
+      const bool rows_live = row0 < p.M;
+      const int n_live = min(BN, p.N - t.n0);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += cols_per_chunk) {
+        const bool live = rows_live && c0 < n_live;      // warp-uniform
+        uint32_t r[64];
+        if (live) {
+          tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+          if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+          tmem_ld_wait();
+        }
+        if (c0 + cols_per_chunk >= BN) {
+          // all TMEM reads of this tile are done: hand the accumulator stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty[as]);
+        }
+        if (!live) continue;
+        // ---- math in the thread = row layout
+        const int ncols = cols_per_chunk;
+        const int nbase = t.n0 + c0;
+#pragma unroll
+        for (int j = 0; j < 64; j += 4) {
+          if (j >= ncols) break;
+          float4 v = make_float4(__uint_as_float(r[j]) * p.alpha, __uint_as_float(r[j + 1]) * p.alpha,
+                                 __uint_as_float(r[j + 2]) * p.alpha, __uint_as_float(r[j + 3]) * p.alpha);
+          if (p.bias && nbase + j < p.N) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + nbase + j));
+            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+          }
+          r[j] = __float_as_uint(v.x); r[j + 1] = __float_as_uint(v.y);
+          r[j + 2] = __float_as_uint(v.z); r[j + 3] = __float_as_uint(v.w);
+        }
+        // ---- optional second output: the pre-activation (bf16), staged and stored first
+        if (p.has_aux_out) {
+          uint8_t* buf = stage + (size_t)(sbuf % kStageBufs) * kStageBufBytes;
+          if (lane == 0) bulk_wait_read<kStageBufs - 1>();
+          __syncwarp();
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            uint4 q;
+            q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
+            q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
+            q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
+            q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
+            *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) { tma_store_3d(&tmAux, buf, nbase, row0, t.z); bulk_commit(); }
+          ++sbuf;
+        }
+        if (p.epilogue == EXG_EPI_QGELU) {
+#pragma unroll
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(quick_gelu(__uint_as_float(r[j])));
+        } else if (p.epilogue == EXG_EPI_RELU) {
+#pragma unroll
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
+        }
+        // ---- stage (128B-swizzled rows) and TMA-store the chunk
+        uint8_t* buf = stage + (size_t)(sbuf % kStageBufs) * kStageBufBytes;
+        if (lane == 0) bulk_wait_read<kStageBufs - 1>();
+        __syncwarp();
+        if (p.out_f32) {
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint4 q = make_uint4(r[u * 4], r[u * 4 + 1], r[u * 4 + 2], r[u * 4 + 3]);
+            *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            uint4 q;
+            q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
+            q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
+            q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
+            q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
+            *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if (p.splits > 1) tma_reduce_add_3d(&tmC, buf, nbase, row0, t.z);
+          else tma_store_3d(&tmC, buf, nbase, row0, t.z);
+          bulk_commit();
+        }
+        ++sbuf;
+      }
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// ---------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 3-D tensor map over [batch][rows][inner] with a {box_inner, box_rows, 1} box, 128B swizzle.
+int make_map(CUtensorMap* out, const void* base, int f32, uint64_t inner, uint64_t rows, uint64_t batch,
+             uint64_t row_stride_elems, uint64_t batch_stride_elems, uint32_t box_inner, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) { exg_set_error("gemm_tc2: cuTensorMapEncodeTiled unavailable"); return EXG_EUNSUPPORTED; }
+  const uint64_t es = f32 ? 4 : 2;
+  cuuint64_t dims[3] = {inner, rows, batch};
+  cuuint64_t strides[2] = {row_stride_elems * es, (batch > 1 ? batch_stride_elems : rows * row_stride_elems) * es};
+  cuuint32_t box[3] = {box_inner, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                  const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    exg_set_error("gemm_tc2: cuTensorMapEncodeTiled failed (%d) inner=%llu rows=%llu batch=%llu ld=%llu",
+                  (int)r, (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)batch,
+                  (unsigned long long)row_stride_elems);
+    return EXG_EINVAL;
+  }
+  return 0;
+}
+
+template <int BN>
+int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+            const Tc2Args& a, cudaStream_t s) {
+  static bool attr_set = false;
+  auto kfn = gemm_tc2_kernel<BN>;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2<BN>::kSmem);
+    if (e != cudaSuccess) { exg_set_error("gemm_tc2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
+    attr_set = true;
+  }
+  const long total = (long)a.tiles_m * a.tiles_n * a.splits * a.batch;
+  const int grid = (int)(total < exg_num_sms() ? total : exg_num_sms());
+  kfn<<<grid, kThreads, Cfg2<BN>::kSmem, s>>>(ta, tb, tc, tx, a);
+  EXG_LAUNCH_CHECK("gemm_tc2");
+  return 0;
+}
+
+bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+double wave_eff(long tiles) {
+  const long sms = exg_num_sms();
+  const long waves = (tiles + sms - 1) / sms;
+  return (double)tiles / (double)(waves * sms);
+}
+
+}  // namespace
+
+// 1 if the persistent TMA-epilogue kernel takes these parameters.
+int exg_gemm_tc2_supported(const exg_gemm_params* p) {
+  if (!p || p->in_dtype != EXG_BF16) return 0;
+  if (p->M <= 0 || p->N <= 0 || p->K <= 0 || p->batch <= 0) return 0;
+  if (p->epilogue != EXG_EPI_NONE && p->epilogue != EXG_EPI_QGELU && p->epilogue != EXG_EPI_RELU) return 0;
+  if (p->aux) return 0;
+  if (p->aux_out && (p->epilogue != EXG_EPI_QGELU || p->out_dtype != EXG_BF16)) return 0;
+  const int es_out = p->out_dtype == EXG_F32 ? 4 : 2;
+  if (p->N < 128 / es_out) return 0;                       // the store box is 128 bytes wide
+  if (p->N % 8 != 0) return 0;
+  if (!al16(p->A) || !al16(p->B) || !al16(p->C) || (p->aux_out && !al16(p->aux_out))) return 0;
+  if (p->lda % 8 || p->ldb % 8 || (p->ldc * es_out) % 16) return 0;
+  if (p->batch > 1 && (p->strideA % 8 || p->strideB % 8 || (p->strideC * es_out) % 16)) return 0;
+  if (p->bias && !al16(p->bias)) return 0;
+  if ((p->transA ? p->M : p->K) < 8 || (p->transB ? p->N : p->K) < 8) return 0;
+  return 1;
+}
+
+int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  Tc2Args a;
+  a.M = q->M; a.N = q->N; a.K = q->K;
+  a.a_mn = q->transA ? 1 : 0; a.b_mn = q->transB ? 1 : 0;
+  a.out_f32 = q->out_dtype == EXG_F32; a.epilogue = q->epilogue;
+  a.bias = q->bias; a.alpha = q->alpha; a.batch = q->batch;
+  a.has_aux_out = q->aux_out ? 1 : 0;
+
+  const int kblocks = (q->K + BK - 1) / BK;
+  const long tm = (q->M + BM - 1) / BM;
+  // tile width: 256 halves the smem traffic per flop; prefer it unless 128 fills the machine much better
+  int bn = 256;
+  {
+    const long t256 = tm * ((q->N + 255) / 256) * q->batch, t128 = tm * ((q->N + 127) / 128) * q->batch;
+    const double e256 = wave_eff(t256), e128 = 0.85 * wave_eff(t128);
+    if (q->N <= 128 || (e128 > e256 && t256 >= exg_num_sms() / 2)) bn = 128;
+  }
+  a.tiles_m = (int)tm; a.tiles_n = (q->N + bn - 1) / bn;
+  const long tiles = tm * a.tiles_n * q->batch;
+  a.splits = 1;
+  if (q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && tiles * 2 <= exg_num_sms() &&
+      kblocks >= 8) {
+    int want = (int)((exg_num_sms() + tiles - 1) / tiles);
+    int maxs = kblocks / 4;
+    a.splits = want < maxs ? want : maxs;
+    if (a.splits < 1) a.splits = 1;
+  }
+  a.kblocks_per_split = (kblocks + a.splits - 1) / a.splits;
+  a.splits = (kblocks + a.kblocks_per_split - 1) / a.kblocks_per_split;
+  if (a.splits > 1) {
+    for (int z = 0; z < q->batch; ++z)
+      EXG_CUDA(cudaMemset2DAsync(reinterpret_cast<float*>(q->C) + (size_t)z * q->strideC, (size_t)q->ldc * 4, 0,
+                                 (size_t)q->N * 4, (size_t)q->M, s));
+  }
+
+  CUtensorMap ta, tb, tc, tx;
+  int rc;
+  a.a_bcast = (q->batch > 1 && q->strideA == 0) ? 1 : 0;
+  a.b_bcast = (q->batch > 1 && q->strideB == 0) ? 1 : 0;
+  const int ba = a.a_bcast ? 1 : q->batch, bb = a.b_bcast ? 1 : q->batch;
+  if (!q->transA) rc = make_map(&ta, q->A, 0, q->K, q->M, ba, q->lda, q->strideA, 64, BM);
+  else            rc = make_map(&ta, q->A, 0, q->M, q->K, ba, q->lda, q->strideA, 64, BK);
+  if (rc) return rc;
+  if (!q->transB) rc = make_map(&tb, q->B, 0, q->K, q->N, bb, q->ldb, q->strideB, 64, bn);
+  else            rc = make_map(&tb, q->B, 0, q->N, q->K, bb, q->ldb, q->strideB, 64, BK);
+  if (rc) return rc;
+  rc = make_map(&tc, q->C, a.out_f32, q->N, q->M, q->batch, q->ldc, q->strideC, a.out_f32 ? 32 : 64, 32);
+  if (rc) return rc;
+  tx = tc;
+  if (q->aux_out) {
+    rc = make_map(&tx, q->aux_out, 0, q->N, q->M, q->batch, q->ldc, q->strideC, 64, 32);
+    if (rc) return rc;
+  }
+  return bn == 256 ? launch2<256>(ta, tb, tc, tx, a, s) : launch2<128>(ta, tb, tc, tx, a, s);
+}

@@ -172,6 +172,7 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
   a.col_all = col_all; a.col_pos = col_pos; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
   const long R = (long)B * T;
   dim3 grid((unsigned)((R + SLAB - 1) / SLAB), (unsigned)S);
+  ExgProfScope prof(EXG_PC_NCE_FWD, (double)S * R * B * N * exg_dtype_size(dtype), stream);
   nce_fwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("nce_fwd");
   return 0;
@@ -192,6 +193,7 @@ extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, co
   a.wr = wr; a.wc = wc; a.G = G; a.g_dtype = g_dtype; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
   const long R = (long)B * T;
   dim3 grid((unsigned)((R + SLAB - 1) / SLAB), (unsigned)S);
+  ExgProfScope prof(EXG_PC_NCE_BWD, (double)S * R * B * N * (exg_dtype_size(dtype) + exg_dtype_size(g_dtype)), stream);
   nce_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("nce_bwd");
   return 0;
@@ -201,6 +203,7 @@ extern "C" int exg_own_max(const void* logits, int dtype, float* own_max, int st
                            void* stream) {
   EXG_CHECK_ARG(logits && own_max && exg_valid_dtype(dtype) && B > 0 && T > 0 && N > 0 && stage >= 0,
                 "own_max: bad argument");
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)B * T * N * exg_dtype_size(dtype), stream);
   own_max_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(logits, dtype, own_max, stage, B, T, N);
   EXG_LAUNCH_CHECK("own_max");
   return 0;

@@ -68,6 +68,7 @@ extern "C" int exg_adamw(float* param, const float* grad, float* exp_avg, float*
   if (n <= 0) return 0;
   const float bc1 = 1.0f - powf(beta1, (float)step);
   const float bc2 = 1.0f - powf(beta2, (float)step);
+  ExgProfScope prof(EXG_PC_OPTIM, (double)n * (28.0 + (shadow_bf16 ? 2.0 : 0.0)), stream);
   adamw_kernel<<<blocks_for(n / 4 + 1), 256, 0, (cudaStream_t)stream>>>(
       param, grad, exp_avg, exp_avg_sq, reinterpret_cast<uint16_t*>(shadow_bf16), n, lr, beta1, beta2, eps,
       weight_decay, bc1, sqrtf(bc2), grad_scale);
@@ -78,6 +79,7 @@ extern "C" int exg_adamw(float* param, const float* grad, float* exp_avg, float*
 extern "C" int exg_ema(float* target, const float* online, long n, float m, void* stream) {
   EXG_CHECK_ARG(target && online, "ema: null pointer");
   if (n <= 0) return 0;
+  ExgProfScope prof(EXG_PC_OPTIM, (double)n * 12.0, stream);
   ema_kernel<<<blocks_for(n), 256, 0, (cudaStream_t)stream>>>(target, online, n, m);
   EXG_LAUNCH_CHECK("ema");
   return 0;

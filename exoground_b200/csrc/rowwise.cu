@@ -372,6 +372,7 @@ extern "C" int exg_layernorm_fwd(const void* x, int x_dtype, const float* gamma,
   if (rows <= 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
   int blocks = (int)((rows + 3) / 4);
+  ExgProfScope prof(EXG_PC_LN_FWD, (double)rows * C * (exg_dtype_size(x_dtype) + (y ? exg_dtype_size(y_dtype) : 0) + (y2 ? exg_dtype_size(y2_dtype) : 0)), stream);
   DISPATCH_NCH(C, ln_fwd_kernel<NCH><<<blocks, kLnThreads, 0, s>>>(
                       x, x_dtype, gamma, beta, y, y_dtype, map_y, y2, y2_dtype, add, add_period, mean,
                       rstd, rows, C, eps));
@@ -397,6 +398,7 @@ extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1
   int blocks = (int)(want < 2L * exg_num_sms() ? want : 2L * exg_num_sms());
   size_t smem = (size_t)nwarps * 2 * C * sizeof(float);
   const float eps = 1e-5f;
+  ExgProfScope prof(EXG_PC_LN_BWD, (double)rows * C * (exg_dtype_size(x_dtype) + exg_dtype_size(dy1_dtype) + (dy2 ? exg_dtype_size(dy2_dtype) : 0) + (dres ? 4 : 0) + (dx ? 4 : 0) + (dxT ? exg_dtype_size(dxT_dtype) : 0)), stream);
 #define LN_BWD_CALL                                                                               \
   do {                                                                                            \
     auto kfn = ln_bwd_kernel<NCH>;                                                                \
@@ -421,6 +423,7 @@ extern "C" int exg_add_rows(const float* x, exg_rowmap map_x, const float* x2, e
   EXG_CHECK_ARG(rowmap_ok(map_x) && rowmap_ok(map_out) && (!x2 || rowmap_ok(map_x2)) &&
                     (!add || add_period > 0), "add_rows: bad row map");
   if (rows <= 0) return 0;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * (4.0 + (x2 ? 4 : 0) + (out ? exg_dtype_size(out_dtype) : 0) + (out2 ? exg_dtype_size(out2_dtype) : 0)), stream);
   add_rows_kernel<<<grid_for(rows * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(
       x, map_x, x2, map_x2, add, add_period, out, out_dtype, map_out, out2, out2_dtype, rows, C);
   EXG_LAUNCH_CHECK("add_rows");
@@ -434,6 +437,7 @@ extern "C" int exg_l2norm_fwd(const void* x, int x_dtype, exg_rowmap map_x, void
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096 && rowmap_ok(map_x), "l2norm_fwd: bad C / map");
   if (rows <= 0) return 0;
   int blocks = (int)((rows + 3) / 4);
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * (exg_dtype_size(x_dtype) + exg_dtype_size(y_dtype)), stream);
   DISPATCH_NCH(C, l2n_fwd_kernel<NCH><<<blocks, kLnThreads, 0, (cudaStream_t)stream>>>(
                       x, x_dtype, map_x, y, y_dtype, inv_norm, rows, C));
   EXG_LAUNCH_CHECK("l2norm_fwd");
@@ -449,6 +453,7 @@ extern "C" int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096 && rowmap_ok(map_dx), "l2norm_bwd: bad C / map");
   if (rows <= 0) return 0;
   int blocks = (int)((rows + 3) / 4);
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * (exg_dtype_size(dy_dtype) + exg_dtype_size(y_dtype) + exg_dtype_size(dx_dtype) * (accumulate ? 2 : 1)), stream);
   DISPATCH_NCH(C, l2n_bwd_kernel<NCH><<<blocks, kLnThreads, 0, (cudaStream_t)stream>>>(
                       dy, dy_dtype, y, y_dtype, inv_norm, dx, dx_dtype, map_dx, accumulate, rows, C));
   EXG_LAUNCH_CHECK("l2norm_bwd");
@@ -460,6 +465,7 @@ extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, 
   EXG_CHECK_ARG(x && out && exg_valid_dtype(x_dtype), "colsum: bad argument");
   EXG_CHECK_ARG(N > 0, "colsum: N must be positive");
   cudaStream_t s = (cudaStream_t)stream;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)M * N * exg_dtype_size(x_dtype), stream);
   if (N % 4 != 0 || ldx % 4 != 0) {
     EXG_CHECK_ARG(N <= 65535, "colsum: unaligned N too large");
     colsum_scalar_kernel<<<(unsigned)N, 256, 0, s>>>(x, x_dtype, M, N, ldx, out, accumulate);
@@ -483,6 +489,7 @@ extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, 
 extern "C" int exg_cast(const void* src, int src_dtype, void* dst, int dst_dtype, long n, void* stream) {
   EXG_CHECK_ARG(src && dst && exg_valid_dtype(src_dtype) && exg_valid_dtype(dst_dtype), "cast: bad argument");
   if (n <= 0) return 0;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)n * (exg_dtype_size(src_dtype) + exg_dtype_size(dst_dtype)), stream);
   cast_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(src, src_dtype, dst, dst_dtype, n);
   EXG_LAUNCH_CHECK("cast");
   return 0;
@@ -494,6 +501,7 @@ extern "C" int exg_stage_mean(const void* x, int x_dtype, long stage_stride, int
                 "stage_mean: bad argument");
   EXG_CHECK_ARG(n % 4 == 0 && stage_stride % 4 == 0, "stage_mean: n must be a multiple of 4");
   if (n <= 0) return 0;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)n * (S * exg_dtype_size(x_dtype) + (out ? 4 : 0) + (outT ? exg_dtype_size(outT_dtype) : 0)), stream);
   stage_mean_kernel<<<grid_for(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(x, x_dtype, stage_stride, S,
                                                                           out, outT, outT_dtype, n);
   EXG_LAUNCH_CHECK("stage_mean");

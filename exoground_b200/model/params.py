@@ -33,26 +33,40 @@ class FlatParams:
         self.grad = None
         self.index = {}          # name -> (offset, numel, shape)
         self.n_no_decay = 0      # elements [0, n_no_decay) take no weight decay
+        self.n_used = 0          # elements [n_no_decay, n_used) take weight decay; [n_used, end) never get a gradient
+        self.unused = set()      # parameter names that receive no gradient (torch.optim skips them: grad is None)
         self._ptr_check = []
 
+    def set_unused(self, names):
+        """Move parameters that never receive a gradient (reference: `mlp`, `text_temporal_pos_embed`, ... —
+        the reason for DDP's find_unused_parameters=True, train/main.py:413) to the tail of the flat buffer,
+        which the fused optimizer and the gradient all-reduce skip (torch.optim skips grad=None parameters)."""
+        names = set(names)
+        if names != self.unused:
+            self.unused = names
+            self.flat = None
+
     def _layout(self):
+        def cls(n):
+            return 2 if n in self.unused else (0 if is_no_decay(n) else 1)
         named = [(n, p) for n, p in self.module.named_parameters()]
-        named.sort(key=lambda np_: (0 if is_no_decay(np_[0]) else 1))
+        named.sort(key=lambda np_: cls(np_[0]))
         off = 0
         index = {}
-        n_no_decay = 0
+        ends = [0, 0, 0]
         for n, p in named:
             index[n] = (off, p.numel(), tuple(p.shape))
             off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
-            if is_no_decay(n):
-                n_no_decay = off
-        return named, index, off, n_no_decay
+            ends[cls(n)] = off
+        n_no_decay = ends[0]
+        n_used = max(ends[0], ends[1])
+        return named, index, off, n_no_decay, n_used
 
     def ensure(self):
         """(Re)build the flat buffer if parameters were moved / replaced since the last call."""
         if self.flat is not None and all(p.data_ptr() == ptr for p, ptr in self._ptr_check):
             return False
-        named, index, total, n_no_decay = self._layout()
+        named, index, total, n_no_decay, n_used = self._layout()
         dev = named[0][1].device
         flat = torch.zeros(total, dtype=torch.float32, device=dev)
         self._ptr_check = []
@@ -62,7 +76,7 @@ class FlatParams:
             view.copy_(p.data)
             p.data = view
             self._ptr_check.append((p, p.data_ptr()))
-        self.flat, self.index, self.n_no_decay = flat, index, n_no_decay
+        self.flat, self.index, self.n_no_decay, self.n_used = flat, index, n_no_decay, n_used
         self.shadow = None
         self.grad = None
         return True
@@ -117,7 +131,9 @@ class ExgModule(torch.nn.Module):
         if T == torch.float32:
             params = dict(self.named_parameters())
             return lambda name: params[name]
-        if rebuilt or fp.shadow is None or self.training or self._shadow_stale or torch.is_grad_enabled():
+        managed = getattr(self, "_shadow_managed", False)     # a trainer's fused AdamW keeps the shadow current
+        if rebuilt or fp.shadow is None or self._shadow_stale or \
+                (not managed and (self.training or torch.is_grad_enabled())):
             fp.refresh_shadow()
             self._shadow_stale = False
         return fp.shadow_view

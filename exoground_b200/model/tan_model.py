@@ -81,10 +81,23 @@ class TemporalAligner(ExgModule):
 
     # ------------------------------------------------------------------ pieces
     def _draw(self, n):
+        """Random positional offset (reference tan_model.py:157,189,218: np.random.randint(0, n/2)).  When a
+        trainer has installed device-side offsets (`_pos_offsets`, a list of 0-d int64 CUDA tensors it refreshes
+        before every step) they are consumed in draw order instead, so a captured CUDA graph sees new offsets."""
+        offs = getattr(self, "_pos_offsets", None)
+        if offs is not None:
+            i = self._pos_cursor
+            self._pos_cursor = i + 1
+            return offs[i]
         return int(np.random.randint(0, int(n / 2))) if self.random_pos_start else 0
 
     def _pos_ln(self, table, p0, size, interpolate_from):
-        rows = interp_rows(table, interpolate_from, size) if interpolate_from else table[p0:p0 + size]
+        if interpolate_from:
+            rows = interp_rows(table, interpolate_from, size)
+        elif torch.is_tensor(p0):      # device-side offset (CUDA-graph replay: train/step.py): rows p0 .. p0+size-1
+            rows = table.index_select(0, p0 + torch.arange(size, device=table.device))
+        else:
+            rows = table[p0:p0 + size]
         return Fn.LayerNormFn.apply(rows.contiguous(), self.ln_position_init.weight, self.ln_position_init.bias,
                                     torch.float32)
 
@@ -137,6 +150,7 @@ class TemporalAligner(ExgModule):
     def forward(self, video_embed, lang_embed, video_padding_mask, lang_padding_mask, text_timestamp=None,
                 interpolate_from=None, abs_text_pos=None):
         self._check(video_embed, lang_embed)
+        self._pos_cursor = 0
         wT = self._weights()
         Tc = self.compute_dtype
         B, T, _ = video_embed.shape

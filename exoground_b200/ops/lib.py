@@ -35,6 +35,10 @@ _SIGS = {
     "exg_version": (C.c_int, []),
     "exg_last_error": (C.c_char_p, []),
     "exg_launch_count": (C.c_longlong, []),
+    "exg_profile_classes": (C.c_int, []),
+    "exg_profile_class_name": (C.c_char_p, [C.c_int]),
+    "exg_profile_begin": (C.c_int, []),
+    "exg_profile_end": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
     "exg_gemm": (C.c_int, [C.POINTER(GemmParams), vp]),
     "exg_gemm_tc_supported": (C.c_int, [C.POINTER(GemmParams)]),
     "exg_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, RowMap, vp, C.c_int, vp, C.c_long,
@@ -100,3 +104,17 @@ def check(rc, what):
 
 def launch_count():
     return int(load().exg_launch_count())
+
+
+def profile_begin():
+    check(load().exg_profile_begin(), "exg_profile_begin")
+
+
+def profile_end():
+    """{class name: {"ms", "work", "launches"}} for the launches since profile_begin (synchronises)."""
+    lib = load()
+    n = lib.exg_profile_classes()
+    ms, work, cnt = (C.c_double * n)(), (C.c_double * n)(), (C.c_longlong * n)()
+    check(lib.exg_profile_end(ms, work, cnt), "exg_profile_end")
+    return {lib.exg_profile_class_name(i).decode(): {"ms": ms[i], "work": work[i], "launches": int(cnt[i])}
+            for i in range(n) if cnt[i]}

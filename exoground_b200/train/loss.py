@@ -65,7 +65,16 @@ def _weights(row_mask, col_mask, S):
 
 
 def _masked_quantile(x, mask, q):
-    return torch.nanquantile(torch.where(mask, x, torch.full_like(x, float('nan'))), q)
+    """torch.quantile(x[mask], q) (linear interpolation) with static shapes and no host round trip, so the
+    loss stays CUDA-graph capturable: sort with +inf in the masked slots, then gather the two neighbours."""
+    n = mask.sum()
+    srt = torch.sort(torch.where(mask, x, torch.full_like(x, float('inf')))).values
+    pos = (n - 1).to(x.dtype) * q
+    lo = pos.floor().long().clamp(min=0)
+    hi = torch.minimum(lo + 1, (n - 1).clamp(min=0))
+    w = pos - lo.to(x.dtype)
+    a, b = srt.gather(0, lo.reshape(1))[0], srt.gather(0, hi.reshape(1))[0]     # no 0-d tensor indexing (host sync)
+    return a + (b - a) * w
 
 
 def _masked_standardise(x, mask):
@@ -86,17 +95,23 @@ def get_loss(input_data, video_seq, text_embed, video_padding_mask, text_padding
         raise NotImplementedError("learn_agreement branch not built yet")
     if args.sim != 'cos':
         raise NotImplementedError("only args.sim == 'cos' is supported")
-    K = ops.get()
-    ld_raw, lj_raw = logits['logits_dual'], logits['logits_joint']
-    device = ld_raw.device
+    device = logits['logits_dual'].device
     B, T, _ = video_seq.shape
     N = text_embed.shape[1]
-    ld, lj = _stage_major(ld_raw), _stage_major(lj_raw)
+    if '_exg_tgt' in input_data:        # device-resident target mask prepared by the caller (train/step.py)
+        tgt = input_data['_exg_tgt']
+    else:
+        tgt, _, _ = get_mask_from_time(input_data['start'], input_data['end'], num_timestamp=T, num_text=N,
+                                       device=device)                               # bool [B,N,T]
+    return loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N)
+
+
+def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N):
+    """Device part of get_loss: everything after the host-built target mask (static shapes, no host sync)."""
+    K = ops.get()
+    ld, lj = _stage_major(logits['logits_dual']), _stage_major(logits['logits_joint'])
     E, D = ld.shape[0], lj.shape[0]
     loss_dict = {}
-
-    tgt, _, _ = get_mask_from_time(input_data['start'], input_data['end'], num_timestamp=T, num_text=N,
-                                   device=device)                                   # bool [B,N,T]
     valid = ~text_padding_mask.bool()                                               # [B,N]
     tgt = tgt & valid[:, :, None]
     tgt_u8 = tgt.to(torch.uint8).contiguous()

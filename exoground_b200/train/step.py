@@ -1,0 +1,174 @@
+"""One TAN training step on one GPU (one process per GPU): forward -> MIL-NCE / alignability loss ->
+backward -> gradient all-reduce -> fused AdamW, i.e. the body of the reference's train() loop
+(train/main.py:36-157: autocast forward :75-81, get_loss :83-90, backward :106, optimizer.step :111) with
+the reference's optimiser policy (train/main.py:350-376,418: AdamW, no weight decay for `.ln_` / `.bias`).
+
+B200 design:
+  * parameters, gradients and AdamW moments live in flat fp32 buffers (model/params.py); the optimizer is two
+    launches of exg_adamw (no-decay segment, decay segment) which also refresh the bf16 shadow weights;
+  * the data-parallel replacement of DistributedDataParallel (train/main.py:413) is ONE NCCL all-reduce of the
+    flat gradient buffer per step (sum; the 1/world_size of DDP's mean is folded into the AdamW kernel);
+  * the device part of the step (everything between the H2D copies and the loss read-back) is static-shape
+    and free of host synchronisation, so it is captured once into a CUDA graph and replayed; the random
+    positional offsets of the reference (tan_model.py:157,189) are drawn on the host every step and fed to
+    the graph through tiny device tensors, so replays keep the reference's augmentation semantics.
+"""
+import numpy as np
+import torch
+
+from .. import ops
+from . import loss as exg_loss
+
+
+class TanTrainStep:
+    def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
+                 device="cuda", use_graph=True, process_group=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
+        self.model, self.args = model.to(device), args
+        self.B, self.T, self.N = B, T, N
+        self.lr, self.wd, self.betas, self.eps = lr, wd, betas, eps
+        self.device = torch.device(device)
+        self.use_graph = use_graph
+        self.pg = process_group
+        self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        self.step_count = 0
+        self.graph = None
+        dev = self.device
+        # static device-side inputs (targets of the per-step H2D copies)
+        self.video = torch.zeros(B, T, d_video, device=dev)
+        self.text = torch.zeros(B, N, d_text, device=dev)
+        self.vmask = torch.zeros(B, T, dtype=torch.bool, device=dev)
+        self.tmask = torch.zeros(B, N, dtype=torch.bool, device=dev)
+        self.tgt = torch.zeros(B, N, T, dtype=torch.bool, device=dev)
+        self.abs_pos = torch.zeros(B, N, 2, device=dev)
+        n_draw = 3 if model.use_text_pos_enc else 2
+        self.pos_host = torch.zeros(n_draw, dtype=torch.int64).pin_memory()
+        self.pos_dev = torch.zeros(n_draw, dtype=torch.int64, device=dev)
+        self.loss_out = torch.zeros((), device=dev)
+        self.model._pos_offsets = [self.pos_dev[i] for i in range(n_draw)]
+        self._prepared = False
+
+    # ------------------------------------------------------------------ host -> device
+    def load_batch(self, batch, non_blocking=True):
+        """Copies one host batch (dict of synth.tan_batch / the loaders' collate dict; pinned tensors give
+        asynchronous copies) into the static device buffers and builds the [B,N,T] target mask.
+        Returns the number of bytes copied host->device."""
+        n = 0
+        for dst, key in ((self.video, "video"), (self.text, "text"), (self.vmask, "video_padding_mask"),
+                         (self.tmask, "text_padding_mask")):
+            src = batch[key]
+            dst.copy_(src, non_blocking=non_blocking)
+            n += src.numel() * src.element_size()
+        if "tgt" in batch:
+            tgt = batch["tgt"]
+        else:
+            tgt = exg_loss.get_mask_from_time(batch["start"], batch["end"], self.T, self.N, device="cpu")[0]
+        self.tgt.copy_(tgt, non_blocking=non_blocking)
+        n += tgt.numel()
+        if batch.get("abs_text_pos") is not None:
+            self.abs_pos.copy_(batch["abs_text_pos"], non_blocking=non_blocking)
+            n += self.abs_pos.numel() * 4
+        return n
+
+    def _draw_offsets(self):
+        m = self.model
+        if m.random_pos_start:
+            self.pos_host[0] = int(np.random.randint(0, int(self.T / 2)))
+            k = 1
+            if m.use_text_pos_enc:
+                self.pos_host[k] = int(np.random.randint(0, int(self.N / 2)))
+                k += 1
+            self.pos_host[k] = int(np.random.randint(0, int(self.T / 2)))
+        self.pos_dev.copy_(self.pos_host, non_blocking=True)
+
+    # ------------------------------------------------------------------ device step
+    def _fwd_bwd(self):
+        m = self.model
+        out = m(self.video, self.text, self.vmask, self.tmask, None)
+        L = exg_loss.loss_core(self.tgt, self.tmask, out, self.args,
+                               self.abs_pos if getattr(self.args, "use_abs_text_pos", False) else None,
+                               self.B, self.T, self.N)
+        L["loss"].backward()
+        self.loss_out.copy_(L["loss"].detach())
+
+    def _optimizer(self):
+        fp = self.model.flat_params()
+        K = ops.get()
+        self.step_count += 1
+        b1, b2 = self.betas
+        shadow = fp.shadow if self.model.compute_dtype == torch.bfloat16 else None
+        segs = ((0, fp.n_no_decay, 0.0), (fp.n_no_decay, fp.n_used, self.wd))
+        for lo, hi, wd in segs:
+            if hi > lo:
+                K.adamw(fp.flat[lo:hi], fp.grad[lo:hi], self.m1[lo:hi], self.m2[lo:hi],
+                        shadow[lo:hi] if shadow is not None else None, self.lr, b1, b2, self.eps, wd,
+                        self.step_count, grad_scale=1.0 / self.world)
+
+    def _allreduce(self):
+        if self.world > 1:
+            fp = self.model.flat_params()
+            torch.distributed.all_reduce(fp.grad[:fp.n_used], group=self.pg)
+
+    def prepare(self):
+        """Discovery pass (which parameters get gradients), flat gradient / moment buffers, kernel warm-up and,
+        if enabled, CUDA-graph capture of forward+loss+backward.  Uses whatever is in the static buffers."""
+        m = self.model
+        m.train()
+        for p in m.parameters():
+            p.grad = None
+        self._draw_offsets()
+        self._fwd_bwd()
+        unused = [n for n, p in m.named_parameters() if p.grad is None]
+        fp = m.flat_params()
+        fp.set_unused(unused)
+        fp = m.flat_params()
+        m._shadow_stale = True
+        g = fp.grad_buffer()
+        for n, p in m.named_parameters():
+            off, numel, shape = fp.index[n]
+            p.grad = g[off:off + numel].view(shape) if n not in fp.unused else None
+        self.m1 = torch.zeros_like(fp.flat)
+        self.m2 = torch.zeros_like(fp.flat)
+        if m.compute_dtype == torch.bfloat16:
+            fp.refresh_shadow()
+            m._shadow_stale = False
+            # from here on the shadow is kept fresh by the AdamW kernel itself
+            m._shadow_managed = True
+        torch.cuda.synchronize()
+        if self.use_graph:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    g.zero_()
+                    self._fwd_bwd()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                g.zero_()
+                self._fwd_bwd()
+            torch.cuda.synchronize()
+        g.zero_()
+        self._prepared = True
+
+    def run(self):
+        """Device part of one step on the current static buffers.  Returns the 0-d loss tensor (device)."""
+        if not self._prepared:
+            self.prepare()
+        self._draw_offsets()
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.model.flat_params().grad.zero_()
+            self._fwd_bwd()
+        self._allreduce()
+        self._optimizer()
+        return self.loss_out
+
+    def step(self, batch):
+        """The user-facing call: host batch in, python float loss out (H2D copies and the loss read-back
+        included)."""
+        self.load_batch(batch)
+        return float(self.run().item())

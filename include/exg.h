@@ -35,6 +35,15 @@ const char* exg_last_error(void);
 /* number of kernels this library has launched since load (process-wide; for bench gpu_launches) */
 long long exg_launch_count(void);
 
+/* Per-kernel-class timing for bench.py's roofline: between exg_profile_begin() and exg_profile_end() every
+ * launch is bracketed by a CUDA-event pair on its stream.  exg_profile_end synchronises those events and
+ * fills, per class c < exg_profile_classes(): ms[c] = summed device time, work[c] = summed algorithmic work
+ * (FLOPs for gemm / attention classes, bytes for the row-wise / loss / optimizer classes), launches[c]. */
+int exg_profile_classes(void);
+const char* exg_profile_class_name(int cls);
+int exg_profile_begin(void);
+int exg_profile_end(double* ms, double* work, long long* launches);
+
 /* Row addressing helper used by the row-wise kernels: logical row r of a [rows, C] operand lives at
  * physical row  (r / group) * group_stride + (r % group) + offset.  {rows,rows,0} == contiguous.
  * Lets kernels read/write the video / text slices of a joint [B, T+N, C] buffer in place

@@ -1,0 +1,82 @@
+"""GPU tests of the training step (exoground_b200/train/step.py): the fused flat-buffer AdamW step must track
+torch.optim.AdamW with the reference's two-group policy (train/main.py:350-376,418), and a CUDA-graph replay
+must equal the eager step."""
+import numpy as np
+import pytest
+import torch
+
+from exoground_b200.model import TemporalAligner
+from exoground_b200.model.params import is_no_decay
+from exoground_b200.train import loss as exg_loss
+from exoground_b200.train.step import TanTrainStep
+from exoground_b200.utils import synth
+
+pytestmark = pytest.mark.gpu
+E, D, B, T, N, DIN = 2, 3, 4, 32, 8, 64
+
+
+def _model(dtype):
+    torch.manual_seed(3)
+    m = TemporalAligner(E, D, use_alignability_head=1, video_embed_dim=DIN, text_embed_dim=DIN, compute_dtype=dtype)
+    m.load_state_dict(synth.fill_state_dict({k: v.shape for k, v in m.state_dict().items()}))
+    return m
+
+
+def _batch():
+    return synth.tan_batch(B=B, T=T, N=N, d_video=DIN, d_text=DIN, seed=5)
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_step_matches_torch_adamw_fp32(use_graph):
+    args = synth.tan_args(loss_threshold=0.0, use_alignability_head=0)
+    b = _batch()
+    # eps is raised so that parameters whose gradient is numerical noise (e.g. the key bias, whose true gradient
+    # is zero) do not take +-lr sign steps that differ between two correct implementations
+    lr, wd, steps, eps = 1e-3, 1e-2, 3, 1e-4
+    # ---- ours: fused step
+    m = _model(torch.float32)
+    m.random_pos_start = 0
+    tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=lr, wd=wd, eps=eps, use_graph=use_graph)
+    tr.load_batch(b)
+    losses = [tr.step(b) for _ in range(steps)]
+    # ---- same model class driven by torch.optim.AdamW with the reference's policy
+    r = _model(torch.float32).cuda()
+    r.random_pos_start = 0
+    nd = [p for n, p in r.named_parameters() if is_no_decay(n)]
+    dc = [p for n, p in r.named_parameters() if not is_no_decay(n)]
+    opt = torch.optim.AdamW([{"params": nd, "weight_decay": 0.0}, {"params": dc, "weight_decay": wd}], lr=lr, eps=eps)
+    dev = lambda t: t.cuda()
+    inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
+    ref_losses = []
+    for _ in range(steps):
+        opt.zero_grad(set_to_none=True)
+        out = r(dev(b["video"]), dev(b["text"]), dev(b["video_padding_mask"]), dev(b["text_padding_mask"]), None)
+        L = exg_loss.get_loss(inp, dev(b["video"]), dev(b["text"]), dev(b["video_padding_mask"]),
+                              dev(b["text_padding_mask"]), out, args, None)
+        L["loss"].backward()
+        opt.step()
+        ref_losses.append(float(L["loss"]))
+    assert np.allclose(losses, ref_losses, rtol=1e-4), (losses, ref_losses)
+    assert losses[-1] < losses[0]
+    pr = dict(r.named_parameters())
+    for n, p in m.named_parameters():
+        d = (p.detach() - pr[n].detach()).abs().max().item()
+        assert d <= 2e-5 + 1e-3 * pr[n].detach().abs().max().item() * lr * steps, (n, d)
+    # parameters that never get a gradient are left untouched (torch.optim skips grad=None)
+    for n in ("mlp.weight", "text_temporal_pos_embed"):
+        assert n in m.flat_params().unused
+
+
+def test_graph_replay_equals_eager_bf16():
+    args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
+    b = _batch()
+    out = []
+    for use_graph in (False, True):
+        np.random.seed(11)
+        m = _model(torch.bfloat16)
+        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, wd=1e-2, use_graph=use_graph)
+        tr.load_batch(b)
+        tr.prepare()
+        np.random.seed(12)        # identical positional-offset draws for both runs after preparation
+        out.append([tr.step(b) for _ in range(3)])
+    assert np.allclose(out[0], out[1], rtol=2e-3), out
