@@ -122,9 +122,10 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
-__device__ __forceinline__ float quick_gelu(float v) { return v / (1.0f + __expf(-1.702f * v)); }
+// x * sigmoid(1.702 x).  __fdividef (2 ulp) keeps the GEMM epilogues free of the IEEE-division slow path.
+__device__ __forceinline__ float quick_gelu(float v) { return __fdividef(v, 1.0f + __expf(-1.702f * v)); }
 __device__ __forceinline__ float quick_gelu_grad(float u) {
-  float s = 1.0f / (1.0f + __expf(-1.702f * u));
+  float s = __fdividef(1.0f, 1.0f + __expf(-1.702f * u));
   return s + 1.702f * u * s * (1.0f - s);
 }
 

@@ -4,6 +4,8 @@
 
 int exg_gemm_simt(const exg_gemm_params* p, void* stream);
 int exg_gemm_tc(const exg_gemm_params* p, void* stream);
+int exg_gemm_tc2(const exg_gemm_params* p, void* stream);
+int exg_gemm_tc2_supported(const exg_gemm_params* p);
 
 extern "C" int exg_gemm(const exg_gemm_params* p, void* stream) {
   EXG_CHECK_ARG(p && p->A && p->B && p->C, "gemm: null pointer");
@@ -26,7 +28,17 @@ extern "C" int exg_gemm(const exg_gemm_params* p, void* stream) {
       return EXG_EUNSUPPORTED;
     }
   }
-  ExgProfScope prof(impl == EXG_GEMM_TC ? EXG_PC_GEMM_TC : EXG_PC_GEMM_SIMT,
+  static const int no_tc2 = getenv("EXG_NO_TC2") ? atoi(getenv("EXG_NO_TC2")) : 0;
+  if (impl == EXG_GEMM_TC2) {
+    if (!exg_gemm_tc2_supported(p)) {
+      exg_set_error("gemm: persistent tcgen05 kernel does not support these operands / epilogue");
+      return EXG_EUNSUPPORTED;
+    }
+  } else if (impl == EXG_GEMM_TC && !no_tc2 && p->impl == EXG_GEMM_AUTO && exg_gemm_tc2_supported(p)) {
+    impl = EXG_GEMM_TC2;     // AUTO prefers the persistent TMA-epilogue kernel
+  }
+  ExgProfScope prof(impl == EXG_GEMM_SIMT ? EXG_PC_GEMM_SIMT : EXG_PC_GEMM_TC,
                     2.0 * p->M * p->N * p->K * p->batch, stream);
+  if (impl == EXG_GEMM_TC2) return exg_gemm_tc2(p, stream);
   return impl == EXG_GEMM_TC ? exg_gemm_tc(p, stream) : exg_gemm_simt(p, stream);
 }

@@ -19,6 +19,7 @@ struct SimtArgs {
   const void* aux; long ldaux, sAux;
   void* aux_out;
   float alpha;
+  int splits, k_per_split;   // split-K (fp32 atomics) for short M x N, long K (head weight gradients)
 };
 
 __device__ __forceinline__ float epilogue_apply(const SimtArgs& p, float v, long m, long n, long z,
@@ -41,7 +42,9 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
   __shared__ float As[BK][BM + 4];
   __shared__ float Bs[BK][BN + 4];
   const int tid = threadIdx.x;
-  const long z = blockIdx.z;
+  const long z = blockIdx.z / p.splits;
+  const int split = blockIdx.z % p.splits;
+  const int kbeg = split * p.k_per_split, kend = min(p.K, kbeg + p.k_per_split);
   const long m0 = (long)blockIdx.y * BM, n0 = (long)blockIdx.x * BN;
   const char* Ab = reinterpret_cast<const char*>(p.A);
   const char* Bb = reinterpret_cast<const char*>(p.B);
@@ -57,7 +60,7 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
 
   const int tx = tid % 16, ty = tid / 16;   // micro-tile: rows ty*8.., cols tx*8..
 
-  for (int k0 = 0; k0 < p.K; k0 += BK) {
+  for (int k0 = kbeg; k0 < kend; k0 += BK) {
     // ---- stage A tile (BM x BK) into As[k][m]
     if (!p.transA) {
       const int r = tid / 2, kk = (tid % 2) * 8;
@@ -65,7 +68,7 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int gk = k0 + kk + i;
-        As[kk + i][r] = (gm < p.M && gk < p.K) ? load1(A, p.in_dtype, gm * p.lda + gk) : 0.f;
+        As[kk + i][r] = (gm < p.M && gk < kend) ? load1(A, p.in_dtype, gm * p.lda + gk) : 0.f;
       }
     } else {
       const int kk = tid / 16, mm = (tid % 16) * 8;
@@ -73,7 +76,7 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const long gm = m0 + mm + i;
-        As[kk][mm + i] = (gm < p.M && gk < p.K) ? load1(A, p.in_dtype, (long)gk * p.lda + gm) : 0.f;
+        As[kk][mm + i] = (gm < p.M && gk < kend) ? load1(A, p.in_dtype, (long)gk * p.lda + gm) : 0.f;
       }
     }
     // ---- stage B tile (BK x BN) into Bs[k][n]
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int gk = k0 + kk + i;
-        Bs[kk + i][c] = (gn < p.N && gk < p.K) ? load1(B, p.in_dtype, gn * p.ldb + gk) : 0.f;
+        Bs[kk + i][c] = (gn < p.N && gk < kend) ? load1(B, p.in_dtype, gn * p.ldb + gk) : 0.f;
       }
     } else {           // stored [K,N]
       const int kk = tid / 16, nn = (tid % 16) * 8;
@@ -91,7 +94,7 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const long gn = n0 + nn + i;
-        Bs[kk][nn + i] = (gn < p.N && gk < p.K) ? load1(B, p.in_dtype, (long)gk * p.ldb + gn) : 0.f;
+        Bs[kk][nn + i] = (gn < p.N && gk < kend) ? load1(B, p.in_dtype, (long)gk * p.ldb + gn) : 0.f;
       }
     }
     __syncthreads();
@@ -125,6 +128,7 @@ __global__ void __launch_bounds__(THREADS) gemm_simt_kernel(SimtArgs p) {
       float pre;
       const float o = epilogue_apply(p, v, m, n, z, &pre);
       const long ci = z * p.sC + m * p.ldc + n;
+      if (p.splits > 1) { atomicAdd(reinterpret_cast<float*>(p.C) + ci, o); continue; }
       store1(p.C, p.out_dtype, ci, o);
       if (p.epilogue == EXG_EPI_QGELU && p.aux_out) store1(p.aux_out, p.out_dtype, ci, pre);
     }
@@ -141,7 +145,20 @@ int exg_gemm_simt(const exg_gemm_params* q, void* stream) {
   a.in_dtype = q->in_dtype; a.out_dtype = q->out_dtype; a.epilogue = q->epilogue;
   a.bias = q->bias; a.aux = q->aux; a.ldaux = q->ldaux; a.sAux = q->strideAux; a.aux_out = q->aux_out;
   a.alpha = q->alpha;
-  dim3 grid((unsigned)((q->N + BN - 1) / BN), (unsigned)((q->M + BM - 1) / BM), (unsigned)q->batch);
+  a.splits = 1; a.k_per_split = q->K;
+  const long tiles = (long)((q->N + BN - 1) / BN) * ((q->M + BM - 1) / BM) * q->batch;
+  if (q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && q->batch == 1 &&
+      tiles * 2 <= exg_num_sms() && q->K >= 512) {
+    int want = (int)(2L * exg_num_sms() / tiles);
+    int maxs = q->K / 128;
+    a.splits = want < maxs ? want : maxs;
+    if (a.splits < 1) a.splits = 1;
+    a.k_per_split = ((q->K + a.splits - 1) / a.splits + BK - 1) / BK * BK;
+    a.splits = (q->K + a.k_per_split - 1) / a.k_per_split;
+    if (a.splits > 1)
+      EXG_CUDA(cudaMemset2DAsync(q->C, (size_t)q->ldc * 4, 0, (size_t)q->N * 4, (size_t)q->M, (cudaStream_t)stream));
+  }
+  dim3 grid((unsigned)((q->N + BN - 1) / BN), (unsigned)((q->M + BM - 1) / BM), (unsigned)(q->batch * a.splits));
   gemm_simt_kernel<<<grid, THREADS, 0, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("gemm_simt");
   return 0;

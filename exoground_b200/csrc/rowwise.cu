@@ -14,7 +14,8 @@ __global__ void __launch_bounds__(kLnThreads)
 ln_fwd_kernel(const void* __restrict__ x, int xd, const float* __restrict__ gamma,
               const float* __restrict__ beta, void* __restrict__ y, int yd, exg_rowmap map_y,
               void* __restrict__ y2, int y2d, const float* __restrict__ add, long add_period,
-              float* __restrict__ mean_out, float* __restrict__ rstd_out, long rows, int C, float eps) {
+              float* __restrict__ mean_out, float* __restrict__ rstd_out, long rows, int C, float eps,
+              const float* __restrict__ resid, float* __restrict__ sum_out) {
   const int lane = threadIdx.x & 31;
   const long row = (long)blockIdx.x * (kLnThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -25,6 +26,11 @@ ln_fwd_kernel(const void* __restrict__ x, int xd, const float* __restrict__ gamm
     int col = (j * 32 + lane) * 4;
     if (col < C) {
       v[j] = load4(x, xd, row * C + col);
+      if (resid) {      // residual stream update fused in: s = resid + x, written back as the new stream
+        const float4 r = *reinterpret_cast<const float4*>(resid + row * C + col);
+        v[j].x += r.x; v[j].y += r.y; v[j].z += r.z; v[j].w += r.w;
+        if (sum_out) *reinterpret_cast<float4*>(sum_out + row * C + col) = v[j];
+      }
       s += v[j].x + v[j].y + v[j].z + v[j].w;
     } else {
       v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -375,8 +381,26 @@ extern "C" int exg_layernorm_fwd(const void* x, int x_dtype, const float* gamma,
   ExgProfScope prof(EXG_PC_LN_FWD, (double)rows * C * (exg_dtype_size(x_dtype) + (y ? exg_dtype_size(y_dtype) : 0) + (y2 ? exg_dtype_size(y2_dtype) : 0)), stream);
   DISPATCH_NCH(C, ln_fwd_kernel<NCH><<<blocks, kLnThreads, 0, s>>>(
                       x, x_dtype, gamma, beta, y, y_dtype, map_y, y2, y2_dtype, add, add_period, mean,
-                      rstd, rows, C, eps));
+                      rstd, rows, C, eps, nullptr, nullptr));
   EXG_LAUNCH_CHECK("layernorm_fwd");
+  return 0;
+}
+
+extern "C" int exg_add_layernorm_fwd(const void* x, int x_dtype, const float* resid, float* sum_out,
+                                     const float* gamma, const float* beta, void* y, int y_dtype,
+                                     exg_rowmap map_y, long rows, int C, float eps, void* stream) {
+  EXG_CHECK_ARG(x && resid && sum_out && gamma && beta && y, "add_layernorm_fwd: null pointer");
+  EXG_CHECK_ARG(exg_valid_dtype(x_dtype) && exg_valid_dtype(y_dtype), "add_layernorm_fwd: bad dtype");
+  EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096, "add_layernorm_fwd: C=%d must be a multiple of 4, <= 4096", C);
+  EXG_CHECK_ARG(rowmap_ok(map_y), "add_layernorm_fwd: bad row map");
+  if (rows <= 0) return 0;
+  cudaStream_t s = (cudaStream_t)stream;
+  int blocks = (int)((rows + 3) / 4);
+  ExgProfScope prof(EXG_PC_LN_FWD, (double)rows * C * (exg_dtype_size(x_dtype) + 8 + exg_dtype_size(y_dtype)), stream);
+  DISPATCH_NCH(C, ln_fwd_kernel<NCH><<<blocks, kLnThreads, 0, s>>>(
+                      x, x_dtype, gamma, beta, y, y_dtype, map_y, nullptr, 0, nullptr, 0, nullptr, nullptr,
+                      rows, C, eps, resid, sum_out));
+  EXG_LAUNCH_CHECK("add_layernorm_fwd");
   return 0;
 }
 

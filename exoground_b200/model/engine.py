@@ -41,11 +41,13 @@ def _mask_u8(mask):
 
 
 # ---------------------------------------------------------------------------------- sub-blocks
-def _self_attn_fwd(K, xn, in_w, in_b, out_w, out_b, x_res, key_pad, B, S):
+def _self_attn_fwd(K, xn, in_w, in_b, out_w, out_b, key_pad, B, S):
+    """Returns the residual-branch output (delta, compute dtype); the `x + delta` of tfm_model.py:36 is fused
+    into the LayerNorm that follows (exg_add_layernorm_fwd), so the GEMM epilogue stays a pure TMA store."""
     qkv = K.gemm(xn, in_w, bias=in_b)                                            # [M,3C]
     o, lse = K.attn_fwd(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], key_pad, B, HEADS, S, S, SCALE)
-    x_out = K.gemm(o, out_w, bias=out_b, epilogue=ops.EPI_RESID, aux=x_res, out_dtype=torch.float32)
-    return x_out, (qkv, o, lse)
+    delta = K.gemm(o, out_w, bias=out_b)
+    return delta, (qkv, o, lse)
 
 
 def _self_attn_bwd(K, dxT, saved, xn, in_w, out_w, key_pad, B, S):
@@ -64,10 +66,11 @@ def _self_attn_bwd(K, dxT, saved, xn, in_w, out_w, key_pad, B, S):
     return dxn, dW_in, db_in, dW_out, db_out
 
 
-def _ffn_fwd(K, h, fc_w, fc_b, proj_w, proj_b, x_res):
+def _ffn_fwd(K, h, fc_w, fc_b, proj_w, proj_b):
+    """Returns the FFN branch output (delta); `x + delta` (tfm_model.py:37) is fused into the next LayerNorm."""
     f, u = K.gemm(h, fc_w, bias=fc_b, epilogue=ops.EPI_QGELU, want_preact=True)
-    x_out = K.gemm(f, proj_w, bias=proj_b, epilogue=ops.EPI_RESID, aux=x_res, out_dtype=torch.float32)
-    return x_out, (u, f)
+    delta = K.gemm(f, proj_w, bias=proj_b)
+    return delta, (u, f)
 
 
 def _ffn_bwd(K, dxT, saved, h, fc_w, proj_w):
@@ -103,13 +106,16 @@ class EncoderStackFn(torch.autograd.Function):
             sh = shadows[i] if shadows is not None else {}
             in_wT, out_wT = _w(in_w, sh.get("in_w"), T), _w(out_w, sh.get("out_w"), T)
             fc_wT, pj_wT = _w(fc_w, sh.get("fc_w"), T), _w(pj_w, sh.get("pj_w"), T)
-            xn, _ = K.layernorm_fwd(x, g1, b1, out_dtype=T, out=stages[i - 1] if i > 0 else None)
-            x_mid, att = _self_attn_fwd(K, xn, in_wT, in_b, out_wT, out_b, x, key_pad, B, S)
-            h, _ = K.layernorm_fwd(x_mid, g2, b2, out_dtype=T)
-            x_new, ffn = _ffn_fwd(K, h, fc_wT, fc_b, pj_wT, pj_b, x_mid)
+            if i == 0:
+                xn, _ = K.layernorm_fwd(x, g1, b1, out_dtype=T)
+            else:   # x_i = x_mid_{i-1} + ffn_{i-1}; stage i-1 = ln_1^{(i)}(x_i)  (tfm_model.py:35-38,49-55)
+                xn, x = K.add_layernorm_fwd(d2, x, g1, b1, out_dtype=T, out=stages[i - 1])
+            d1, att = _self_attn_fwd(K, xn, in_wT, in_b, out_wT, out_b, key_pad, B, S)
+            h, x_mid = K.add_layernorm_fwd(d1, x, g2, b2, out_dtype=T)
+            d2, ffn = _ffn_fwd(K, h, fc_wT, fc_b, pj_wT, pj_b)
             saved.append((x, xn, att, x_mid, h, ffn, (in_wT, out_wT, fc_wT, pj_wT)))
-            x = x_new
-        K.layernorm_fwd(x, g_post, b_post, out_dtype=T, out=stages[L - 1])
+            x = x_mid
+        _, x = K.add_layernorm_fwd(d2, x, g_post, b_post, out_dtype=T, out=stages[L - 1])
         ctx.saved = saved
         ctx.x_last = x
         ctx.key_pad = key_pad
@@ -164,20 +170,26 @@ class DecoderStackFn(torch.autograd.Function):
             cin_wT, cout_wT = _w(cin_w, sh.get("in_w"), T), _w(cout_w, sh.get("out_w"), T)
             fc_wT, pj_wT = _w(fc_w, sh.get("fc_w"), T), _w(pj_w, sh.get("pj_w"), T)
             sin_wT, sout_wT = _w(sin_w, sh.get("sin_w"), T), _w(sout_w, sh.get("sout_w"), T)
-            xn, _ = K.layernorm_fwd(x, g1, b1, out_dtype=T)
-            x1, att = _self_attn_fwd(K, xn, sin_wT, sin_b, sout_wT, sout_b, x, tgt_pad, B, N)
-            h2, _ = K.layernorm_fwd(x1, g2, b2, out_dtype=T)
+            if i == 0:
+                xn, _ = K.layernorm_fwd(x, g1, b1, out_dtype=T)
+            else:
+                xn, x = K.add_layernorm_fwd(d3, x, g1, b1, out_dtype=T)
+            d1, att = _self_attn_fwd(K, xn, sin_wT, sin_b, sout_wT, sout_b, tgt_pad, B, N)
+            h2, x1 = K.add_layernorm_fwd(d1, x, g2, b2, out_dtype=T)
             q = K.gemm(h2, cin_wT[:C], bias=cin_b[:C])                            # [B*N, C]
             kv = K.gemm(mem, cin_wT[C:], bias=cin_b[C:])                          # [B*Sm, 2C]
             o, lse = K.attn_fwd(q, kv[:, :C], kv[:, C:], mem_pad, B, HEADS, N, Sm, SCALE)
-            x2 = K.gemm(o, cout_wT, bias=cout_b, epilogue=ops.EPI_RESID, aux=x1, out_dtype=torch.float32)
-            h3, _ = K.layernorm_fwd(x2, g3, b3, out_dtype=T)
-            x3, ffn = _ffn_fwd(K, h3, fc_wT, fc_b, pj_wT, pj_b, x2)
+            d2 = K.gemm(o, cout_wT, bias=cout_b)
+            h3, x2 = K.add_layernorm_fwd(d2, x1, g3, b3, out_dtype=T)
+            d3, ffn = _ffn_fwd(K, h3, fc_wT, fc_b, pj_wT, pj_b)
             saved.append((x, xn, att, x1, h2, q, kv, o, lse, x2, h3, ffn,
                           (cin_wT, cout_wT, fc_wT, pj_wT, sin_wT, sout_wT)))
-            x = x3
+            x = x2
         ctx.saved, ctx.mem, ctx.pads, ctx.meta, ctx.params = saved, mem, (tgt_pad, mem_pad), (B, N, Sm, L, T), params
-        return K.cast(x, T) if T != torch.float32 else x
+        # raw output of the last block: x2 + ffn (tfm_model.py:86), in the compute dtype
+        d3f = d3 if d3.dtype == torch.float32 else K.cast(d3, torch.float32)
+        out, _ = K.add_rows(x, B * N, x2=d3f, out_dtype=T)
+        return out
 
     @staticmethod
     def backward(ctx, d_out):

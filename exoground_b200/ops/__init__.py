@@ -4,7 +4,7 @@ torch re-statement of the op specs (tests/fake_backend.py) to validate host logi
 a GPU; nothing inside this package ever installs a non-CUDA backend."""
 from . import lib
 from .lib import (F32, BF16, EPI_NONE, EPI_QGELU, EPI_RESID, EPI_QGELU_BWD, EPI_RELU, EPI_RELU_BWD,
-                  GEMM_AUTO, GEMM_SIMT, GEMM_TC, ExgError)
+                  GEMM_AUTO, GEMM_SIMT, GEMM_TC, GEMM_TC2, ExgError)
 
 _backend = None
 

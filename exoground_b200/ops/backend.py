@@ -118,6 +118,18 @@ class CudaBackend:
                                            _stream()), "exg_layernorm_fwd")
         return out, y2
 
+    def add_layernorm_fwd(self, x, resid, gamma, beta, *, out_dtype, out=None, out_map=None, eps=1e-5):
+        """s = resid + x (fp32 residual stream, new tensor); y[map(r)] = LN(s).  Returns (y, s)."""
+        _cuda(x, resid, gamma, beta, out)
+        rows, Cn = x.shape
+        if out is None:
+            out = torch.empty((rows, Cn), dtype=out_dtype, device=x.device)
+        s = torch.empty((rows, Cn), dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_add_layernorm_fwd(_p(x), _dt(x.dtype), _p(resid), _p(s), _p(gamma), _p(beta), _p(out),
+                                               _dt(out.dtype), _rm(out_map, rows), rows, Cn, float(eps), _stream()),
+                "exg_add_layernorm_fwd")
+        return out, s
+
     def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
                       want_dx=True):
         """Backward of y = LN(x)*gamma+beta with dy = dy1[map1] (+ dy2[map2]).

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(HERE, "libexg.so")
 
 F32, BF16 = 0, 1
 EPI_NONE, EPI_QGELU, EPI_RESID, EPI_QGELU_BWD, EPI_RELU, EPI_RELU_BWD = 0, 1, 2, 3, 4, 5
-GEMM_AUTO, GEMM_SIMT, GEMM_TC = 0, 1, 2
+GEMM_AUTO, GEMM_SIMT, GEMM_TC, GEMM_TC2 = 0, 1, 2, 3
 
 vp = C.c_void_p
 
@@ -43,6 +43,8 @@ _SIGS = {
     "exg_gemm_tc_supported": (C.c_int, [C.POINTER(GemmParams)]),
     "exg_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, RowMap, vp, C.c_int, vp, C.c_long,
                                     vp, vp, C.c_long, C.c_int, C.c_float, vp]),
+    "exg_add_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, RowMap, C.c_long, C.c_int,
+                                        C.c_float, vp]),
     "exg_layernorm_bwd": (C.c_int, [vp, C.c_int, RowMap, vp, C.c_int, RowMap, vp, C.c_int, vp, vp, vp, vp,
                                     vp, vp, C.c_int, vp, vp, C.c_long, C.c_int, vp]),
     "exg_add_rows": (C.c_int, [vp, RowMap, vp, RowMap, vp, C.c_long, vp, C.c_int, RowMap, vp, C.c_int,

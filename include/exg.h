@@ -69,7 +69,8 @@ typedef struct { long group; long group_stride; long offset; } exg_rowmap;
 
 #define EXG_GEMM_AUTO 0
 #define EXG_GEMM_SIMT 1
-#define EXG_GEMM_TC 2
+#define EXG_GEMM_TC 2      /* one tile per CTA, register epilogue (every epilogue, aux operands) */
+#define EXG_GEMM_TC2 3     /* persistent, TMEM double-buffered, TMA-store epilogue (NONE/QGELU/RELU) */
 
 typedef struct {
   const void* A; const void* B; void* C;
@@ -100,6 +101,12 @@ int exg_layernorm_fwd(const void* x, int x_dtype, const float* gamma, const floa
                       void* y, int y_dtype, exg_rowmap map_y, void* y2, int y2_dtype,
                       const float* add, long add_period,
                       float* mean, float* rstd, long rows, int C, float eps, void* stream);
+/* Residual-stream update fused with the following LayerNorm (model/tfm_model.py:36-37 `x = x + attn(...)`,
+ * `x = x + mlp(...)` followed by ln_2 / the next block's ln_1):
+ *   sum_out[r] = resid[r] + x[r]   (fp32; may alias resid)  ;  y[map_y(r)] = LN(sum_out[r]) * gamma + beta */
+int exg_add_layernorm_fwd(const void* x, int x_dtype, const float* resid, float* sum_out,
+                          const float* gamma, const float* beta, void* y, int y_dtype, exg_rowmap map_y,
+                          long rows, int C, float eps, void* stream);
 /* LayerNorm backward.  dy = dy1[map1(r)] (+ dy2[map2(r)] if dy2);
  *   dx[r] = (dres ? dres[r] : 0) + LN'(dy)        written fp32 to dx and (optional) dtype copy dxT
  *   dgamma[C] += sum_r dy*xhat ; dbeta[C] += sum_r dy    (fp32 atomics: caller zero-initialises) */

@@ -1,0 +1,53 @@
+"""GPU helper: TFLOP/s of the tcgen05 GEMM variants on the shapes of the TAN train step (CUDA events)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from exoground_b200 import ops
+from exoground_b200.ops import lib as L
+
+K = ops.get()
+SHAPES = [  # (M, N, K, tA, tB, epilogue, bias, out_f32, tag)
+    (8192, 1536, 512, 0, 0, L.EPI_NONE, 1, 0, "qkv"),
+    (8192, 512, 512, 0, 0, L.EPI_NONE, 1, 0, "out_proj"),
+    (12288, 2048, 512, 0, 0, L.EPI_QGELU, 1, 0, "c_fc+qgelu"),
+    (12288, 512, 2048, 0, 0, L.EPI_NONE, 1, 0, "c_proj"),
+    (12288, 2048, 512, 0, 1, L.EPI_NONE, 0, 0, "du (dx @ Wp)"),
+    (2048, 512, 12288, 1, 1, L.EPI_NONE, 0, 1, "dW_fc splitK"),
+    (512, 512, 8192, 1, 1, L.EPI_NONE, 0, 1, "dW_out splitK"),
+    (8192, 512, 4096, 0, 0, L.EPI_NONE, 0, 0, "video_pre_proj"),
+    (8192, 4096, 512, 0, 0, L.EPI_NONE, 0, 0, "sim (1 stage)"),
+    (8192, 8192, 8192, 0, 0, L.EPI_NONE, 0, 0, "square 8192"),
+]
+impls = [("tc", L.GEMM_TC), ("tc2", L.GEMM_TC2)]
+for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
+    A = torch.randn((Kd, M) if tA else (M, Kd), device="cuda").bfloat16()
+    B = torch.randn((Kd, N) if tB else (N, Kd), device="cuda").bfloat16()
+    bs = torch.randn(N, device="cuda") if bias else None
+    out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
+    line = f"{tag:16s} M{M} N{N} K{Kd}: "
+    for name, impl in impls:
+        try:
+            for _ in range(3):
+                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl,
+                       want_preact=False)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            reps = 20
+            for _ in range(reps):
+                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl)
+            e1.record(); torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / reps
+            line += f"{name} {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s | "
+        except Exception as ex:
+            line += f"{name} ERR {str(ex)[:60]} | "
+    a = A.float().t() if tA else A.float()
+    torch.matmul(a[:8].bfloat16(), a[:8].bfloat16().t())
+    Ab = (A.t() if tA else A).contiguous(); Bb = (B if tB else B.t()).contiguous()
+    for _ in range(3): torch.matmul(Ab, Bb)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20): torch.matmul(Ab, Bb)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 20
+    line += f"cublas {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s"
+    print(line, flush=True)

@@ -74,6 +74,11 @@ class TorchBackend:
         y2 = y.to(y2_dtype) if y2_dtype is not None else None
         return out, y2
 
+    def add_layernorm_fwd(self, x, resid, gamma, beta, *, out_dtype, out=None, out_map=None, eps=1e-5):
+        s = resid.float() + x.float()
+        y, _ = self.layernorm_fwd(s, gamma, beta, out_dtype=out_dtype, out=out, out_map=out_map, eps=eps)
+        return y, s
+
     def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
                       want_dx=True):
         rows, C = x.shape

@@ -309,3 +309,33 @@ def test_adamw_and_ema(K):
     K.ema(t, o, 0.999)
     REF.ema(tr, o, 0.999)
     _check(t, tr, torch.float32, "ema")
+
+
+# ------------------------------------------------------------------------------------------- persistent GEMM
+@pytest.mark.parametrize("tA,tB", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("shape", [(128, 128, 64), (256, 256, 512), (384, 512, 2048), (8192, 1536, 512),
+                                   (200, 72, 136), (136, 264, 72), (20000, 512, 512)])
+def test_gemm_tc2_layouts(K, tA, tB, shape):
+    _gemm_case(K, *shape, tA, tB, torch.bfloat16, L.GEMM_TC2)
+
+
+@pytest.mark.parametrize("epi", [L.EPI_NONE, L.EPI_QGELU, L.EPI_RELU])
+@pytest.mark.parametrize("shape", [(300, 520, 512), (12288, 2048, 512)])
+def test_gemm_tc2_epilogues(K, epi, shape):
+    _gemm_case(K, *shape, False, False, torch.bfloat16, L.GEMM_TC2, epilogue=epi, bias=True)
+
+
+def test_gemm_tc2_fp32_out_splitk_batch(K):
+    _gemm_case(K, 512, 512, 8192, True, True, torch.bfloat16, L.GEMM_TC2, out_dtype=torch.float32)
+    _gemm_case(K, 1536, 512, 12288, True, True, torch.bfloat16, L.GEMM_TC2, out_dtype=torch.float32)
+    _gemm_case(K, 300, 520, 512, False, False, torch.bfloat16, L.GEMM_TC2, out_dtype=torch.float32, bias=True)
+    _gemm_case(K, 256, 264, 512, False, False, torch.bfloat16, L.GEMM_TC2, batch=3)
+    _gemm_case(K, 256, 264, 512, False, False, torch.bfloat16, L.GEMM_TC2, batch=3, bcast_b=True)
+    _gemm_case(K, 192, 136, 520, False, True, torch.bfloat16, L.GEMM_TC2, batch=2)
+    _gemm_case(K, 264, 64, 520, True, True, torch.bfloat16, L.GEMM_TC2, batch=2, out_dtype=torch.float32)
+    _gemm_case(K, 512, 512, 8192, True, True, torch.bfloat16, L.GEMM_TC2, batch=2, out_dtype=torch.float32)
+
+
+def test_gemm_tc2_refuses_aux_epilogues(K):
+    with pytest.raises(L.ExgError):
+        _gemm_case(K, 256, 512, 512, False, False, torch.bfloat16, L.GEMM_TC2, epilogue=L.EPI_RESID)
