@@ -34,6 +34,7 @@ struct Tc2Args {
   int tiles_m, tiles_n, splits, kblocks_per_split, batch;
   int a_bcast, b_bcast;
   int has_aux_out;
+  int has_aux_in;    // QGELU_BWD / RELU_BWD: bf16 aux tile streamed in by TMA, chunk by chunk, by the epilogue warps
 };
 
 template <int BN> struct Cfg2 {
@@ -81,7 +82,8 @@ __device__ __forceinline__ TileCoord tile_coord(const Tc2Args& p, int tile, int 
 template <int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux, Tc2Args p) {
+                const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
+                const __grid_constant__ CUtensorMap tmAuxIn, Tc2Args p) {
   using C_ = Cfg2<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -90,7 +92,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* empty = full + C_::kStages;
   uint64_t* tmem_full = empty + C_::kStages;     // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* aux_bar = tmem_empty + 2;            // [kEpiWarps][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 2 * kEpiWarps);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits * p.batch;
@@ -98,11 +101,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (threadIdx.x == 0) {
     for (int s = 0; s < C_::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], kEpiWarps); }
+    for (int s = 0; s < 2 * kEpiWarps; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); tma_prefetch_desc(&tmC);
     if (p.has_aux_out) tma_prefetch_desc(&tmAux);
+    if (p.has_aux_in) tma_prefetch_desc(&tmAuxIn);
   }
   if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
   tc_fence_before();
@@ -180,6 +185,15 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint32_t sbuf = 0;                            // next staging buffer (ring)
     uint32_t ti = 0;
     const int cols_per_chunk = p.out_f32 ? 32 : 64;
+    // aux-in mode: staging buffers 0,1 hold outputs, 2,3 receive the aux chunks (double-buffered prefetch)
+    const uint32_t n_out_bufs = p.has_aux_in ? 2 : kStageBufs;
+    uint64_t* my_aux_bar = aux_bar + 2 * ew;
+    uint32_t ci = 0;                              // running chunk index of this warp (aux ring position)
+    if (p.has_aux_in && lane == 0 && (int)blockIdx.x < total_tiles) {
+      const TileCoord t0 = tile_coord(p, blockIdx.x, BN);
+      mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
+      tma_load_3d(stage + 2 * kStageBufBytes, &tmAuxIn, &my_aux_bar[0], t0.n0, t0.m0 + lg * 32, t0.z);
+    }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
       const TileCoord t = tile_coord(p, tile, BN);
       const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
@@ -193,6 +207,31 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int c0 = 0; c0 < BN; c0 += cols_per_chunk) {
         const bool live = rows_live && c0 < n_live;      // warp-uniform
         uint32_t r[64];
+        uint4 ax[8];
+        if (p.has_aux_in) {
+          // prefetch the aux chunk after this one (same tile, or first chunk of this CTA's next tile) ...
+          if (lane == 0) {
+            int nt = tile, nc = c0 + cols_per_chunk;
+            if (nc >= BN) { nt = tile + gridDim.x; nc = 0; }
+            if (nt < total_tiles) {
+              const TileCoord tn = tile_coord(p, nt, BN);
+              const uint32_t nb = (ci + 1) & 1;
+              mbar_arrive_expect_tx(&my_aux_bar[nb], kStageBufBytes);
+              tma_load_3d(stage + (2 + nb) * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
+                          tn.m0 + lg * 32, tn.z);
+            }
+          }
+          // ... and take this chunk's aux rows (thread = row, 128B-swizzled) into registers
+          const uint32_t cb = ci & 1;
+          mbar_wait(&my_aux_bar[cb], (ci >> 1) & 1);
+          const uint8_t* abuf = stage + (2 + cb) * kStageBufBytes;
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            ax[u] = *reinterpret_cast<const uint4*>(abuf + lane * 128 + ((u ^ (lane & 7)) << 4));
+          fence_proxy_async();       // order these generic-proxy reads before the next TMA write into this buffer
+          __syncwarp();
+          ++ci;
+        }
         if (live) {
           tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
           if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
@@ -222,7 +261,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         // ---- optional second output: the pre-activation (bf16), staged and stored first
         if (p.has_aux_out) {
-          uint8_t* buf = stage + (size_t)(sbuf % kStageBufs) * kStageBufBytes;
+          uint8_t* buf = stage + (size_t)(sbuf % n_out_bufs) * kStageBufBytes;
           if (lane == 0) bulk_wait_read<kStageBufs - 1>();
           __syncwarp();
 #pragma unroll
@@ -245,10 +284,24 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         } else if (p.epilogue == EXG_EPI_RELU) {
 #pragma unroll
           for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
+        } else if (p.epilogue == EXG_EPI_QGELU_BWD || p.epilogue == EXG_EPI_RELU_BWD) {
+          const bool gelu = p.epilogue == EXG_EPI_QGELU_BWD;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t w[4] = {ax[u].x, ax[u].y, ax[u].z, ax[u].w};
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              const float a0 = __uint_as_float(w[h] << 16), a1 = __uint_as_float(w[h] & 0xffff0000u);
+              const int j = u * 8 + h * 2;
+              const float v0 = __uint_as_float(r[j]), v1 = __uint_as_float(r[j + 1]);
+              r[j] = __float_as_uint(gelu ? v0 * quick_gelu_grad(a0) : (a0 > 0.f ? v0 : 0.f));
+              r[j + 1] = __float_as_uint(gelu ? v1 * quick_gelu_grad(a1) : (a1 > 0.f ? v1 : 0.f));
+            }
+          }
         }
         // ---- stage (128B-swizzled rows) and TMA-store the chunk
-        uint8_t* buf = stage + (size_t)(sbuf % kStageBufs) * kStageBufBytes;
-        if (lane == 0) bulk_wait_read<kStageBufs - 1>();
+        uint8_t* buf = stage + (size_t)(sbuf % n_out_bufs) * kStageBufBytes;
+        if (lane == 0) { if (p.has_aux_in) bulk_wait_read<1>(); else bulk_wait_read<kStageBufs - 1>(); }
         __syncwarp();
         if (p.out_f32) {
 #pragma unroll
@@ -329,7 +382,7 @@ int make_map(CUtensorMap* out, const void* base, int f32, uint64_t inner, uint64
 
 template <int BN>
 int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
-            const Tc2Args& a, cudaStream_t s) {
+            const CUtensorMap& ti, const Tc2Args& a, cudaStream_t s) {
   static bool attr_set = false;
   auto kfn = gemm_tc2_kernel<BN>;
   if (!attr_set) {
@@ -339,7 +392,7 @@ int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
   }
   const long total = (long)a.tiles_m * a.tiles_n * a.splits * a.batch;
   const int grid = (int)(total < exg_num_sms() ? total : exg_num_sms());
-  kfn<<<grid, kThreads, Cfg2<BN>::kSmem, s>>>(ta, tb, tc, tx, a);
+  kfn<<<grid, kThreads, Cfg2<BN>::kSmem, s>>>(ta, tb, tc, tx, ti, a);
   EXG_LAUNCH_CHECK("gemm_tc2");
   return 0;
 }
@@ -358,8 +411,12 @@ double wave_eff(long tiles) {
 int exg_gemm_tc2_supported(const exg_gemm_params* p) {
   if (!p || p->in_dtype != EXG_BF16) return 0;
   if (p->M <= 0 || p->N <= 0 || p->K <= 0 || p->batch <= 0) return 0;
-  if (p->epilogue != EXG_EPI_NONE && p->epilogue != EXG_EPI_QGELU && p->epilogue != EXG_EPI_RELU) return 0;
-  if (p->aux) return 0;
+  const bool aux_in = p->epilogue == EXG_EPI_QGELU_BWD || p->epilogue == EXG_EPI_RELU_BWD;
+  if (p->epilogue != EXG_EPI_NONE && p->epilogue != EXG_EPI_QGELU && p->epilogue != EXG_EPI_RELU && !aux_in) return 0;
+  if (aux_in) {   // bf16 aux tile arrives by TMA: bf16 output, 16-byte aligned aux rows
+    if (!p->aux || p->out_dtype != EXG_BF16 || !al16(p->aux) || p->ldaux % 8 ||
+        (p->batch > 1 && p->strideAux % 8)) return 0;
+  } else if (p->aux) return 0;
   if (p->aux_out && (p->epilogue != EXG_EPI_QGELU || p->out_dtype != EXG_BF16)) return 0;
   const int es_out = p->out_dtype == EXG_F32 ? 4 : 2;
   if (p->N < 128 / es_out) return 0;                       // the store box is 128 bytes wide
@@ -380,6 +437,7 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.out_f32 = q->out_dtype == EXG_F32; a.epilogue = q->epilogue;
   a.bias = q->bias; a.alpha = q->alpha; a.batch = q->batch;
   a.has_aux_out = q->aux_out ? 1 : 0;
+  a.has_aux_in = (q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD) ? 1 : 0;
 
   const int kblocks = (q->K + BK - 1) / BK;
   const long tm = (q->M + BM - 1) / BM;
@@ -408,7 +466,7 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
                                  (size_t)q->N * 4, (size_t)q->M, s));
   }
 
-  CUtensorMap ta, tb, tc, tx;
+  CUtensorMap ta, tb, tc, tx, ti;
   int rc;
   a.a_bcast = (q->batch > 1 && q->strideA == 0) ? 1 : 0;
   a.b_bcast = (q->batch > 1 && q->strideB == 0) ? 1 : 0;
@@ -426,5 +484,10 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
     rc = make_map(&tx, q->aux_out, 0, q->N, q->M, q->batch, q->ldc, q->strideC, 64, 32);
     if (rc) return rc;
   }
-  return bn == 256 ? launch2<256>(ta, tb, tc, tx, a, s) : launch2<128>(ta, tb, tc, tx, a, s);
+  ti = tc;
+  if (a.has_aux_in) {
+    rc = make_map(&ti, q->aux, 0, q->N, q->M, q->batch, q->ldaux, q->strideAux, 64, 32);
+    if (rc) return rc;
+  }
+  return bn == 256 ? launch2<256>(ta, tb, tc, tx, ti, a, s) : launch2<128>(ta, tb, tc, tx, ti, a, s);
 }

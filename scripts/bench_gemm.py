@@ -12,6 +12,7 @@ SHAPES = [  # (M, N, K, tA, tB, epilogue, bias, out_f32, tag)
     (12288, 2048, 512, 0, 0, L.EPI_QGELU, 1, 0, "c_fc+qgelu"),
     (12288, 512, 2048, 0, 0, L.EPI_NONE, 1, 0, "c_proj"),
     (12288, 2048, 512, 0, 1, L.EPI_NONE, 0, 0, "du (dx @ Wp)"),
+    (12288, 2048, 512, 0, 1, L.EPI_QGELU_BWD, 0, 0, "du + qgelu_bwd"),
     (2048, 512, 12288, 1, 1, L.EPI_NONE, 0, 1, "dW_fc splitK"),
     (512, 512, 8192, 1, 1, L.EPI_NONE, 0, 1, "dW_out splitK"),
     (8192, 512, 4096, 0, 0, L.EPI_NONE, 0, 0, "video_pre_proj"),
@@ -24,17 +25,18 @@ for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
     B = torch.randn((Kd, N) if tB else (N, Kd), device="cuda").bfloat16()
     bs = torch.randn(N, device="cuda") if bias else None
     out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
+    aux = torch.randn(M, N, device="cuda").bfloat16() if epi == L.EPI_QGELU_BWD else None
     line = f"{tag:16s} M{M} N{N} K{Kd}: "
     for name, impl in impls:
         try:
             for _ in range(3):
                 K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl,
-                       want_preact=False)
+                       aux=aux)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             reps = 20
             for _ in range(reps):
-                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl)
+                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl, aux=aux)
             e1.record(); torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
             line += f"{name} {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s | "

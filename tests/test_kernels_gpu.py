@@ -319,8 +319,8 @@ def test_gemm_tc2_layouts(K, tA, tB, shape):
     _gemm_case(K, *shape, tA, tB, torch.bfloat16, L.GEMM_TC2)
 
 
-@pytest.mark.parametrize("epi", [L.EPI_NONE, L.EPI_QGELU, L.EPI_RELU])
-@pytest.mark.parametrize("shape", [(300, 520, 512), (12288, 2048, 512)])
+@pytest.mark.parametrize("epi", [L.EPI_NONE, L.EPI_QGELU, L.EPI_RELU, L.EPI_QGELU_BWD, L.EPI_RELU_BWD])
+@pytest.mark.parametrize("shape", [(300, 520, 512), (12288, 2048, 512), (8192, 2048, 512)])
 def test_gemm_tc2_epilogues(K, epi, shape):
     _gemm_case(K, *shape, False, False, torch.bfloat16, L.GEMM_TC2, epilogue=epi, bias=True)
 
