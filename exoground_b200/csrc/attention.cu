@@ -298,12 +298,25 @@ int check_common(int dtype, long ldq, long ldk, long ldv, long ldo, int B, int H
 
 }  // namespace
 
+int exg_attn_tc_ok(int dtype, long ldq, long ldk, long ldv, long ldo, int Sq, int Sk, int d, bool bwd,
+                   const void* q, const void* k, const void* v, const void* o);
+int exg_attn_tc_fwd(const void* q, const void* k, const void* v, long ldq, long ldk, long ldv,
+                    const uint8_t* key_pad, void* o, long ldo, float* lse, int B, int H, int Sq, int Sk,
+                    float scale, void* stream);
+int exg_attn_tc_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout, long ldq,
+                    long ldk, long ldv, long ldo, const uint8_t* key_pad, const float* lse, void* dq, void* dk,
+                    void* dv, int B, int H, int Sq, int Sk, float scale, void* stream);
+
 extern "C" int exg_attn_fwd(const void* q, const void* k, const void* v, int dtype, long ldq, long ldk,
                             long ldv, const uint8_t* key_pad, void* o, long ldo, float* lse, int B, int H,
                             int Sq, int Sk, int d, float scale, void* stream) {
   EXG_CHECK_ARG(q && k && v && o, "attn_fwd: null pointer");
   int rc = check_common(dtype, ldq, ldk, ldv, ldo, B, H, Sq, Sk, d);
   if (rc) return rc;
+  if (lse && exg_attn_tc_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, false, q, k, v, o)) {
+    ExgProfScope prof(EXG_PC_ATTN_FWD, 4.0 * B * H * Sq * Sk * d, stream);
+    return exg_attn_tc_fwd(q, k, v, ldq, ldk, ldv, key_pad, o, ldo, lse, B, H, Sq, Sk, scale, stream);
+  }
   AttnArgs a = {};
   a.q = q; a.k = k; a.v = v; a.out = o; a.dtype = dtype; a.ldq = ldq; a.ldk = ldk; a.ldv = ldv; a.ldo = ldo;
   a.key_pad = key_pad; a.lse = lse; a.B = B; a.H = H; a.Sq = Sq; a.Sk = Sk; a.scale = scale;
@@ -324,6 +337,12 @@ extern "C" int exg_attn_bwd(const void* q, const void* k, const void* v, const v
   EXG_CHECK_ARG(q && k && v && o && dout && lse && delta && dq && dk && dv, "attn_bwd: null pointer");
   int rc = check_common(dtype, ldq, ldk, ldv, ldo, B, H, Sq, Sk, d);
   if (rc) return rc;
+  if (exg_attn_tc_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, true, q, k, v, o) &&
+      exg_attn_tc_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, true, dq, dk, dv, dout)) {
+    ExgProfScope prof(EXG_PC_ATTN_BWD, 10.0 * B * H * Sq * Sk * d, stream);
+    return exg_attn_tc_bwd(q, k, v, o, dout, ldq, ldk, ldv, ldo, key_pad, lse, dq, dk, dv, B, H, Sq, Sk, scale,
+                           stream);
+  }
   AttnArgs a = {};
   a.q = q; a.k = k; a.v = v; a.o = o; a.dout = dout; a.dq = dq; a.dk = dk; a.dv = dv; a.dtype = dtype;
   a.ldq = ldq; a.ldk = ldk; a.ldv = ldv; a.ldo = ldo; a.key_pad = key_pad;

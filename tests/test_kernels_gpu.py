@@ -225,7 +225,8 @@ def test_cast_and_stage_mean(K):
 # ------------------------------------------------------------------------------------------- attention
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,Sq,Sk,masked", [(2, 64, 64, True), (3, 96, 96, True), (2, 100, 100, True),
-                                            (2, 8, 200, True), (1, 300, 300, False)])
+                                            (2, 8, 200, True), (1, 300, 300, False), (4, 64, 64, False),
+                                            (2, 24, 120, True), (3, 128, 128, True), (2, 200, 72, True)])
 def test_attention(K, dt, B, Sq, Sk, masked):
     H, d = 8, 64
     self_attn = Sq == Sk
