@@ -122,11 +122,28 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
-// x * sigmoid(1.702 x).  __fdividef (2 ulp) keeps the GEMM epilogues free of the IEEE-division slow path.
+// x * sigmoid(1.702 x) (model/tfm_model.py:11-13).  __fdividef (2 ulp) keeps the fp32 paths free of the
+// IEEE-division slow path.
 __device__ __forceinline__ float quick_gelu(float v) { return __fdividef(v, 1.0f + __expf(-1.702f * v)); }
 __device__ __forceinline__ float quick_gelu_grad(float u) {
   float s = __fdividef(1.0f, 1.0f + __expf(-1.702f * u));
   return s + 1.702f * u * s * (1.0f - s);
+}
+// bf16-output variants for the tensor-core GEMM epilogues: sigmoid(x) = 0.5 tanh(x/2) + 0.5 with the single-MUFU
+// tanh.approx.f32 (rel. error ~2^-11, below bf16 resolution).  ex2 + rcp would be two quarter-rate MUFU ops per
+// element and make the c_fc / c_proj-backward epilogues MUFU-bound (128x256 tile: 4096 MUFU cycles = the MMA time).
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float quick_gelu_fast(float v) {
+  const float h = 0.5f * v;
+  return fmaf(h, tanh_fast(0.851f * v), h);
+}
+__device__ __forceinline__ float quick_gelu_grad_fast(float u) {
+  const float s = fmaf(0.5f, tanh_fast(0.851f * u), 0.5f);
+  return fmaf(1.702f * u * s, 1.0f - s, s);
 }
 
 static inline int exg_num_sms() {

@@ -263,7 +263,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         if (p.epilogue == EXG_EPI_QGELU) {
 #pragma unroll
-          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(quick_gelu(__uint_as_float(r[j])));
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(quick_gelu_fast(__uint_as_float(r[j])));
         } else if (p.epilogue == EXG_EPI_RELU) {
 #pragma unroll
           for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
@@ -277,8 +277,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               const float a0 = __uint_as_float(w[h] << 16), a1 = __uint_as_float(w[h] & 0xffff0000u);
               const int j = u * 8 + h * 2;
               const float v0 = __uint_as_float(r[j]), v1 = __uint_as_float(r[j + 1]);
-              r[j] = __float_as_uint(gelu ? v0 * quick_gelu_grad(a0) : (a0 > 0.f ? v0 : 0.f));
-              r[j + 1] = __float_as_uint(gelu ? v1 * quick_gelu_grad(a1) : (a1 > 0.f ? v1 : 0.f));
+              r[j] = __float_as_uint(gelu ? v0 * quick_gelu_grad_fast(a0) : (a0 > 0.f ? v0 : 0.f));
+              r[j + 1] = __float_as_uint(gelu ? v1 * quick_gelu_grad_fast(a1) : (a1 > 0.f ? v1 : 0.f));
             }
           }
         }

@@ -1,5 +1,6 @@
 // nce.cu — masked bidirectional MIL-NCE over materialised stage-major logits L[S, R=B*T, Cc=B*N]
-// (train/loss.py:234-278): one streaming pass for the four exp-sums, one streaming pass for dL.
+// (train/loss.py:234-278): one streaming pass for the four exp-sums, one streaming pass for dL; 16-byte
+// loads / stores, column partial sums in registers (one atomic per column per 256-row CTA).
 // HBM-bound: forward reads L once; backward reads L once and writes G once.
 // Because L is a cosine, |L*inv_temp| <= inv_temp, so exp(L*inv_temp - inv_temp) in (0, 1] needs no
 // running max; the shift cancels in every log-ratio and in every softmax quotient.
@@ -7,8 +8,14 @@
 
 namespace {
 
-constexpr int SLAB = 32;       // rows per CTA
-constexpr int NT = 256;
+constexpr int NT = 256;        // threads per CTA; a thread owns 8 consecutive columns
+constexpr int CPT = 8;
+constexpr int CB = NT * CPT;   // 2048 columns per CTA
+constexpr int SUB = 16;        // rows per register sub-slab
+constexpr int FWD_ROWS = 128;  // rows per CTA, forward (column partial sums stay in registers across them)
+constexpr int BWD_ROWS = 64;  // (multiple of LDB)
+constexpr int LDB = 8;        // rows whose loads are issued back to back before any is consumed (memory-level parallelism)
+  // rows per CTA, backward
 
 struct NceArgs {
   const void* L; int dtype;
@@ -19,77 +26,153 @@ struct NceArgs {
   int S, B, T, N; float inv_temp;
 };
 
-__device__ __forceinline__ float comp(const float4& v, int j) {
-  return j == 0 ? v.x : (j == 1 ? v.y : (j == 2 ? v.z : v.w));
-}
-
-__global__ void __launch_bounds__(NT) nce_fwd_kernel(NceArgs p) {
-  __shared__ float red[NT / 32][2 * SLAB];
-  const int s = blockIdx.y;
-  const long R = (long)p.B * p.T, Cc = (long)p.B * p.N;
-  const long r0 = (long)blockIdx.x * SLAB;
-  const int nrows = (int)min((long)SLAB, R - r0);
-  const size_t base = (size_t)s * R * Cc;
-  float ra[SLAB], rp[SLAB];
-#pragma unroll
-  for (int i = 0; i < SLAB; ++i) ra[i] = rp[i] = 0.f;
-
-  for (long c4 = (long)threadIdx.x * 4; c4 < Cc; c4 += NT * 4) {
-    int cb[4]; bool cv[4];
+// 8 consecutive logits of one row as fp32 (16-byte load for bf16, 2 x 16-byte for fp32)
+__device__ __forceinline__ void load8(const void* p, int dtype, size_t i, float (&v)[8]) {
+  if (dtype == EXG_F32) {
+    const float4 a = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + i);
+    const float4 b = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p) + i + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+    const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p) + i);
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      cb[j] = (int)((c4 + j) / p.N);
-      cv[j] = p.col_valid[c4 + j] != 0;
+      v[2 * j] = __uint_as_float(w[j] << 16);
+      v[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
     }
-    float ca[4] = {0.f, 0.f, 0.f, 0.f}, cp[4] = {0.f, 0.f, 0.f, 0.f};
+  }
+}
+// raw 16-byte row segment (bf16 x 8) and its conversion; the fp32 path keeps load8
+__device__ __forceinline__ void cvt8(const uint4& u, float (&v)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-    for (int i = 0; i < SLAB; ++i) {      // fully unrolled: ra/rp must stay in registers
-      if (i >= nrows) continue;
-      const long r = r0 + i;
-      const int a = (int)(r / p.T), t = (int)(r % p.T);
-      const float4 v = load4(p.L, p.dtype, base + (size_t)r * Cc + c4);
+  for (int j = 0; j < 4; ++j) {
+    v[2 * j] = __uint_as_float(w[j] << 16);
+    v[2 * j + 1] = __uint_as_float(w[j] & 0xffff0000u);
+  }
+}
+// Cc % 8 != 0: rows are not 16-byte aligned -> element-wise access of the in-range columns
+__device__ __forceinline__ void load8_any(const void* p, int dtype, size_t i, float (&v)[8], bool vec, int nvalid) {
+  if (vec) { load8(p, dtype, i, v); return; }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (!cv[j]) continue;
-        const float e = __expf(comp(v, j) * p.inv_temp - p.inv_temp);
-        ra[i] += e; ca[j] += e;
-        if (cb[j] == a && p.tgt[((size_t)(c4 + j)) * p.T + t]) { rp[i] += e; cp[j] += e; }
+  for (int j = 0; j < 8; ++j) v[j] = j < nvalid ? load1(p, dtype, (long)(i + j)) : 0.f;
+}
+__device__ __forceinline__ void store8(void* p, int dtype, size_t i, const float (&v)[8]);
+__device__ __forceinline__ void store8_any(void* p, int dtype, size_t i, const float (&v)[8], bool vec, int nvalid) {
+  if (vec) { store8(p, dtype, i, v); return; }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) if (j < nvalid) store1(p, dtype, (long)(i + j), v[j]);
+}
+__device__ __forceinline__ void store8(void* p, int dtype, size_t i, const float (&v)[8]) {
+  if (dtype == EXG_F32) {
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p) + i) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(reinterpret_cast<float*>(p) + i + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  } else {
+    uint4 u;
+    u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+    u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+    *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p) + i) = u;
+  }
+}
+
+// Forward: CTA = FWD_ROWS rows x CB columns of one stage.  Column sums live in registers for the whole CTA (one
+// atomic per column per CTA); row sums are reduced over the CTA per 32-row sub-slab (one atomic per row).
+__global__ void __launch_bounds__(NT, 2) nce_fwd_kernel(NceArgs p) {
+  __shared__ float red[NT / 32][2 * SUB];
+  const int s = blockIdx.z;
+  const long R = (long)p.B * p.T, Cc = (long)p.B * p.N;
+  const long rbeg = (long)blockIdx.x * FWD_ROWS;
+  const long rend = min(R, rbeg + FWD_ROWS);
+  const long c0 = (long)blockIdx.y * CB + (long)threadIdx.x * CPT;
+  const size_t base = (size_t)s * R * Cc;
+  const float k1 = p.inv_temp * 1.4426950408889634f;
+  const bool act = c0 < Cc;
+  const bool vec = (Cc % CPT) == 0;
+  const int nvalid = act ? (int)min((long)CPT, Cc - c0) : 0;
+  int cb[CPT]; bool cv[CPT];
+  float ca[CPT], cp[CPT];
+#pragma unroll
+  for (int j = 0; j < CPT; ++j) {
+    cb[j] = j < nvalid ? (int)((c0 + j) / p.N) : -1;
+    cv[j] = j < nvalid && p.col_valid[c0 + j] != 0;
+    ca[j] = cp[j] = 0.f;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (long r0 = rbeg; r0 < rend; r0 += SUB) {
+    float ra[SUB], rp[SUB];
+#pragma unroll
+    for (int i = 0; i < SUB; ++i) ra[i] = rp[i] = 0.f;
+    if (act) {
+      const bool fast = vec && p.dtype == EXG_BF16;
+#pragma unroll
+      for (int i0 = 0; i0 < SUB; i0 += LDB) {
+        uint4 raw[LDB];
+        if (fast) {       // issue LDB independent 16-byte loads before consuming any of them
+#pragma unroll
+          for (int u = 0; u < LDB; ++u) {
+            const long r = min(r0 + i0 + u, rend - 1);
+            raw[u] = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.L) + base +
+                                                           (size_t)r * Cc + c0));
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < LDB; ++u) {
+          const int i = i0 + u;
+          const long r = r0 + i;
+          if (r >= rend) continue;
+          float v[8];
+          if (fast) cvt8(raw[u], v);
+          else load8_any(p.L, p.dtype, base + (size_t)r * Cc + c0, v, vec, nvalid);
+          const int a = (int)(r / p.T), t = (int)(r % p.T);
+          const bool own = cb[0] == a || cb[CPT - 1] == a;     // can any of this thread's columns be positive here?
+#pragma unroll
+          for (int j = 0; j < CPT; ++j) {
+            if (!cv[j]) continue;
+            const float e = exp2f(fmaf(v[j], k1, -k1));
+            ra[i] += e; ca[j] += e;
+            if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) { rp[i] += e; cp[j] += e; }
+          }
+        }
       }
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (!cv[j]) continue;
-      atomicAdd(p.col_all + (size_t)s * Cc + c4 + j, ca[j]);
-      if (cp[j] != 0.f) atomicAdd(p.col_pos + (size_t)s * Cc + c4 + j, cp[j]);
+    for (int i = 0; i < SUB; ++i) {
+      const float x = warp_sum(ra[i]), y = warp_sum(rp[i]);
+      if (lane == 0) { red[warp][i] = x; red[warp][SUB + i] = y; }
     }
-  }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (threadIdx.x < 2 * SUB) {
+      float tsum = 0.f;
 #pragma unroll
-  for (int i = 0; i < SLAB; ++i) {
-    const float x = warp_sum(ra[i]), y = warp_sum(rp[i]);
-    if (lane == 0) { red[warp][i] = x; red[warp][SLAB + i] = y; }
+      for (int w = 0; w < NT / 32; ++w) tsum += red[w][threadIdx.x];
+      const int i = threadIdx.x % SUB;
+      if (r0 + i < rend && tsum != 0.f) {
+        float* dst = threadIdx.x < SUB ? p.row_all : p.row_pos;
+        atomicAdd(dst + (size_t)s * R + r0 + i, tsum);
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
-  if (threadIdx.x < 2 * SLAB) {
-    float t = 0.f;
+  if (act) {
 #pragma unroll
-    for (int w = 0; w < NT / 32; ++w) t += red[w][threadIdx.x];
-    const int i = threadIdx.x % SLAB;
-    if (i < nrows) {
-      float* dst = threadIdx.x < SLAB ? p.row_all : p.row_pos;
-      dst[(size_t)s * R + r0 + i] = t;
+    for (int j = 0; j < CPT; ++j) {
+      if (!cv[j]) continue;
+      atomicAdd(p.col_all + (size_t)s * Cc + c0 + j, ca[j]);
+      if (cp[j] != 0.f) atomicAdd(p.col_pos + (size_t)s * Cc + c0 + j, cp[j]);
     }
   }
 }
 
+// Backward: G = inv_temp * e * (wr/row_all + wc/col_all - pos * (wr/row_pos + wc/col_pos)); one streaming pass.
 __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
-  __shared__ float ra_s[SLAB], rp_s[SLAB];
-  const int s = blockIdx.y;
+  __shared__ float ra_s[BWD_ROWS], rp_s[BWD_ROWS];
+  const int s = blockIdx.z;
   const long R = (long)p.B * p.T, Cc = (long)p.B * p.N;
-  const long r0 = (long)blockIdx.x * SLAB;
-  const int nrows = (int)min((long)SLAB, R - r0);
+  const long r0 = (long)blockIdx.x * BWD_ROWS;
+  const int nrows = (int)min((long)BWD_ROWS, R - r0);
   const size_t base = (size_t)s * R * Cc;
-  if (threadIdx.x < SLAB) {
+  const float k1 = p.inv_temp * 1.4426950408889634f;
+  if (threadIdx.x < BWD_ROWS) {
     float a = 0.f, b = 0.f;
     if (threadIdx.x < nrows) {
       const long r = r0 + threadIdx.x;
@@ -100,40 +183,56 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
         b = rp > 0.f ? w / rp : 0.f;
       }
     }
-    ra_s[threadIdx.x] = a; rp_s[threadIdx.x] = b;
+    ra_s[threadIdx.x] = a * p.inv_temp; rp_s[threadIdx.x] = b * p.inv_temp;
   }
   __syncthreads();
-  for (long c4 = (long)threadIdx.x * 4; c4 < Cc; c4 += NT * 4) {
-    int cb[4]; bool cv[4]; float ka[4], kp[4];
+  const long c0 = (long)blockIdx.y * CB + (long)threadIdx.x * CPT;
+  if (c0 >= Cc) return;
+  const bool vec = (Cc % CPT) == 0;
+  const int nvalid = (int)min((long)CPT, Cc - c0);
+  int cb[CPT]; bool cv[CPT]; float ka[CPT], kp[CPT];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      cb[j] = (int)((c4 + j) / p.N);
-      cv[j] = p.col_valid[c4 + j] != 0;
-      const float w = p.wc[c4 + j];
-      ka[j] = kp[j] = 0.f;
-      if (cv[j] && w != 0.f) {
-        ka[j] = w / p.col_all[(size_t)s * Cc + c4 + j];
-        const float cp = p.col_pos[(size_t)s * Cc + c4 + j];
-        kp[j] = cp > 0.f ? w / cp : 0.f;
+  for (int j = 0; j < CPT; ++j) {
+    cb[j] = j < nvalid ? (int)((c0 + j) / p.N) : -1;
+    cv[j] = j < nvalid && p.col_valid[c0 + j] != 0;
+    const float w = j < nvalid ? p.wc[c0 + j] : 0.f;
+    ka[j] = kp[j] = 0.f;
+    if (cv[j] && w != 0.f) {
+      ka[j] = p.inv_temp * w / p.col_all[(size_t)s * Cc + c0 + j];
+      const float cpv = p.col_pos[(size_t)s * Cc + c0 + j];
+      kp[j] = cpv > 0.f ? p.inv_temp * w / cpv : 0.f;
+    }
+  }
+  const bool fast = vec && p.dtype == EXG_BF16;
+  for (int i0 = 0; i0 < nrows; i0 += LDB) {
+    uint4 raw[LDB];
+    if (fast) {
+#pragma unroll
+      for (int u = 0; u < LDB; ++u) {
+        const long r = r0 + min(i0 + u, nrows - 1);
+        raw[u] = __ldcs(reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.L) + base +
+                                                       (size_t)r * Cc + c0));
       }
     }
-#pragma unroll 4
-    for (int i = 0; i < SLAB; ++i) {
+#pragma unroll
+    for (int u = 0; u < LDB; ++u) {
+      const int i = i0 + u;
       if (i >= nrows) break;
       const long r = r0 + i;
       const int a = (int)(r / p.T), t = (int)(r % p.T);
-      const float4 v = load4(p.L, p.dtype, base + (size_t)r * Cc + c4);
-      float g[4];
+      float v[8], g[8];
+      if (fast) cvt8(raw[u], v);
+      else load8_any(p.L, p.dtype, base + (size_t)r * Cc + c0, v, vec, nvalid);
+      const float ra = ra_s[i], rp = rp_s[i];
+      const bool own = cb[0] == a || cb[CPT - 1] == a;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        g[j] = 0.f;
-        if (!cv[j]) continue;
-        const float e = __expf(comp(v, j) * p.inv_temp - p.inv_temp);
-        float coef = ra_s[i] + ka[j];
-        if (cb[j] == a && p.tgt[((size_t)(c4 + j)) * p.T + t]) coef -= rp_s[i] + kp[j];
-        g[j] = p.inv_temp * e * coef;
+      for (int j = 0; j < CPT; ++j) {
+        const float e = exp2f(fmaf(v[j], k1, -k1));
+        float coef = ra + ka[j];
+        if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) coef -= rp + kp[j];
+        g[j] = cv[j] ? e * coef : 0.f;
       }
-      store4(p.G, p.g_dtype, base + (size_t)r * Cc + c4, make_float4(g[0], g[1], g[2], g[3]));
+      store8_any(p.G, p.g_dtype, base + (size_t)r * Cc + c0, g, vec, nvalid);
     }
   }
 }
@@ -155,7 +254,6 @@ int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* 
   EXG_CHECK_ARG(logits && tgt && col_valid, "nce: null pointer");
   EXG_CHECK_ARG(exg_valid_dtype(dtype), "nce: bad dtype");
   EXG_CHECK_ARG(S > 0 && B > 0 && T > 0 && N > 0 && S <= 65535, "nce: bad sizes");
-  EXG_CHECK_ARG(((long)B * N) % 4 == 0, "nce: B*N must be a multiple of 4");
   return 0;
 }
 
@@ -170,10 +268,16 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
   NceArgs a = {};
   a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid; a.row_all = row_all; a.row_pos = row_pos;
   a.col_all = col_all; a.col_pos = col_pos; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
-  const long R = (long)B * T;
-  dim3 grid((unsigned)((R + SLAB - 1) / SLAB), (unsigned)S);
+  const long R = (long)B * T, Cc = (long)B * N;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the kernel accumulates with atomics: zero the four outputs here (captured as memset nodes under a graph)
+  EXG_CUDA(cudaMemsetAsync(row_all, 0, (size_t)S * R * 4, st));
+  EXG_CUDA(cudaMemsetAsync(row_pos, 0, (size_t)S * R * 4, st));
+  EXG_CUDA(cudaMemsetAsync(col_all, 0, (size_t)S * Cc * 4, st));
+  EXG_CUDA(cudaMemsetAsync(col_pos, 0, (size_t)S * Cc * 4, st));
+  dim3 grid((unsigned)((R + FWD_ROWS - 1) / FWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
   ExgProfScope prof(EXG_PC_NCE_FWD, (double)S * R * B * N * exg_dtype_size(dtype), stream);
-  nce_fwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);
+  nce_fwd_kernel<<<grid, NT, 0, st>>>(a);
   EXG_LAUNCH_CHECK("nce_fwd");
   return 0;
 }
@@ -191,8 +295,8 @@ extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, co
   a.row_all = const_cast<float*>(row_all); a.row_pos = const_cast<float*>(row_pos);
   a.col_all = const_cast<float*>(col_all); a.col_pos = const_cast<float*>(col_pos);
   a.wr = wr; a.wc = wc; a.G = G; a.g_dtype = g_dtype; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
-  const long R = (long)B * T;
-  dim3 grid((unsigned)((R + SLAB - 1) / SLAB), (unsigned)S);
+  const long R = (long)B * T, Cc = (long)B * N;
+  dim3 grid((unsigned)((R + BWD_ROWS - 1) / BWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
   ExgProfScope prof(EXG_PC_NCE_BWD, (double)S * R * B * N * (exg_dtype_size(dtype) + exg_dtype_size(g_dtype)), stream);
   nce_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("nce_bwd");

@@ -50,18 +50,23 @@ def _self_attn_fwd(K, xn, in_w, in_b, out_w, out_b, key_pad, B, S):
     return delta, (qkv, o, lse)
 
 
-def _self_attn_bwd(K, dxT, saved, xn, in_w, out_w, key_pad, B, S):
+def _sk(sinks, i):
+    return sinks[i] if sinks is not None else None
+
+
+def _self_attn_bwd(K, dxT, saved, xn, in_w, out_w, key_pad, B, S, sk=(None, None, None, None)):
     """dxT: grad of the block output of the attention residual branch, in T.  Returns
-    (dxn T, dW_in, db_in, dW_out, db_out)."""
+    (dxn T, dW_in, db_in, dW_out, db_out).  sk = gradient sinks (dW_in, db_in, dW_out, db_out): fp32 views of
+    the trainer's flat gradient buffer that the kernels write / accumulate into directly (no autograd add)."""
     qkv, o, lse = saved
-    db_out = K.colsum(dxT)
-    dW_out = K.gemm(dxT, o, transA=True, transB=True, out_dtype=torch.float32)
+    db_out = K.colsum(dxT, out=sk[3])
+    dW_out = K.gemm(dxT, o, transA=True, transB=True, out_dtype=torch.float32, out=sk[2])
     do = K.gemm(dxT, out_w, transB=True)
     dqkv = torch.empty_like(qkv)
     K.attn_bwd(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], o, do, lse, key_pad,
                dqkv[:, :C], dqkv[:, C:2 * C], dqkv[:, 2 * C:], B, HEADS, S, S, SCALE)
-    db_in = K.colsum(dqkv)
-    dW_in = K.gemm(dqkv, xn, transA=True, transB=True, out_dtype=torch.float32)
+    db_in = K.colsum(dqkv, out=sk[1])
+    dW_in = K.gemm(dqkv, xn, transA=True, transB=True, out_dtype=torch.float32, out=sk[0])
     dxn = K.gemm(dqkv, in_w, transB=True)
     return dxn, dW_in, db_in, dW_out, db_out
 
@@ -73,13 +78,14 @@ def _ffn_fwd(K, h, fc_w, fc_b, proj_w, proj_b):
     return delta, (u, f)
 
 
-def _ffn_bwd(K, dxT, saved, h, fc_w, proj_w):
+def _ffn_bwd(K, dxT, saved, h, fc_w, proj_w, sk=(None, None, None, None)):
+    """sk = gradient sinks (dW_fc, db_fc, dW_proj, db_proj)."""
     u, f = saved
-    db_proj = K.colsum(dxT)
-    dW_proj = K.gemm(dxT, f, transA=True, transB=True, out_dtype=torch.float32)
+    db_proj = K.colsum(dxT, out=sk[3])
+    dW_proj = K.gemm(dxT, f, transA=True, transB=True, out_dtype=torch.float32, out=sk[2])
     du = K.gemm(dxT, proj_w, transB=True, epilogue=ops.EPI_QGELU_BWD, aux=u)
-    db_fc = K.colsum(du)
-    dW_fc = K.gemm(du, h, transA=True, transB=True, out_dtype=torch.float32)
+    db_fc = K.colsum(du, out=sk[1])
+    dW_fc = K.gemm(du, h, transA=True, transB=True, out_dtype=torch.float32, out=sk[0])
     dh = K.gemm(du, fc_w, transB=True)
     return dh, dW_fc, db_fc, dW_proj, db_proj
 
@@ -96,7 +102,8 @@ class EncoderStackFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x0, key_pad, meta, g_post, b_post, *params):
         K = ops.get()
-        B, S, L, T, shadows = meta
+        B, S, L, T, shadows = meta[:5]
+        ctx.sinks = meta[5] if len(meta) > 5 else None      # per-parameter gradient sinks (ENC_KEYS order) or None
         M = B * S
         stages = torch.empty((L, M, C), dtype=T, device=x0.device)
         saved = []
@@ -133,18 +140,24 @@ class EncoderStackFn(torch.autograd.Function):
         d_stages = d_stages.contiguous()
         TT = None if T == torch.float32 else T
         grads = [None] * (12 * L)
+        sinks = ctx.sinks
         dx, dxT, dg_post, db_post = K.layernorm_bwd(d_stages[L - 1], ctx.x_last, ctx.post[0], dxT_dtype=TT)
         for i in reversed(range(L)):
             (in_w, in_b, out_w, out_b, g1, b1, fc_w, fc_b, pj_w, pj_b, g2, b2) = params[12 * i:12 * i + 12]
             x_in, xn, att, x_mid, h, ffn, (in_wT, out_wT, fc_wT, pj_wT) = ctx.saved[i]
-            dh, dW_fc, db_fc, dW_pj, db_pj = _ffn_bwd(K, dxT if TT else dx, ffn, h, fc_wT, pj_wT)
-            dxm, dxmT, dg2, db2 = K.layernorm_bwd(dh, x_mid, g2, dres=dx, dxT_dtype=TT)
+            sk = sinks[12 * i:12 * i + 12] if sinks is not None else [None] * 12
+            dh, dW_fc, db_fc, dW_pj, db_pj = _ffn_bwd(K, dxT if TT else dx, ffn, h, fc_wT, pj_wT,
+                                                      (sk[6], sk[7], sk[8], sk[9]))
+            dxm, dxmT, dg2, db2 = K.layernorm_bwd(dh, x_mid, g2, dres=dx, dxT_dtype=TT,
+                                                  dg_out=(sk[10], sk[11]) if sk[10] is not None else None)
             dxn, dW_in, db_in, dW_out, db_out = _self_attn_bwd(K, dxmT if TT else dxm, att, xn, in_wT, out_wT,
-                                                               key_pad, B, S)
+                                                               key_pad, B, S, (sk[0], sk[1], sk[2], sk[3]))
             dx, dxT, dg1, db1 = K.layernorm_bwd(dxn, x_in, g1, dy2=d_stages[i - 1] if i > 0 else None,
-                                                dres=dxm, dxT_dtype=TT if i > 0 else None)
-            grads[12 * i:12 * i + 12] = [dW_in, db_in, dW_out, db_out, dg1, db1, dW_fc, db_fc, dW_pj, db_pj,
-                                         dg2, db2]
+                                                dres=dxm, dxT_dtype=TT if i > 0 else None,
+                                                dg_out=(sk[4], sk[5]) if sk[4] is not None else None)
+            if sinks is None:
+                grads[12 * i:12 * i + 12] = [dW_in, db_in, dW_out, db_out, dg1, db1, dW_fc, db_fc, dW_pj, db_pj,
+                                             dg2, db2]
             ctx.saved[i] = None
         return (dx, None, None, dg_post, db_post, *grads)
 

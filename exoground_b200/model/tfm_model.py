@@ -74,7 +74,13 @@ class TemporalEncoder(nn.Module):
     def run(self, x0, key_pad_u8, B, S, wT, prefix, g_post, b_post, T):
         """x0 fp32 [B*S, C] -> stages [L, B*S, C] (T); last stage has (g_post, b_post) LayerNorm applied."""
         params, shadows = _stack_args(self, prefix, engine.ENC_KEYS, wT, T)
-        return engine.EncoderStackFn.apply(x0, key_pad_u8, (B, S, self.layers, T, shadows), g_post, b_post, *params)
+        sinks = None
+        if getattr(self, "_grad_sink", False) and torch.is_grad_enabled():
+            # a trainer owns (and zeroes) the .grad views: the backward kernels write into them directly
+            if all(p.grad is not None and p.grad.dtype == torch.float32 and p.grad.is_contiguous() for p in params):
+                sinks = [p.grad for p in params]
+        return engine.EncoderStackFn.apply(x0, key_pad_u8, (B, S, self.layers, T, shadows, sinks), g_post, b_post,
+                                           *params)
 
 
 class TemporalDecoder(nn.Module):

@@ -131,14 +131,17 @@ class CudaBackend:
         return out, s
 
     def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
-                      want_dx=True):
+                      want_dx=True, dg_out=None):
         """Backward of y = LN(x)*gamma+beta with dy = dy1[map1] (+ dy2[map2]).
         Returns (dx fp32 [rows,C] = dres + LN'(dy), dxT copy or None, dgamma fp32 [C], dbeta fp32 [C])."""
         _cuda(dy1, x, gamma, dy2, dres)
         rows, Cn = x.shape
         dx = torch.empty((rows, Cn), dtype=torch.float32, device=x.device) if want_dx else None
         dxT = torch.empty((rows, Cn), dtype=dxT_dtype, device=x.device) if dxT_dtype is not None else None
-        dg = torch.zeros(2, Cn, dtype=torch.float32, device=x.device)
+        if dg_out is not None:      # (dgamma, dbeta) gradient sinks: the kernel accumulates into them
+            dg = dg_out
+        else:
+            dg = torch.zeros(2, Cn, dtype=torch.float32, device=x.device)
         L.check(self.lib.exg_layernorm_bwd(_p(dy1), _dt(dy1.dtype), _rm(map1, rows), _p(dy2),
                                            _dt(dy2.dtype) if dy2 is not None else 0, _rm(map2, rows), _p(x),
                                            _dt(x.dtype), _p(gamma), None, None, _p(dres), _p(dx), _p(dxT),
@@ -178,12 +181,14 @@ class CudaBackend:
                                         _rm(map_dx, rows), int(accumulate), rows, Cn, _stream()), "exg_l2norm_bwd")
         return dx
 
-    def colsum(self, x):
-        """fp32 [N] = sum over rows of x [M,N]."""
-        _cuda(x)
+    def colsum(self, x, out=None):
+        """fp32 [N] = sum over rows of x [M,N]; with `out` the sums are ACCUMULATED into it (gradient sinks)."""
+        _cuda(x, out)
         M, N = x.shape
-        out = torch.empty(N, dtype=torch.float32, device=x.device)
-        L.check(self.lib.exg_colsum(_p(x), _dt(x.dtype), M, N, _rows2d(x), _p(out), 0, _stream()), "exg_colsum")
+        acc = out is not None
+        if out is None:
+            out = torch.empty(N, dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_colsum(_p(x), _dt(x.dtype), M, N, _rows2d(x), _p(out), int(acc), _stream()), "exg_colsum")
         return out
 
     def cast(self, src, dtype, out=None):

@@ -128,6 +128,8 @@ class TanTrainStep:
         for n, p in m.named_parameters():
             off, numel, shape = fp.index[n]
             p.grad = g[off:off + numel].view(shape) if n not in fp.unused else None
+        for mod in m.modules():           # stack weight gradients go straight into the flat buffer (engine sinks)
+            mod._grad_sink = True
         self.m1 = torch.zeros_like(fp.flat)
         self.m2 = torch.zeros_like(fp.flat)
         if m.compute_dtype == torch.bfloat16:

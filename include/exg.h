@@ -159,7 +159,8 @@ int exg_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
  * tgt[b,k,t]; columns with col_valid==0 (padded sentences, loss.py:244) are skipped.
  * fwd: exp-sums with a fixed shift (|logit*inv_temp| <= inv_temp since |cos|<=1):
  *   row_all[s,r]=sum_c e, row_pos[s,r]=sum_{c pos} e, col_all[s,c]=sum_r e, col_pos[s,c]=sum_{r pos} e,
- *   e = exp(L*inv_temp - inv_temp).  col_* are accumulated with atomics: caller zero-initialises.
+ *   e = exp(L*inv_temp - inv_temp).  All four outputs are zeroed by the call and accumulated with atomics.
+ *   Rows are read with 16-byte loads when B*N is a multiple of 8 (element-wise otherwise).
  * bwd: G[s,r,c] = inv_temp * ( wr[r]*(e/row_all - pos*e/row_pos) + wc[c]*(e/col_all - pos*e/col_pos) )
  *   written in g_dtype; invalid columns get 0.  wr/wc: fp32 per-row / per-column weights (0 = unused).
  */

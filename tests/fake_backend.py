@@ -80,7 +80,7 @@ class TorchBackend:
         return y, s
 
     def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
-                      want_dx=True):
+                      want_dx=True, dg_out=None):
         rows, C = x.shape
         dy = dy1.view(-1, C)[_map_idx(map1, rows, x.device)].float()
         if dy2 is not None:
@@ -95,7 +95,11 @@ class TorchBackend:
         if dres is not None:
             dx = dx + dres
         dxT = dx.to(dxT_dtype) if dxT_dtype is not None else None
-        return (dx if want_dx else None), dxT, (dy * xhat).sum(0), dy.sum(0)
+        dgam, dbet = (dy * xhat).sum(0), dy.sum(0)
+        if dg_out is not None:
+            dg_out[0].add_(dgam); dg_out[1].add_(dbet)
+            dgam, dbet = dg_out[0], dg_out[1]
+        return (dx if want_dx else None), dxT, dgam, dbet
 
     def add_rows(self, x, rows, *, map_x=None, x2=None, map_x2=None, add=None, add_period=0, out=None,
                  out_dtype=torch.float32, map_out=None, out2_dtype=None):
@@ -128,7 +132,10 @@ class TorchBackend:
         dv[idx] = d.to(dx.dtype)
         return dx
 
-    def colsum(self, x):
+    def colsum(self, x, out=None):
+        if out is not None:
+            out += x.float().sum(0)
+            return out
         return x.float().sum(0)
 
     def cast(self, src, dtype, out=None):
