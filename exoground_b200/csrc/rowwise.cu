@@ -348,6 +348,16 @@ __global__ void stage_mean_kernel(const void* __restrict__ x, int xd, long strid
   }
 }
 
+__global__ void bcast_rows_kernel(const float* __restrict__ g, float alpha, void* __restrict__ out, int od,
+                                  long stride, int S, long n) {
+  const long n4 = n / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    float4 v = *reinterpret_cast<const float4*>(g + i * 4);
+    v.x *= alpha; v.y *= alpha; v.z *= alpha; v.w *= alpha;
+    for (int s = 0; s < S; ++s) store4(out, od, (long)s * stride + i * 4, v);
+  }
+}
+
 inline int grid_for(long work_items, int threads, int max_blocks_per_sm = 8) {
   long b = (work_items + threads - 1) / threads;
   long cap = (long)exg_num_sms() * max_blocks_per_sm;
@@ -529,5 +539,17 @@ extern "C" int exg_stage_mean(const void* x, int x_dtype, long stage_stride, int
   stage_mean_kernel<<<grid_for(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(x, x_dtype, stage_stride, S,
                                                                           out, outT, outT_dtype, n);
   EXG_LAUNCH_CHECK("stage_mean");
+  return 0;
+}
+
+extern "C" int exg_bcast_rows(const float* g, float alpha, void* out, int out_dtype, long stage_stride, int S,
+                              long n, void* stream) {
+  EXG_CHECK_ARG(g && out && exg_valid_dtype(out_dtype) && S > 0, "bcast_rows: bad argument");
+  EXG_CHECK_ARG(n % 4 == 0 && stage_stride % 4 == 0, "bcast_rows: n must be a multiple of 4");
+  if (n <= 0) return 0;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)n * (4.0 + S * exg_dtype_size(out_dtype)), stream);
+  bcast_rows_kernel<<<grid_for(n / 4, 256), 256, 0, (cudaStream_t)stream>>>(g, alpha, out, out_dtype, stage_stride,
+                                                                          S, n);
+  EXG_LAUNCH_CHECK("bcast_rows");
   return 0;
 }

@@ -223,3 +223,113 @@ class NceLossFn(torch.autograd.Function):
         G = ops.get().nce_bwd(logits, tgt, col_valid, sums, (wr * g).contiguous(), (wc * g).contiguous(),
                               B, T, N, inv_temp)
         return G, None, None, None, None, None, None, None
+
+
+class StageMeanFn(torch.autograd.Function):
+    """mean over the stage axis of stages [S, M, C] -> fp32 [M, C]
+    (`get_unimodal_features(...).mean(dim=1)`: exo_ground_model.py:153-154)."""
+
+    @staticmethod
+    def forward(ctx, stages):
+        out, _ = ops.get().stage_mean(stages.contiguous())
+        ctx.meta = (stages.shape[0], stages.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        S, dtype = ctx.meta
+        return ops.get().bcast_rows(g.contiguous().float(), S, 1.0 / S, dtype)
+
+
+class InfoNceBmmFn(torch.autograd.Function):
+    """-mean_b,t log_softmax(f1n[b] f2n[b]^T / temp)[t, t] for L2-normalised f1n, f2n [B,T,D]
+    (compute_info_nce_loss: exo_ground_model.py:206-234, loss_egoexo4d.py:325-347).  One batched GEMM for the
+    T x T similarities, one row-wise diagonal cross-entropy kernel; the gradient goes back through two GEMMs."""
+
+    @staticmethod
+    def forward(ctx, f1n, f2n, inv_temp):
+        K = ops.get()
+        B, T, D = f1n.shape
+        sim = K.gemm(f1n, f2n, alpha=inv_temp, out_dtype=torch.float32)           # [B,T,T]
+        loss_rows, lse = K.xent_diag_fwd(sim.view(B * T, T), T)
+        ctx.saved = (f1n, f2n, sim, lse, inv_temp)
+        return loss_rows.mean()
+
+    @staticmethod
+    def backward(ctx, g):
+        K = ops.get()
+        f1n, f2n, sim, lse, inv_temp = ctx.saved
+        B, T, D = f1n.shape
+        # d sim (already holds the 1/(B*T) of the mean; the upstream scalar is applied on the small outputs)
+        G = K.xent_diag_bwd(sim.view(B * T, T), lse, inv_temp / (B * T), T, g_dtype=f1n.dtype).view(B, T, T)
+        d1 = K.gemm(G, f2n, transB=True) if ctx.needs_input_grad[0] else None      # [B,T,D] = G @ f2n
+        d2 = K.gemm(G, f1n, transA=True, transB=True) if ctx.needs_input_grad[1] else None   # G^T @ f1n
+        return (d1 * g if d1 is not None else None), (d2 * g if d2 is not None else None), None
+
+
+class XviewNceFn(torch.autograd.Function):
+    """Per-(b,t) cross-view InfoNCE + monitors (loss_egoexo4d.py:269-323, :201-233); differentiable in out_feat."""
+
+    @staticmethod
+    def forward(ctx, out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp):
+        K = ops.get()
+        loss, l1, pc, nc, stats = K.xview_nce_fwd(out_feat.contiguous(), ego, pos_idx, neg_idx, same_feat, same_idx,
+                                                  only_same, inv_temp)
+        ctx.saved = (out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp, stats)
+        ctx.mark_non_differentiable(l1, pc, nc)
+        return loss, l1, pc, nc
+
+    @staticmethod
+    def backward(ctx, gl, *_):
+        out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp, stats = ctx.saved
+        go = ops.get().xview_nce_bwd(out_feat.contiguous(), ego, pos_idx, neg_idx, same_feat, same_idx, only_same,
+                                     inv_temp, stats, gl.contiguous().float())
+        return go, None, None, None, None, None, None, None
+
+
+class GroundLossFn(torch.autograd.Function):
+    """(1 - mean IoU) + L1 terms of get_grounding_loss_reg_head (loss_egoexo4d.py:73-145) in one launch.
+    Returns (loss, stats, iou); only `loss` is differentiable (w.r.t. preds [M,2])."""
+
+    @staticmethod
+    def forward(ctx, preds, gt_a, gt_b, text_pad_u8, use_cd, eps, thresholds):
+        stats, iou, dp = ops.get().ground_loss(preds.contiguous().float(), gt_a, gt_b, text_pad_u8, use_cd, eps,
+                                               thresholds)
+        l1 = stats[0] + stats[1] if use_cd else (stats[0] + stats[1]) * 0.5
+        loss = (1.0 - stats[2]) + l1
+        ctx.saved = (dp, preds.dtype)
+        ctx.mark_non_differentiable(stats, iou)
+        return loss, stats, iou
+
+    @staticmethod
+    def backward(ctx, g, *_):
+        dp, dtype = ctx.saved
+        return (dp * g).to(dtype), None, None, None, None, None, None
+
+
+class MlpReluFn(torch.autograd.Function):
+    """y = relu(x W1^T + b1) W2^T + b2 (ViewInvariantMLP.mlp: vi_encoder.py:215-219).  ReLU lives in the first GEMM's
+    epilogue, its mask in the epilogue of the GEMM that produces dh.  x [M,D] in T; y in out_dtype."""
+
+    @staticmethod
+    def forward(ctx, x, w1, w1T, b1, w2, w2T, b2, out_dtype):
+        from ..ops import lib as L
+        K = ops.get()
+        h = K.gemm(x, w1T, bias=b1, epilogue=L.EPI_RELU)
+        y = K.gemm(h, w2T, bias=b2, out_dtype=out_dtype)
+        ctx.saved = (x, h, w1T, w2T)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from ..ops import lib as L
+        K = ops.get()
+        x, h, w1T, w2T = ctx.saved
+        dy = _T(dy.contiguous(), x.dtype)
+        dW2 = K.gemm(dy, h, transA=True, transB=True, out_dtype=torch.float32)
+        db2 = K.colsum(dy)
+        dh = K.gemm(dy, w2T, transB=True, epilogue=L.EPI_RELU_BWD, aux=h)
+        dW1 = K.gemm(dh, x, transA=True, transB=True, out_dtype=torch.float32)
+        db1 = K.colsum(dh)
+        dx = K.gemm(dh, w1T, transB=True) if ctx.needs_input_grad[0] else None
+        return dx, dW1, None, db1, dW2, None, db2, None

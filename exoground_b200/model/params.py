@@ -25,6 +25,13 @@ def is_no_decay(name):
     return any(k in name for k in (".ln_", ".bias", ".logit_scale", ".entropy_scale"))
 
 
+def own_named_parameters(module):
+    """named_parameters() minus those that live under a nested ExgModule (e.g. the frozen `vi_encoder` inside
+    keystep_ground_model.GroundingModel), which keeps its own flat buffer."""
+    nested = [n + "." for n, m in module.named_modules() if n and isinstance(m, ExgModule)]
+    return [(n, p) for n, p in module.named_parameters() if not any(n.startswith(pre) for pre in nested)]
+
+
 class FlatParams:
     def __init__(self, module):
         self.module = module
@@ -49,7 +56,7 @@ class FlatParams:
     def _layout(self):
         def cls(n):
             return 2 if n in self.unused else (0 if is_no_decay(n) else 1)
-        named = [(n, p) for n, p in self.module.named_parameters()]
+        named = own_named_parameters(self.module)
         named.sort(key=lambda np_: cls(np_[0]))
         off = 0
         index = {}

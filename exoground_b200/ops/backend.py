@@ -208,6 +208,71 @@ class CudaBackend:
                                         _dt(outT.dtype) if outT is not None else 0, n, _stream()), "exg_stage_mean")
         return out, outT
 
+    def bcast_rows(self, g, S, alpha, out_dtype):
+        """out[s] = alpha * g for s < S (backward of stage_mean); g fp32 [...]. Returns [S, ...] of out_dtype."""
+        _cuda(g)
+        out = torch.empty((S,) + tuple(g.shape), dtype=out_dtype, device=g.device)
+        L.check(self.lib.exg_bcast_rows(_p(g), float(alpha), _p(out), _dt(out.dtype), g.numel(), S, g.numel(),
+                                        _stream()), "exg_bcast_rows")
+        return out
+
+    # ------------------------------------------------------------------ ExoGround losses
+    def xent_diag_fwd(self, logits, period):
+        """logits [rows, cols]; target column of row r is r % period.  Returns fp32 (loss_rows, lse_rows)."""
+        _cuda(logits)
+        rows, cols = logits.shape
+        out = torch.empty((2, rows), dtype=torch.float32, device=logits.device)
+        L.check(self.lib.exg_xent_diag_fwd(_p(logits), _dt(logits.dtype), _p(out[0]), _p(out[1]), rows, cols,
+                                           int(period), _stream()), "exg_xent_diag_fwd")
+        return out[0], out[1]
+
+    def xent_diag_bwd(self, logits, lse, scale, period, g_dtype=None):
+        _cuda(logits, lse)
+        rows, cols = logits.shape
+        G = torch.empty(logits.shape, dtype=g_dtype or logits.dtype, device=logits.device)
+        L.check(self.lib.exg_xent_diag_bwd(_p(logits), _dt(logits.dtype), _p(lse), float(scale), _p(G), _dt(G.dtype),
+                                           rows, cols, int(period), _stream()), "exg_xent_diag_bwd")
+        return G
+
+    def xview_nce_fwd(self, out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp):
+        """out_feat [B,T,D] (T dtype), ego fp32 [B,V,T,D], idx int64 [B,T]; same_* optional.
+        Returns (loss, l1, pos_cos, neg_cos) fp32 [B,T] and the stats workspace [B,T,8]."""
+        _cuda(out_feat, ego, pos_idx, neg_idx, same_feat, same_idx)
+        B, T, D = out_feat.shape
+        V = ego.shape[1]
+        res = torch.empty((4, B, T), dtype=torch.float32, device=out_feat.device)
+        stats = torch.empty((B, T, 8), dtype=torch.float32, device=out_feat.device)
+        L.check(self.lib.exg_xview_nce_fwd(_p(out_feat), _dt(out_feat.dtype), _p(ego), _p(pos_idx), _p(neg_idx),
+                                           _p(same_feat), _p(same_idx), int(bool(only_same)), B, V, T, D,
+                                           float(inv_temp), _p(res[0]), _p(res[1]), _p(res[2]), _p(res[3]),
+                                           _p(stats), _stream()), "exg_xview_nce_fwd")
+        return res[0], res[1], res[2], res[3], stats
+
+    def xview_nce_bwd(self, out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp, stats, gl):
+        _cuda(out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, stats, gl)
+        B, T, D = out_feat.shape
+        V = ego.shape[1]
+        go = torch.empty_like(out_feat)
+        L.check(self.lib.exg_xview_nce_bwd(_p(out_feat), _dt(out_feat.dtype), _p(ego), _p(pos_idx), _p(neg_idx),
+                                           _p(same_feat), _p(same_idx), int(bool(only_same)), B, V, T, D,
+                                           float(inv_temp), _p(stats), _p(gl), _p(go), _dt(go.dtype), _stream()),
+                "exg_xview_nce_bwd")
+        return go
+
+    def ground_loss(self, preds, gt_a, gt_b, text_pad, use_cd, eps, thresholds):
+        """preds fp32 [M,2] contiguous; gt fp32 [M]; text_pad uint8 [M].  Returns (stats [4+n], iou [M],
+        dpreds [M,2]); stats = (mean|d0|, mean|d1|, mean IoU, n_valid, counts(IoU > th)...)."""
+        _cuda(preds, gt_a, gt_b, text_pad)
+        M = preds.shape[0]
+        n = len(thresholds)
+        th = (C.c_float * max(n, 1))(*[float(t) for t in thresholds])
+        stats = torch.empty(4 + n, dtype=torch.float32, device=preds.device)
+        iou = torch.empty(M, dtype=torch.float32, device=preds.device)
+        dp = torch.empty((M, 2), dtype=torch.float32, device=preds.device)
+        L.check(self.lib.exg_ground_loss(_p(preds), _p(gt_a), _p(gt_b), _p(text_pad), M, int(bool(use_cd)),
+                                         float(eps), th, n, _p(stats), _p(iou), _p(dp), _stream()), "exg_ground_loss")
+        return stats, iou, dp
+
     # ------------------------------------------------------------------ attention
     def attn_fwd(self, q, k, v, key_pad, B, H, Sq, Sk, scale):
         """q [B*Sq, H*64] / k,v [B*Sk, H*64] row-strided views (T); key_pad uint8 [B,Sk] or None.

@@ -55,6 +55,15 @@ _SIGS = {
     "exg_colsum": (C.c_int, [vp, C.c_int, C.c_long, C.c_long, C.c_long, vp, C.c_int, vp]),
     "exg_cast": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_long, vp]),
     "exg_stage_mean": (C.c_int, [vp, C.c_int, C.c_long, C.c_int, vp, vp, C.c_int, C.c_long, vp]),
+    "exg_bcast_rows": (C.c_int, [vp, C.c_float, vp, C.c_int, C.c_long, C.c_int, C.c_long, vp]),
+    "exg_xent_diag_fwd": (C.c_int, [vp, C.c_int, vp, vp, C.c_long, C.c_int, C.c_int, vp]),
+    "exg_xent_diag_bwd": (C.c_int, [vp, C.c_int, vp, C.c_float, vp, C.c_int, C.c_long, C.c_int, C.c_int, vp]),
+    "exg_xview_nce_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_float, vp, vp, vp, vp, vp, vp]),
+    "exg_xview_nce_bwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.c_float, vp, vp, vp, C.c_int, vp]),
+    "exg_ground_loss": (C.c_int, [vp, vp, vp, vp, C.c_long, C.c_int, C.c_float, C.POINTER(C.c_float), C.c_int,
+                                  vp, vp, vp, vp]),
     "exg_attn_fwd": (C.c_int, [vp, vp, vp, C.c_int, C.c_long, C.c_long, C.c_long, vp, vp, C.c_long, vp,
                                C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]),
     "exg_attn_bwd": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_long, C.c_long, C.c_long, C.c_long, vp, vp,

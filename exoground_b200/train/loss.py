@@ -17,6 +17,17 @@ from ..model.functional import NceLossFn
 INV_TEMP = 1.0 / 0.07      # train/loss.py:68-69 (logits / 0.07 for args.sim == 'cos')
 
 
+def circulant(tensor, dim):
+    """Circulant expansion along `dim`, new axis last: circulant([0,1,2], 0) = [[0,1,2],[2,0,1],[1,2,0]]
+    (train/loss.py:12-20 / loss_egoexo4d.py:18-26, used by the self-labelling branch); out[.., i, .., j] =
+    tensor[.., (j - i) mod S, ..], one index_select instead of the reference's flip / cat / unfold."""
+    S = tensor.shape[dim]
+    dim = dim % tensor.dim()
+    ar = torch.arange(S, device=tensor.device)
+    idx = (ar[None, :] - ar[:, None]) % S
+    return tensor.index_select(dim, idx.reshape(-1)).unflatten(dim, (S, S)).movedim(dim + 1, -1)
+
+
 def get_mask_from_time(start_list, end_list, num_timestamp, num_text, device='cuda'):
     """bool [B, num_text, T]: 1 where start <= t < end (reference train/loss.py:26-43, minus its prints).
     Built on the host from the python lists and copied once."""

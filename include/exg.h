@@ -137,6 +137,10 @@ int exg_cast(const void* src, int src_dtype, void* dst, int dst_dtype, long n, v
 int exg_stage_mean(const void* x, int x_dtype, long stage_stride, int S, float* out, void* outT,
                    int outT_dtype, long n, void* stream);
 
+/* backward of exg_stage_mean: out[s*stage_stride + i] = alpha * g[i] for s < S (alpha = 1/S) */
+int exg_bcast_rows(const float* g, float alpha, void* out, int out_dtype, long stage_stride, int S, long n,
+                   void* stream);
+
 /* ---------------------------------------------------------------- attention -------------------
  * softmax(q k^T * scale + key_padding_mask) v per (batch, head); replaces nn.MultiheadAttention's
  * scaled-dot-product core at model/tfm_model.py:32,75,79 (need_weights=False).
@@ -174,6 +178,37 @@ int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t
 /* own_max[b,k] = max_t L[stage, (b,t), (b,k)]   (train/loss.py:283-286) */
 int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B, int T, int N,
                 void* stream);
+
+/* ---------------------------------------------------------------- ExoGround losses ------------
+ * Row-wise softmax cross-entropy with the target on the diagonal: the per-clip T x T InfoNCE of
+ * compute_info_nce_loss (model/exo_ground_model.py:206-234, keystep_ground_model.py:221-249,
+ * train/loss_egoexo4d.py:325-347) after the normalised-feature GEMM.  Row r has target column r % period.
+ *   fwd: lse_rows[r] = logsumexp(logits[r,:]); loss_rows[r] = lse - logits[r, r % period]
+ *   bwd: G[r,c] = scale * (softmax(logits[r,:])[c] - [c == r % period]) */
+int exg_xent_diag_fwd(const void* logits, int dtype, float* loss_rows, float* lse_rows, long rows, int cols,
+                      int period, void* stream);
+int exg_xent_diag_bwd(const void* logits, int dtype, const float* lse_rows, float scale, void* G, int g_dtype,
+                      long rows, int cols, int period, void* stream);
+/* Fused cross-view InfoNCE (train/loss_egoexo4d.py:269-323) and the L1 / cosine monitors (:201-233):
+ * per (b,t): o = out_feat[b,t], p = ego[b,pos_idx[b,t],t], n = ego[b,neg_idx[b,t],t],
+ * s = same_feat[b,same_idx[b,t]] (optional); logits = cos(o,.) * inv_temp over {p, n, s} ({p, s} if only_same);
+ * loss = -log_softmax[0]; l1 = mean |o_hat - p_hat|; pos_cos / neg_cos = cos(o,p) / cos(o,n).
+ * stats: fp32 [B,T,8] workspace carried to the backward, which writes d loss / d out_feat scaled by grad_loss[b,t]. */
+int exg_xview_nce_fwd(const void* out_feat, int dtype, const float* ego, const long* pos_idx, const long* neg_idx,
+                      const float* same_feat, const long* same_idx, int only_same, int B, int V, int T, int D,
+                      float inv_temp, float* loss, float* l1, float* pos_cos, float* neg_cos, float* stats,
+                      void* stream);
+int exg_xview_nce_bwd(const void* out_feat, int dtype, const float* ego, const long* pos_idx, const long* neg_idx,
+                      const float* same_feat, const long* same_idx, int only_same, int B, int V, int T, int D,
+                      float inv_temp, const float* stats, const float* grad_loss, void* grad_out, int g_dtype,
+                      void* stream);
+/* Grounding regression loss (train/loss_egoexo4d.py:73-145) in one launch, no host round trip:
+ * preds fp32 [M,2]; gt_a / gt_b fp32 [M] (center, duration | start, end); text_pad uint8 [M] (1 = padded).
+ * stats (device) = {mean|p0-g0|, mean|p1-g1|, mean IoU, n_valid, count(IoU > thresholds[k])...}; iou [M] (0 for
+ * padded rows); dpreds [M,2] = d[(1 - mean IoU) + L1 terms] / d preds.  thresholds is a HOST array (<= 8). */
+int exg_ground_loss(const float* preds, const float* gt_a, const float* gt_b, const uint8_t* text_pad, long M,
+                    int use_center_duration, float eps, const float* thresholds, int n_thresh, float* stats,
+                    float* iou, float* dpreds, void* stream);
 
 /* ---------------------------------------------------------------- optimizer -------------------
  * AdamW (torch.optim.AdamW semantics, train/main.py:418) on a flat fp32 segment; optional bf16

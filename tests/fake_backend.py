@@ -148,6 +148,74 @@ class TorchBackend:
         m = x.float().mean(0)
         return m, (m.to(outT_dtype) if outT_dtype is not None else None)
 
+    def bcast_rows(self, g, S, alpha, out_dtype):
+        return (g.float() * alpha).to(out_dtype).unsqueeze(0).repeat((S,) + (1,) * g.dim())
+
+    def xent_diag_fwd(self, logits, period):
+        x = logits.float()
+        rows = x.shape[0]
+        lse = torch.logsumexp(x, dim=1)
+        tgt = torch.arange(rows, device=x.device) % period
+        return lse - x[torch.arange(rows, device=x.device), tgt], lse
+
+    def xent_diag_bwd(self, logits, lse, scale, period, g_dtype=None):
+        x = logits.float()
+        rows = x.shape[0]
+        g = torch.exp(x - lse[:, None])
+        tgt = torch.arange(rows, device=x.device) % period
+        g[torch.arange(rows, device=x.device), tgt] -= 1.0
+        return (g * scale).to(g_dtype or logits.dtype)
+
+    @staticmethod
+    def _xview_parts(out_feat, ego, pos_idx, neg_idx, same_feat, same_idx):
+        B, T, D = out_feat.shape
+        bi = torch.arange(B, device=ego.device)[:, None]
+        ti = torch.arange(T, device=ego.device)[None, :]
+        o = out_feat.float()
+        ks = [ego[bi, pos_idx, ti], ego[bi, neg_idx, ti]]
+        if same_feat is not None:
+            ks.append(same_feat[bi, same_idx])
+        nrm = lambda x: x / x.norm(dim=2, keepdim=True).clamp(min=1e-12)
+        return o, nrm(o), [nrm(k.float()) for k in ks]
+
+    def xview_nce_fwd(self, out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp):
+        o, oh, kh = self._xview_parts(out_feat, ego, pos_idx, neg_idx, same_feat, same_idx)
+        c = [(oh * k).sum(2) for k in kh]
+        use = [0, 2] if (same_feat is not None and only_same) else list(range(len(kh)))
+        sims = torch.stack([c[i] * inv_temp for i in use], 2)
+        loss = -torch.log_softmax(sims, dim=2)[:, :, 0]
+        l1 = (oh - kh[0]).abs().mean(2)
+        return loss, l1, c[0], c[1], None
+
+    def xview_nce_bwd(self, out_feat, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp, stats, gl):
+        with torch.enable_grad():
+            o = out_feat.detach().float().requires_grad_(True)
+            loss = self.xview_nce_fwd(o, ego, pos_idx, neg_idx, same_feat, same_idx, only_same, inv_temp)[0]
+            (g,) = torch.autograd.grad((loss * gl).sum(), o)
+        return g.to(out_feat.dtype)
+
+    def ground_loss(self, preds, gt_a, gt_b, text_pad, use_cd, eps, thresholds):
+        with torch.enable_grad():
+            p = preds.detach().float().requires_grad_(True)
+            v = ~text_pad.bool()
+            a, b = p[:, 0], p[:, 1]
+            if use_cd:
+                ps, pe, gs, ge = a - b / 2, a + b / 2, gt_a - gt_b / 2, gt_a + gt_b / 2
+            else:
+                ps, pe, gs, ge = a, b, gt_a, gt_b
+            inter = (torch.minimum(pe, ge) - torch.maximum(ps, gs)).clamp(min=0)
+            union = torch.maximum(pe, ge) - torch.minimum(ps, gs)
+            iou = torch.where(v, inter / (union + eps), torch.zeros_like(inter))
+            n = v.float().sum()
+            l1a = ((a - gt_a).abs() * v).sum() / n
+            l1b = ((b - gt_b).abs() * v).sum() / n
+            miou = iou.sum() / n
+            loss = (1 - miou) + (l1a + l1b if use_cd else (l1a + l1b) / 2)
+            (dp,) = torch.autograd.grad(loss, p)
+        cnt = [((iou > t) & v).float().sum() for t in thresholds]
+        stats = torch.stack([l1a.detach(), l1b.detach(), miou.detach(), n] + cnt)
+        return stats, iou.detach(), dp
+
     def attn_fwd(self, q, k, v, key_pad, B, H, Sq, Sk, scale):
         d = 64
         qf = q.float().reshape(B, Sq, H, d).transpose(1, 2)

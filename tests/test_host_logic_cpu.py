@@ -69,3 +69,43 @@ def test_state_dict_roundtrip_with_ddp_prefix():
     m2.load_state_dict(sd)
     for (k1, v1), (k2, v2) in zip(m.state_dict().items(), m2.state_dict().items()):
         assert k1 == k2 and torch.equal(v1, v2)
+
+
+# ---------------------------------------------------------------------- ExoGround family
+def test_exo_small_host_logic(golden_dir):
+    from tests.exo_cases import run_exo_case
+    run_exo_case(_load(golden_dir, "exo_small"), "cpu", torch.float32)
+
+
+def test_keystep_small_host_logic(golden_dir):
+    from tests.exo_cases import run_keystep_case
+    run_keystep_case(_load(golden_dir, "keystep_small"), _load(golden_dir, "exo_small"), "cpu", torch.float32)
+
+
+def test_vi_mlp_grads_host_logic():
+    from tests.exo_cases import run_vi_mlp_grad_case
+    run_vi_mlp_grad_case("cpu", torch.float32)
+
+
+def test_exo_loss_dispatch_and_errors():
+    from exoground_b200.train import loss_egoexo4d as exo_loss
+    from exoground_b200.model import ExoGroundingTransformer
+    with pytest.raises(NotImplementedError):
+        ExoGroundingTransformer(1, 1, use_audio=True, video_embed_dim=16, text_embed_dim=16)
+    assert exo_loss.get_mode_cam_rank([["a", "b", "b"], ["c"]]) == ["b", "c"]
+    tm = torch.tensor([[False, False, True], [False, True, True]])
+    assert exo_loss.expand_ranks_with_mask(["x", "y"], tm) == ["x", "x", "y"]
+    # no-decoder variant: head on every stage of the joint encoder -> [B, E, N, 2]
+    m = ExoGroundingTransformer(2, 1, use_decoder=False, video_embed_dim=16, text_embed_dim=24,
+                                compute_dtype=torch.float32)
+    b = synth.exo_batch(B=2, T=8, N=4, d_video=16, d_text=24)
+    out = m(b["video_features"], b["narration_features"], b["video_padding_mask"], b["narration_padding_mask"])
+    assert out["interval_preds"].shape == (2, 2, 4, 2)
+    # grounding-only dispatch on the decoder variant
+    m = ExoGroundingTransformer(1, 1, video_embed_dim=16, text_embed_dim=24, compute_dtype=torch.float32)
+    out = m(b["video_features"], b["narration_features"], b["video_padding_mask"], b["narration_padding_mask"])
+    L, iou = exo_loss.get_loss(b, out, b["narration_padding_mask"], synth.exo_args(model="grounding", test=True))
+    assert iou.numel() == int((~b["narration_padding_mask"]).sum())
+    assert any(k.startswith("Rank ") for k in L)
+    L["loss"].backward()
+    assert m.grounding_head.weight.grad is not None

@@ -340,3 +340,62 @@ def test_gemm_tc2_fp32_out_splitk_batch(K):
 def test_gemm_tc2_refuses_aux_epilogues(K):
     with pytest.raises(L.ExgError):
         _gemm_case(K, 256, 512, 512, False, False, torch.bfloat16, L.GEMM_TC2, epilogue=L.EPI_RESID)
+
+
+# ------------------------------------------------------------------------------------------- ExoGround ops
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_bcast_rows(K, dt):
+    g = _rand((37, 512), torch.float32, 5)
+    got = K.bcast_rows(g, 3, 1.0 / 3, dt)
+    _check(got, REF.bcast_rows(g, 3, 1.0 / 3, dt), dt, "bcast_rows")
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,T", [(3, 16), (5, 64), (2, 100)])
+def test_xent_diag(K, dt, B, T):
+    lg = _rand((B * T, T), dt, 11, scale=3.0)
+    loss, lse = K.xent_diag_fwd(lg, T)
+    rl, rlse = REF.xent_diag_fwd(lg, T)
+    _check(loss, rl, torch.float32, "xent loss")
+    _check(lse, rlse, torch.float32, "xent lse")
+    G = K.xent_diag_bwd(lg, lse, 0.37, T, g_dtype=dt)
+    _check(G, REF.xent_diag_bwd(lg, rlse, 0.37, T, g_dtype=dt), dt, "xent G", scale=0.37)
+
+
+@pytest.mark.parametrize("same,only", [(False, False), (True, False), (True, True)])
+@pytest.mark.parametrize("D", [48, 512, 4096])
+def test_xview_nce(K, same, only, D):
+    B, V, T = 3, 5, 16
+    o = _rand((B, T, D), torch.float32, 1)
+    ego = _rand((B, V, T, D), torch.float32, 2)
+    g = _g(3)
+    pi = torch.randint(0, V, (B, T), generator=g).to(DEV)
+    ni = torch.randint(0, V, (B, T), generator=g).to(DEV)
+    sf = _rand((B, T, D), torch.float32, 4) if same else None
+    si = torch.randint(0, T, (B, T), generator=g).to(DEV) if same else None
+    got = K.xview_nce_fwd(o, ego, pi, ni, sf, si, only, 10.0)
+    ref = REF.xview_nce_fwd(o, ego, pi, ni, sf, si, only, 10.0)
+    for a, b, w in zip(got[:4], ref[:4], ("loss", "l1", "pos_cos", "neg_cos")):
+        _check(a, b, torch.float32, f"xview {w}")
+    gl = _rand((B, T), torch.float32, 6)
+    go = K.xview_nce_bwd(o, ego, pi, ni, sf, si, only, 10.0, got[4], gl)
+    _check(go, REF.xview_nce_bwd(o, ego, pi, ni, sf, si, only, 10.0, None, gl), torch.float32, "xview grad")
+
+
+@pytest.mark.parametrize("use_cd", [True, False])
+@pytest.mark.parametrize("M", [24, 1000, 5000])
+def test_ground_loss(K, use_cd, M):
+    g = _g(9)
+    ga = torch.rand(M, generator=g).to(DEV)
+    gb = (torch.rand(M, generator=g) * 0.3).to(DEV)
+    if not use_cd:
+        ga, gb = ga - gb / 2, ga + gb / 2
+    preds = torch.stack((ga, gb), 1) + _rand((M, 2), torch.float32, 10, scale=0.05)
+    pad = (torch.rand(M, generator=g) < 0.3).to(torch.uint8).to(DEV)
+    th = (0.1, 0.3, 0.5, 0.7)
+    stats, iou, dp = K.ground_loss(preds.contiguous(), ga, gb, pad, use_cd, 1e-8, th)
+    rs, ri, rd = REF.ground_loss(preds, ga, gb, pad, use_cd, 1e-8, th)
+    _check(stats[:3], rs[:3], torch.float32, "ground stats")
+    assert torch.equal(stats[3:], rs[3:]), (stats, rs)
+    _check(iou, ri, torch.float32, "iou")
+    _check(dp, rd, torch.float32, "dpreds")

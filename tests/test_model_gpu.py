@@ -40,3 +40,24 @@ def test_launches_counted():
     x = torch.randn(8, 512, device="cuda")
     ops.get().cast(x, torch.bfloat16)
     assert ops.lib.launch_count() == before + 1
+
+
+# ---------------------------------------------------------------------- ExoGround family
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_exo_small(golden_dir, dt):
+    from tests.exo_cases import run_exo_case
+    from tests.tan_cases import load_golden
+    run_exo_case(load_golden(golden_dir, "exo_small"), "cuda", dt)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_keystep_small(golden_dir, dt):
+    from tests.exo_cases import run_keystep_case
+    from tests.tan_cases import load_golden
+    run_keystep_case(load_golden(golden_dir, "keystep_small"), load_golden(golden_dir, "exo_small"), "cuda", dt)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_vi_mlp_grads(dt):
+    from tests.exo_cases import run_vi_mlp_grad_case
+    run_vi_mlp_grad_case("cuda", dt)
