@@ -23,13 +23,14 @@ from . import loss as exg_loss
 class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
                  device="cuda", use_graph=True, process_group=None):
-        if not torch.cuda.is_available():
+        if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
+        self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
         self.model, self.args = model.to(device), args
         self.B, self.T, self.N = B, T, N
         self.lr, self.wd, self.betas, self.eps = lr, wd, betas, eps
         self.device = torch.device(device)
-        self.use_graph = use_graph
+        self.use_graph = use_graph and torch.device(device).type == "cuda"
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.step_count = 0
@@ -43,7 +44,9 @@ class TanTrainStep:
         self.tgt = torch.zeros(B, N, T, dtype=torch.bool, device=dev)
         self.abs_pos = torch.zeros(B, N, 2, device=dev)
         n_draw = 3 if model.use_text_pos_enc else 2
-        self.pos_host = torch.zeros(n_draw, dtype=torch.int64).pin_memory()
+        self.pos_host = torch.zeros(n_draw, dtype=torch.int64)
+        if self._on_cuda:
+            self.pos_host = self.pos_host.pin_memory()
         self.pos_dev = torch.zeros(n_draw, dtype=torch.int64, device=dev)
         self.loss_out = torch.zeros((), device=dev)
         self.model._pos_offsets = [self.pos_dev[i] for i in range(n_draw)]
@@ -137,7 +140,8 @@ class TanTrainStep:
             m._shadow_stale = False
             # from here on the shadow is kept fresh by the AdamW kernel itself
             m._shadow_managed = True
-        torch.cuda.synchronize()
+        if self._on_cuda:
+            torch.cuda.synchronize()
         if self.use_graph:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
