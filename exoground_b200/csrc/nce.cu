@@ -249,6 +249,13 @@ __global__ void own_max_kernel(const void* __restrict__ L, int dtype, float* __r
   }
 }
 
+}  // namespace
+int exg_nce_tma_fwd(const void*, int, const uint32_t*, const uint8_t*, float*, float*, float*, float*, int, int, int,
+                    int, float, cudaStream_t);
+int exg_nce_tma_bwd(const void*, int, const uint32_t*, const uint8_t*, const float*, const float*, const float*,
+                    const float*, const float*, const float*, void*, int, int, int, int, int, float, cudaStream_t);
+namespace {
+
 int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid, int S, int B, int T,
               int N) {
   EXG_CHECK_ARG(logits && tgt && col_valid, "nce: null pointer");
@@ -259,8 +266,8 @@ int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* 
 
 }  // namespace
 
-extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid,
-                           float* row_all, float* row_pos, float* col_all, float* col_pos, int S, int B, int T,
+extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits,
+                           const uint8_t* col_valid, float* row_all, float* row_pos, float* col_all, float* col_pos, int S, int B, int T,
                            int N, float inv_temp, void* stream) {
   int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N);
   if (rc) return rc;
@@ -277,13 +284,15 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
   EXG_CUDA(cudaMemsetAsync(col_pos, 0, (size_t)S * Cc * 4, st));
   dim3 grid((unsigned)((R + FWD_ROWS - 1) / FWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
   ExgProfScope prof(EXG_PC_NCE_FWD, (double)S * R * B * N * exg_dtype_size(dtype), stream);
+  rc = exg_nce_tma_fwd(logits, dtype, tgt_bits, col_valid, row_all, row_pos, col_all, col_pos, S, B, T, N, inv_temp, st);
+  if (rc) return rc == 1 ? 0 : rc;
   nce_fwd_kernel<<<grid, NT, 0, st>>>(a);
   EXG_LAUNCH_CHECK("nce_fwd");
   return 0;
 }
 
-extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid,
-                           const float* row_all, const float* row_pos, const float* col_all,
+extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits,
+                           const uint8_t* col_valid, const float* row_all, const float* row_pos, const float* col_all,
                            const float* col_pos, const float* wr, const float* wc, void* G, int g_dtype, int S,
                            int B, int T, int N, float inv_temp, void* stream) {
   int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N);
@@ -298,6 +307,9 @@ extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, co
   const long R = (long)B * T, Cc = (long)B * N;
   dim3 grid((unsigned)((R + BWD_ROWS - 1) / BWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
   ExgProfScope prof(EXG_PC_NCE_BWD, (double)S * R * B * N * (exg_dtype_size(dtype) + exg_dtype_size(g_dtype)), stream);
+  rc = exg_nce_tma_bwd(logits, dtype, tgt_bits, col_valid, row_all, row_pos, col_all, col_pos, wr, wc, G, g_dtype, S, B, T,
+                       N, inv_temp, (cudaStream_t)stream);
+  if (rc) return rc == 1 ? 0 : rc;
   nce_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("nce_bwd");
   return 0;

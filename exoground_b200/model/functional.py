@@ -220,8 +220,9 @@ class NceLossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         logits, sums, tgt, col_valid, wr, wc, (B, T, N), inv_temp = ctx.saved
+        tgt, bits = tgt if isinstance(tgt, tuple) else (tgt, None)     # (uint8 mask, nce_pack_targets(mask))
         G = ops.get().nce_bwd(logits, tgt, col_valid, sums, (wr * g).contiguous(), (wc * g).contiguous(),
-                              B, T, N, inv_temp)
+                              B, T, N, inv_temp, tgt_bits=bits)
         return G, None, None, None, None, None, None, None
 
 

@@ -130,8 +130,10 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N):
     rowp = tgt.any(dim=1).reshape(-1)                                               # [B*T]
     colp = tgt.any(dim=2).reshape(-1)                                               # [B*N]
 
-    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP)
-    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP)
+    tgt_bits = K.nce_pack_targets(tgt_u8)          # per-(clip, second) bit rows, shared by the 4 NCE launches
+    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits)
+    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits)
+    tgt_u8 = (tgt_u8, tgt_bits)
     wr_d, wc_d = _weights(rowp, colp, E)
     wr_j, wc_j = _weights(rowp, colp, D)
     use_th = args.loss_threshold > 0

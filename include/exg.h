@@ -167,11 +167,15 @@ int exg_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
  *   Rows are read with 16-byte loads when B*N is a multiple of 8 (element-wise otherwise).
  * bwd: G[s,r,c] = inv_temp * ( wr[r]*(e/row_all - pos*e/row_pos) + wc[c]*(e/col_all - pos*e/col_pos) )
  *   written in g_dtype; invalid columns get 0.  wr/wc: fp32 per-row / per-column weights (0 = unused).
+ * tgt_bits (optional): the same targets packed by exg_nce_pack_targets as [B*T, ceil(N/32)] uint32 rows
+ *   (bit n of row (b,t) = tgt[b,n,t]); with it, bf16 logits and B*N % 8 == 0 the calls take the TMA streaming
+ *   kernels (nce_tma.cu), otherwise the generic ones.
  */
-int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid,
+int exg_nce_pack_targets(const uint8_t* tgt, uint32_t* tgt_bits, int B, int T, int N, void* stream);
+int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits, const uint8_t* col_valid,
                 float* row_all, float* row_pos, float* col_all, float* col_pos,
                 int S, int B, int T, int N, float inv_temp, void* stream);
-int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid,
+int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits, const uint8_t* col_valid,
                 const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
                 const float* wr, const float* wc, void* G, int g_dtype,
                 int S, int B, int T, int N, float inv_temp, void* stream);

@@ -257,12 +257,22 @@ class TorchBackend:
         pos = pos & col_valid.bool().view(1, B * N)
         return e, pos
 
-    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp):
+    def nce_pack_targets(self, tgt):
+        B, N, T = tgt.shape
+        W = (N + 31) // 32
+        t = torch.zeros((B, W * 32, T), dtype=torch.int64, device=tgt.device)
+        t[:, :N] = (tgt != 0).long()
+        sh = (torch.arange(W * 32, device=tgt.device) % 32).view(1, -1, 1)
+        words = (t << sh).view(B, W, 32, T).sum(2)                       # [B, W, T]
+        words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)     # two's complement int32
+        return words.permute(0, 2, 1).reshape(B * T, W).to(torch.int32)
+
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None):
         e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp)
         ep = e * pos[None]
         return e.sum(-1), ep.sum(-1), e.sum(-2), ep.sum(-2)
 
-    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None):
+    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None):
         e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp)
         ra, rp, ca, cp = sums
         safe = lambda w, s: torch.where((w != 0) & (s > 0), w / s.clamp(min=1e-38), torch.zeros_like(s))

@@ -264,13 +264,15 @@ def test_attention(K, dt, B, Sq, Sk, masked):
 
 # ------------------------------------------------------------------------------------------- NCE
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("S,B,T,N", [(2, 3, 16, 8), (3, 5, 24, 4), (6, 16, 64, 32)])
+@pytest.mark.parametrize("S,B,T,N", [(2, 3, 16, 8), (3, 5, 24, 4), (6, 16, 64, 32), (2, 20, 5, 216), (1, 7, 3, 40),
+                                     (2, 33, 7, 8), (2, 64, 64, 32)])
 def test_nce(K, dt, S, B, T, N):
     Lg = (torch.rand((S, B * T, B * N), generator=_g(1)) * 2 - 1).to(dt).to(DEV)
     tgt = (torch.rand((B, N, T), generator=_g(2)) < 0.15).to(torch.uint8).to(DEV)
     cv = (torch.rand((B * N,), generator=_g(3)) < 0.8).to(torch.uint8).to(DEV)
     tgt = tgt * cv.view(B, N, 1)
     it = 1 / 0.07
+    assert torch.equal(K.nce_pack_targets(tgt), REF.nce_pack_targets(tgt))
     got = K.nce_fwd(Lg, tgt, cv, B, T, N, it)
     ref = REF.nce_fwd(Lg, tgt, cv, B, T, N, it)
     for a, r, n in zip(got, ref, ("row_all", "row_pos", "col_all", "col_pos")):
