@@ -2,8 +2,10 @@
 //
 //   warp 0      : TMA producer   (global -> 128B-swizzled smem ring, mbarrier complete_tx)
 //   warp 1      : MMA issuer     (one elected lane, tcgen05.mma cta_group::1, 128 x BN x 16 per instruction)
-//   warps 2..5  : epilogue       (tcgen05.ld TMEM -> registers -> bias / QuickGELU / ReLU -> 128B-swizzled smem
-//                                 staging -> TMA store, or TMA reduce-add for split-K partial sums)
+//   warps 2..9  : epilogue       (tcgen05.ld TMEM -> registers -> bias / QuickGELU / ReLU -> 128B-swizzled smem
+//                                 staging -> TMA store, or TMA reduce-add for split-K partial sums).  Two warps per
+//                                 TMEM lane quarter (= per SM sub-partition) take alternate 64-column chunks, so each
+//                                 scheduler has a second warp to issue from while one waits on TMEM / MUFU / TMA.
 //
 // One CTA per SM loops over output tiles (static round-robin).  The fp32 accumulator is double-buffered in
 // TMEM (2 x BN columns), so the epilogue of tile i overlaps the MMAs of tile i+1, and every global access is a
@@ -19,10 +21,11 @@ using namespace sm100;
 namespace {
 
 constexpr int BM = 128, BK = 64, UK = 16;
-constexpr int kEpiWarps = 4;
+constexpr int kEpiWarps = 8;
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
-constexpr int kStageBufs = 4;                      // staging ring per epilogue warp
+constexpr int kOutBufs = 2;                        // output staging ring per epilogue warp (plain epilogues)
+constexpr int kAuxBufs = 3;                        // aux-in epilogues: 1 output buffer + 2 aux-in buffers per warp
 constexpr uint32_t kStageBufBytes = 32 * 128;      // 32 rows x 128 B
 
 struct Tc2Args {
@@ -41,8 +44,10 @@ template <int BN> struct Cfg2 {
   static constexpr uint32_t kBBytes = BN * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 3 : 4;
-  static constexpr uint32_t kEpiBytes = kEpiWarps * kStageBufs * kStageBufBytes;     // 64 KB
-  static constexpr uint32_t kSmem = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+  __host__ __device__ static constexpr uint32_t epi_bytes(int aux_in) { return kEpiWarps * (aux_in ? kAuxBufs : kOutBufs) * kStageBufBytes; }
+  __host__ __device__ static constexpr uint32_t smem_bytes(int aux_in) {
+    return kStages * kStageBytes + epi_bytes(aux_in) + 1024 /*align*/ + 256 /*barriers*/;
+  }
 };
 
 struct TileCoord { int m0, n0, z, kb0, nkb; };
@@ -71,7 +76,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* epi_smem = smem + C_::kStages * C_::kStageBytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C_::kEpiBytes);
+  uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C_::epi_bytes(p.has_aux_in));
   uint64_t* empty = full + C_::kStages;
   uint64_t* tmem_full = empty + C_::kStages;     // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
@@ -164,18 +169,21 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===================== epilogue =====================
     const int ew = warp - 2;                      // staging slot
     const int lg = warp & 3;                      // TMEM lane group this warp may access
-    uint8_t* stage = epi_smem + (size_t)ew * kStageBufs * kStageBufBytes;
+    const int half = ew >> 2;                     // which of the two interleaved chunk sequences this warp takes
+    const uint32_t n_bufs = p.has_aux_in ? kAuxBufs : kOutBufs;
+    uint8_t* stage = epi_smem + (size_t)ew * n_bufs * kStageBufBytes;
     uint32_t sbuf = 0;                            // next staging buffer (ring)
     uint32_t ti = 0;
     const int cols_per_chunk = p.out_f32 ? 32 : 64;
-    // aux-in mode: staging buffers 0,1 hold outputs, 2,3 receive the aux chunks (double-buffered prefetch)
-    const uint32_t n_out_bufs = p.has_aux_in ? 2 : kStageBufs;
+    // aux-in mode: staging buffer 0 holds the output chunk, 1,2 receive the aux chunks (double-buffered prefetch)
+    const uint32_t n_out_bufs = p.has_aux_in ? 1 : kOutBufs;
+    const int c_first = half * cols_per_chunk, c_step = 2 * cols_per_chunk;
     uint64_t* my_aux_bar = aux_bar + 2 * ew;
     uint32_t ci = 0;                              // running chunk index of this warp (aux ring position)
     if (p.has_aux_in && lane == 0 && (int)blockIdx.x < total_tiles) {
       const TileCoord t0 = tile_coord(p, blockIdx.x, BN);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
-      tma_load_3d(stage + 2 * kStageBufBytes, &tmAuxIn, &my_aux_bar[0], t0.n0, t0.m0 + lg * 32, t0.z);
+      tma_load_3d(stage + 1 * kStageBufBytes, &tmAuxIn, &my_aux_bar[0], t0.n0 + c_first, t0.m0 + lg * 32, t0.z);
     }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
       const TileCoord t = tile_coord(p, tile, BN);
@@ -187,27 +195,27 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const bool rows_live = row0 < p.M;
       const int n_live = min(BN, p.N - t.n0);
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += cols_per_chunk) {
+      for (int c0 = c_first; c0 < BN; c0 += c_step) {
         const bool live = rows_live && c0 < n_live;      // warp-uniform
         uint32_t r[64];
         uint4 ax[8];
         if (p.has_aux_in) {
           // prefetch the aux chunk after this one (same tile, or first chunk of this CTA's next tile) ...
           if (lane == 0) {
-            int nt = tile, nc = c0 + cols_per_chunk;
-            if (nc >= BN) { nt = tile + gridDim.x; nc = 0; }
+            int nt = tile, nc = c0 + c_step;
+            if (nc >= BN) { nt = tile + gridDim.x; nc = c_first; }
             if (nt < total_tiles) {
               const TileCoord tn = tile_coord(p, nt, BN);
               const uint32_t nb = (ci + 1) & 1;
               mbar_arrive_expect_tx(&my_aux_bar[nb], kStageBufBytes);
-              tma_load_3d(stage + (2 + nb) * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
+              tma_load_3d(stage + (1 + nb) * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
                           tn.m0 + lg * 32, tn.z);
             }
           }
           // ... and take this chunk's aux rows (thread = row, 128B-swizzled) into registers
           const uint32_t cb = ci & 1;
           mbar_wait(&my_aux_bar[cb], (ci >> 1) & 1);
-          const uint8_t* abuf = stage + (2 + cb) * kStageBufBytes;
+          const uint8_t* abuf = stage + (1 + cb) * kStageBufBytes;
 #pragma unroll
           for (int u = 0; u < 8; ++u)
             ax[u] = *reinterpret_cast<const uint4*>(abuf + lane * 128 + ((u ^ (lane & 7)) << 4));
@@ -220,7 +228,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
           tmem_ld_wait();
         }
-        if (c0 + cols_per_chunk >= BN) {
+        if (c0 + c_step >= BN) {
           // all TMEM reads of this tile are done: hand the accumulator stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
@@ -245,7 +253,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         // ---- optional second output: the pre-activation (bf16), staged and stored first
         if (p.has_aux_out) {
           uint8_t* buf = stage + (size_t)(sbuf % n_out_bufs) * kStageBufBytes;
-          if (lane == 0) bulk_wait_read<kStageBufs - 1>();
+          if (lane == 0) bulk_wait_read<kOutBufs - 1>();
           __syncwarp();
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
@@ -284,7 +292,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         // ---- stage (128B-swizzled rows) and TMA-store the chunk
         uint8_t* buf = stage + (size_t)(sbuf % n_out_bufs) * kStageBufBytes;
-        if (lane == 0) { if (p.has_aux_in) bulk_wait_read<1>(); else bulk_wait_read<kStageBufs - 1>(); }
+        if (lane == 0) { if (p.has_aux_in) bulk_wait_read<0>(); else bulk_wait_read<kOutBufs - 1>(); }
         __syncwarp();
         if (p.out_f32) {
 #pragma unroll
@@ -368,14 +376,17 @@ int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
             const CUtensorMap& ti, const Tc2Args& a, cudaStream_t s) {
   static bool attr_set = false;
   auto kfn = gemm_tc2_kernel<BN>;
+  const uint32_t smem = Cfg2<BN>::smem_bytes(a.has_aux_in);
+  if (smem > 232448u) { exg_set_error("gemm_tc2: %u bytes of shared memory (BN=%d aux_in=%d)", smem, BN, a.has_aux_in); return EXG_EINVAL; }
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2<BN>::kSmem);
+    const uint32_t mx = Cfg2<BN>::smem_bytes(1) <= 232448u ? Cfg2<BN>::smem_bytes(1) : Cfg2<BN>::smem_bytes(0);
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx);
     if (e != cudaSuccess) { exg_set_error("gemm_tc2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
     attr_set = true;
   }
   const long total = (long)a.tiles_m * a.tiles_n * a.splits * a.batch;
   const int grid = (int)(total < exg_num_sms() ? total : exg_num_sms());
-  kfn<<<grid, kThreads, Cfg2<BN>::kSmem, s>>>(ta, tb, tc, tx, ti, a);
+  kfn<<<grid, kThreads, smem, s>>>(ta, tb, tc, tx, ti, a);
   EXG_LAUNCH_CHECK("gemm_tc2");
   return 0;
 }
@@ -430,6 +441,7 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
     const long t256 = tm * ((q->N + 255) / 256) * q->batch, t128 = tm * ((q->N + 127) / 128) * q->batch;
     const double e256 = wave_eff(t256), e128 = 0.85 * wave_eff(t128);
     if (q->N <= 128 || (e128 > e256 && t256 >= exg_num_sms() / 2)) bn = 128;
+    if (a.has_aux_in) bn = 128;      // 3 staging buffers per epilogue warp only fit beside the 4 x 32 KB ring
   }
   a.tiles_m = (int)tm; a.tiles_n = (q->N + bn - 1) / bn;
   const long tiles = tm * a.tiles_n * q->batch;
