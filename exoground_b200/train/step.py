@@ -8,6 +8,9 @@ B200 design:
     launches of exg_adamw (no-decay segment, decay segment) which also refresh the bf16 shadow weights;
   * the data-parallel replacement of DistributedDataParallel (train/main.py:413) is ONE NCCL all-reduce of the
     flat gradient buffer per step (sum; the 1/world_size of DDP's mean is folded into the AdamW kernel);
+  * host batches land in fp32 staging buffers (optionally on a copy stream while the previous step computes:
+    `step(batch, next_batch=...)` / `prefetch()`), and one cast kernel per feature tensor moves them into the
+    compute-dtype buffers the step reads, so the forward has no input cast and the PCIe copy overlaps compute;
   * the device part of the step (everything between the H2D copies and the loss read-back) is static-shape
     and free of host synchronisation, so it is captured once into a CUDA graph and replayed; the random
     positional offsets of the reference (tan_model.py:157,189) are drawn on the host every step and fed to
@@ -36,13 +39,24 @@ class TanTrainStep:
         self.step_count = 0
         self.graph = None
         dev = self.device
-        # static device-side inputs (targets of the per-step H2D copies)
-        self.video = torch.zeros(B, T, d_video, device=dev)
-        self.text = torch.zeros(B, N, d_text, device=dev)
-        self.vmask = torch.zeros(B, T, dtype=torch.bool, device=dev)
-        self.tmask = torch.zeros(B, N, dtype=torch.bool, device=dev)
-        self.tgt = torch.zeros(B, N, T, dtype=torch.bool, device=dev)
-        self.abs_pos = torch.zeros(B, N, 2, device=dev)
+        # staging buffers (targets of the per-step H2D copies, possibly written by the copy stream while a step runs)
+        self.video_s = torch.zeros(B, T, d_video, device=dev)
+        self.text_s = torch.zeros(B, N, d_text, device=dev)
+        self.vmask_s = torch.zeros(B, T, dtype=torch.bool, device=dev)
+        self.tmask_s = torch.zeros(B, N, dtype=torch.bool, device=dev)
+        self.tgt_s = torch.zeros(B, N, T, dtype=torch.bool, device=dev)
+        self.abs_pos_s = torch.zeros(B, N, 2, device=dev)
+        # static inputs of the (captured) device step; features already in the compute dtype
+        Tc = model.compute_dtype
+        self.video = torch.zeros(B, T, d_video, device=dev, dtype=Tc)
+        self.text = torch.zeros(B, N, d_text, device=dev, dtype=Tc)
+        self.vmask = torch.zeros_like(self.vmask_s)
+        self.tmask = torch.zeros_like(self.tmask_s)
+        self.tgt = torch.zeros_like(self.tgt_s)
+        self.abs_pos = torch.zeros_like(self.abs_pos_s)
+        self._copy_stream = None
+        self._staged_ready = self._staging_free = None
+        self._staged_id = None
         n_draw = 3 if model.use_text_pos_enc else 2
         self.pos_host = torch.zeros(n_draw, dtype=torch.int64)
         if self._on_cuda:
@@ -53,13 +67,11 @@ class TanTrainStep:
         self._prepared = False
 
     # ------------------------------------------------------------------ host -> device
-    def load_batch(self, batch, non_blocking=True):
-        """Copies one host batch (dict of synth.tan_batch / the loaders' collate dict; pinned tensors give
-        asynchronous copies) into the static device buffers and builds the [B,N,T] target mask.
-        Returns the number of bytes copied host->device."""
+    def _stage(self, batch, non_blocking=True):
+        """H2D copies of one host batch into the staging buffers, on the current stream.  Returns bytes copied."""
         n = 0
-        for dst, key in ((self.video, "video"), (self.text, "text"), (self.vmask, "video_padding_mask"),
-                         (self.tmask, "text_padding_mask")):
+        for dst, key in ((self.video_s, "video"), (self.text_s, "text"), (self.vmask_s, "video_padding_mask"),
+                         (self.tmask_s, "text_padding_mask")):
             src = batch[key]
             dst.copy_(src, non_blocking=non_blocking)
             n += src.numel() * src.element_size()
@@ -67,12 +79,65 @@ class TanTrainStep:
             tgt = batch["tgt"]
         else:
             tgt = exg_loss.get_mask_from_time(batch["start"], batch["end"], self.T, self.N, device="cpu")[0]
-        self.tgt.copy_(tgt, non_blocking=non_blocking)
+        self.tgt_s.copy_(tgt, non_blocking=non_blocking)
         n += tgt.numel()
         if batch.get("abs_text_pos") is not None:
-            self.abs_pos.copy_(batch["abs_text_pos"], non_blocking=non_blocking)
-            n += self.abs_pos.numel() * 4
+            self.abs_pos_s.copy_(batch["abs_text_pos"], non_blocking=non_blocking)
+            n += self.abs_pos_s.numel() * 4
         return n
+
+    def _commit(self):
+        """staging -> static step inputs on the current stream (feature tensors: one cast kernel each)."""
+        K = ops.get()
+        for src, dst in ((self.video_s, self.video), (self.text_s, self.text)):
+            if dst.dtype == src.dtype:
+                dst.copy_(src)
+            else:
+                K.cast(src, dst.dtype, out=dst)
+        self.vmask.copy_(self.vmask_s)
+        self.tmask.copy_(self.tmask_s)
+        self.tgt.copy_(self.tgt_s)
+        self.abs_pos.copy_(self.abs_pos_s)
+
+    def load_batch(self, batch, non_blocking=True):
+        """Copies one host batch (dict of synth.tan_batch / the loaders' collate dict; pinned tensors give
+        asynchronous copies) into the device buffers the step reads and builds the [B,N,T] target mask.
+        Returns the number of bytes copied host->device."""
+        if self._staging_free is not None:
+            torch.cuda.current_stream().wait_event(self._staged_ready)     # never race a prefetch in flight
+        n = self._stage(batch, non_blocking)
+        self._commit()
+        if self._staging_free is not None:
+            self._staging_free.record()
+        self._staged_id = None
+        return n
+
+    def prefetch(self, batch):
+        """Starts the H2D copies of a FUTURE batch on a side stream; they overlap whatever the main stream is
+        running.  The next step(batch) / load_batch of the same dict object picks the staged copy up."""
+        if not self._on_cuda:
+            self._stage(batch, False)
+            self._staged_id = id(batch)
+            return
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream()
+            self._staged_ready = torch.cuda.Event()
+            self._staging_free = torch.cuda.Event()
+            self._staging_free.record()
+        cs = self._copy_stream
+        cs.wait_event(self._staging_free)           # the last _commit() has read the staging buffers
+        with torch.cuda.stream(cs):
+            self._stage(batch, True)
+            self._staged_ready.record(cs)
+        self._staged_id = id(batch)
+
+    def _take_staged(self):
+        if self._on_cuda:
+            torch.cuda.current_stream().wait_event(self._staged_ready)
+        self._commit()
+        if self._on_cuda:
+            self._staging_free.record()
+        self._staged_id = None
 
     def _draw_offsets(self):
         m = self.model
@@ -173,8 +238,15 @@ class TanTrainStep:
         self._optimizer()
         return self.loss_out
 
-    def step(self, batch):
+    def step(self, batch, next_batch=None):
         """The user-facing call: host batch in, python float loss out (H2D copies and the loss read-back
-        included)."""
-        self.load_batch(batch)
-        return float(self.run().item())
+        included).  `next_batch` (optional) is staged on the copy stream while this step computes, so a loop
+        `for b, nb in zip(batches, batches[1:]): step(b, next_batch=nb)` hides the PCIe copy behind the step."""
+        if self._staged_id is not None and self._staged_id == id(batch):
+            self._take_staged()
+        else:
+            self.load_batch(batch)
+        loss = self.run()
+        if next_batch is not None:
+            self.prefetch(next_batch)
+        return float(loss.item())

@@ -80,3 +80,27 @@ def test_graph_replay_equals_eager_bf16():
         np.random.seed(12)        # identical positional-offset draws for both runs after preparation
         out.append([tr.step(b) for _ in range(3)])
     assert np.allclose(out[0], out[1], rtol=2e-3), out
+
+
+def test_prefetch_pipeline_matches_plain_steps():
+    """step(b, next_batch=nb) (H2D of nb on the copy stream while b computes) == the same steps without prefetch."""
+    args = synth.tan_args(loss_threshold=0.0, use_alignability_head=0)
+    batches = [synth.tan_batch(B=B, T=T, N=N, d_video=DIN, d_text=DIN, seed=300 + i) for i in range(4)]
+    for b in batches:
+        for k in ("video", "text", "video_padding_mask", "text_padding_mask"):
+            b[k] = b[k].pin_memory()
+    runs = []
+    for prefetch in (False, True):
+        m = _model(torch.bfloat16)
+        m.random_pos_start = 0
+        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, use_graph=True)
+        tr.load_batch(batches[0])
+        tr.prepare()
+        out = []
+        for i, b in enumerate(batches):
+            nb = batches[i + 1] if (prefetch and i + 1 < len(batches)) else None
+            out.append(tr.step(b, next_batch=nb))
+        runs.append(out)
+    # fp32 atomics (NCE sums, split-K reduce-add) make the last bits order-dependent
+    assert np.allclose(runs[0], runs[1], rtol=1e-5), runs
+    assert len(set(runs[0])) == len(batches)          # the batches really differ
