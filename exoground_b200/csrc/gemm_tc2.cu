@@ -448,10 +448,16 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.splits = 1;
   if (q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && tiles * 2 <= exg_num_sms() &&
       kblocks >= 8) {
-    int want = (int)((exg_num_sms() + tiles - 1) / tiles);
-    int maxs = kblocks / 4;
-    a.splits = want < maxs ? want : maxs;
-    if (a.splits < 1) a.splits = 1;
+    // pick the split count with the shortest critical path: rounds x (k-blocks per item + fixed per-item cost)
+    const int maxs = kblocks / 4 < 64 ? kblocks / 4 : 64;
+    double best = 1e30;
+    for (int sp = 1; sp <= maxs; ++sp) {
+      const long kb = (kblocks + sp - 1) / sp;
+      const long items = tiles * ((kblocks + kb - 1) / kb);
+      const long rounds = (items + exg_num_sms() - 1) / exg_num_sms();
+      const double cost = (double)rounds * ((double)kb + 6.0);
+      if (cost < best - 1e-9) { best = cost; a.splits = sp; }
+    }
   }
   a.kblocks_per_split = (kblocks + a.splits - 1) / a.splits;
   a.splits = (kblocks + a.kblocks_per_split - 1) / a.kblocks_per_split;

@@ -278,18 +278,34 @@ l2n_bwd_kernel(const void* __restrict__ dy, int dyd, const void* __restrict__ y,
   }
 }
 
-// out[n] += sum over a slab of rows.  blockDim = (32, 8): x = 4-column group, y = row lane.
-__global__ void colsum_kernel(const void* __restrict__ x, int xd, long M, long N, long ldx,
-                              float* __restrict__ out, long rows_per_block) {
+// out[n] += sum over a slab of rows (optionally weighted per row).  blockDim = (32, 8): x = 4-column group,
+// y = row lane; 4 independent row loads in flight per thread.
+__global__ void colsum_kernel(const void* __restrict__ x, int xd, const float* __restrict__ roww, long M, long N,
+                              long ldx, float* __restrict__ out, long rows_per_block) {
   __shared__ float4 sm[8][32];
   const long col = ((long)blockIdx.x * 32 + threadIdx.x) * 4;
   const long r0 = (long)blockIdx.y * rows_per_block;
   const long r1 = min(M, r0 + rows_per_block);
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (col < N) {
-    for (long r = r0 + threadIdx.y; r < r1; r += 8) {
-      float4 v = load4(x, xd, r * ldx + col);
-      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    long r = r0 + threadIdx.y;
+    for (; r + 24 < r1; r += 32) {
+      float4 v[4];
+      float w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        v[u] = load4(x, xd, (r + 8 * u) * ldx + col);
+        w[u] = roww ? roww[r + 8 * u] : 1.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        acc.x += v[u].x * w[u]; acc.y += v[u].y * w[u]; acc.z += v[u].z * w[u]; acc.w += v[u].w * w[u];
+      }
+    }
+    for (; r < r1; r += 8) {
+      const float4 v = load4(x, xd, r * ldx + col);
+      const float w = roww ? roww[r] : 1.f;
+      acc.x += v.x * w; acc.y += v.y * w; acc.z += v.z * w; acc.w += v.w * w;
     }
   }
   sm[threadIdx.y][threadIdx.x] = acc;
@@ -302,6 +318,35 @@ __global__ void colsum_kernel(const void* __restrict__ x, int xd, long M, long N
     }
     atomicAdd(out + col, acc.x); atomicAdd(out + col + 1, acc.y);
     atomicAdd(out + col + 2, acc.z); atomicAdd(out + col + 3, acc.w);
+  }
+}
+
+// y[r] = <x[r, :], w> (+ bias[0]): one warp per row (Linear with one output: the alignability head, tan_model.py:64-68)
+__global__ void rowdot_kernel(const void* __restrict__ x, int xd, const float* __restrict__ w,
+                              const float* __restrict__ bias, float* __restrict__ y, long rows, int C) {
+  const int lane = threadIdx.x & 31;
+  const long row = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= rows) return;
+  float a = 0.f;
+  for (int c = lane * 4; c < C; c += 128) {
+    const float4 v = load4(x, xd, row * C + c);
+    const float4 ww = *reinterpret_cast<const float4*>(w + c);
+    a += v.x * ww.x + v.y * ww.y + v.z * ww.z + v.w * ww.w;
+  }
+  a = warp_sum(a);
+  if (lane == 0) y[row] = a + (bias ? bias[0] : 0.f);
+}
+
+// out[r, :] = g[r] * w   (gradient of rowdot w.r.t. x)
+__global__ void outer_rows_kernel(const float* __restrict__ g, const float* __restrict__ w, void* __restrict__ out,
+                                  int od, long rows, int C) {
+  const long n4 = rows * (C / 4);
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
+    const long r = i / (C / 4);
+    const int c = (int)(i % (C / 4)) * 4;
+    const float s = g[r];
+    const float4 ww = *reinterpret_cast<const float4*>(w + c);
+    store4(out, od, r * C + c, make_float4(s * ww.x, s * ww.y, s * ww.z, s * ww.w));
   }
 }
 
@@ -494,13 +539,14 @@ extern "C" int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y
   return 0;
 }
 
-extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, float* out,
-                          int accumulate, void* stream) {
+static int colsum_impl(const void* x, int x_dtype, const float* roww, long M, long N, long ldx, float* out,
+                       int accumulate, void* stream) {
   EXG_CHECK_ARG(x && out && exg_valid_dtype(x_dtype), "colsum: bad argument");
   EXG_CHECK_ARG(N > 0, "colsum: N must be positive");
   cudaStream_t s = (cudaStream_t)stream;
   ExgProfScope prof(EXG_PC_ROWWISE, (double)M * N * exg_dtype_size(x_dtype), stream);
   if (N % 4 != 0 || ldx % 4 != 0) {
+    EXG_CHECK_ARG(!roww, "wcolsum: N and ldx must be multiples of 4");
     EXG_CHECK_ARG(N <= 65535, "colsum: unaligned N too large");
     colsum_scalar_kernel<<<(unsigned)N, 256, 0, s>>>(x, x_dtype, M, N, ldx, out, accumulate);
     EXG_LAUNCH_CHECK("colsum_scalar");
@@ -515,8 +561,39 @@ extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, 
   if (rows_per_block < 64) rows_per_block = 64;
   splits = (M + rows_per_block - 1) / rows_per_block;
   dim3 grid((unsigned)strips, (unsigned)splits), block(32, 8);
-  colsum_kernel<<<grid, block, 0, s>>>(x, x_dtype, M, N, ldx, out, rows_per_block);
+  colsum_kernel<<<grid, block, 0, s>>>(x, x_dtype, roww, M, N, ldx, out, rows_per_block);
   EXG_LAUNCH_CHECK("colsum");
+  return 0;
+}
+
+extern "C" int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, float* out,
+                          int accumulate, void* stream) {
+  return colsum_impl(x, x_dtype, nullptr, M, N, ldx, out, accumulate, stream);
+}
+
+extern "C" int exg_wcolsum(const void* x, int x_dtype, const float* row_w, long M, long N, long ldx, float* out,
+                           int accumulate, void* stream) {
+  EXG_CHECK_ARG(row_w, "wcolsum: null row weights");
+  return colsum_impl(x, x_dtype, row_w, M, N, ldx, out, accumulate, stream);
+}
+
+extern "C" int exg_rowdot(const void* x, int x_dtype, const float* w, const float* bias, float* y, long rows, int C,
+                          void* stream) {
+  EXG_CHECK_ARG(x && w && y && exg_valid_dtype(x_dtype) && C > 0 && C % 4 == 0, "rowdot: bad argument");
+  if (rows <= 0) return 0;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * exg_dtype_size(x_dtype), stream);
+  rowdot_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, x_dtype, w, bias, y, rows, C);
+  EXG_LAUNCH_CHECK("rowdot");
+  return 0;
+}
+
+extern "C" int exg_outer_rows(const float* g, const float* w, void* out, int out_dtype, long rows, int C,
+                              void* stream) {
+  EXG_CHECK_ARG(g && w && out && exg_valid_dtype(out_dtype) && C > 0 && C % 4 == 0, "outer_rows: bad argument");
+  if (rows <= 0) return 0;
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * exg_dtype_size(out_dtype), stream);
+  outer_rows_kernel<<<grid_for(rows * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(g, w, out, out_dtype, rows, C);
+  EXG_LAUNCH_CHECK("outer_rows");
   return 0;
 }
 

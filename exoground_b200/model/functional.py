@@ -48,6 +48,27 @@ class LinearFn(torch.autograd.Function):
         return dx, dW, None, db, None
 
 
+class RowDotFn(torch.autograd.Function):
+    """y [M] = x @ w[0] + b for a one-output nn.Linear (the alignability head, tan_model.py:64-68,128-134):
+    a GEMM with N = 1 is pure HBM traffic, so forward, dx and dw are row-wise kernels.  x [M,C] in T; fp32 y."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        ctx.saved = (x, w)
+        ctx.has_bias = bias is not None
+        return ops.get().rowdot(x, w.reshape(-1), bias)
+
+    @staticmethod
+    def backward(ctx, dy):
+        K = ops.get()
+        x, w = ctx.saved
+        dy = dy.contiguous().float()
+        dw = K.wcolsum(x, dy).view(1, -1)
+        db = dy.sum().reshape(1) if ctx.has_bias else None
+        dx = K.outer_rows(dy, w.reshape(-1), x.dtype) if ctx.needs_input_grad[0] else None
+        return dx, dw, db
+
+
 class LayerNormFn(torch.autograd.Function):
     """y = LN(x) (* gamma + beta), rows [rows, C]; y in out_dtype; dx returned in x.dtype."""
 

@@ -143,8 +143,7 @@ class TemporalAligner(ExgModule):
         return Fn.AddPosFn.apply(xt, pos, B, N)
 
     def _head(self, x_rows, wT):
-        return Fn.LinearFn.apply(x_rows, self.binary_head.weight, wT("binary_head.weight"), self.binary_head.bias,
-                                 torch.float32)
+        return Fn.RowDotFn.apply(x_rows, self.binary_head.weight, self.binary_head.bias)
 
     # ------------------------------------------------------------------ forward
     def forward(self, video_embed, lang_embed, video_padding_mask, lang_padding_mask, text_timestamp=None,
@@ -181,7 +180,7 @@ class TemporalAligner(ExgModule):
             out['dual_feature_video'] = vn.view(E, B, T, C).permute(1, 0, 2, 3)
             out['dual_feature_text'] = tn.view(B, N, C)
         if self.use_alignability_head:
-            out['dual_logits_alignability'] = self._head(Fn.CastFn.apply(xt, Tc), wT).view(B, N, 1)
+            out['dual_logits_alignability'] = self._head(xt, wT).view(B, N, 1)
             jt = Fn.GatherRowsFn.apply(st_j, D * B * N, (N, T + N, T), Tc)           # joint_text_out rows
             out['joint_logits_alignability'] = self._head(jt, wT).view(D, B, N, 1).permute(1, 0, 2, 3)
         return out
@@ -280,7 +279,7 @@ class TemporalAligner(ExgModule):
         Tc = self.compute_dtype
         D = self.num_decoder_layers
         jt = Fn.GatherRowsFn.apply(st, D * B * N, (N, T + N, T), Tc)
-        dual = self._head(Fn.CastFn.apply(self._text_proj(lang_embed, wT), Tc), wT).view(B, N, 1)
+        dual = self._head(self._text_proj(lang_embed, wT), wT).view(B, N, 1)
         return {'alignability-dual': dual,
                 'alignability-joint': self._head(jt, wT).view(D, B, N, 1).permute(1, 0, 2, 3)}
 

@@ -191,6 +191,33 @@ class CudaBackend:
         L.check(self.lib.exg_colsum(_p(x), _dt(x.dtype), M, N, _rows2d(x), _p(out), int(acc), _stream()), "exg_colsum")
         return out
 
+    def wcolsum(self, x, row_w, out=None):
+        """fp32 [N] = sum_m row_w[m] * x[m, :]; with `out` the sums are ACCUMULATED into it."""
+        _cuda(x, row_w, out)
+        M, N = x.shape
+        acc = out is not None
+        if out is None:
+            out = torch.empty(N, dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_wcolsum(_p(x), _dt(x.dtype), _p(row_w), M, N, _rows2d(x), _p(out), int(acc), _stream()),
+                "exg_wcolsum")
+        return out
+
+    def rowdot(self, x, w, bias=None):
+        """fp32 [rows] = x [rows, C] @ w [C] (+ bias[0]); w, bias fp32."""
+        _cuda(x, w, bias)
+        rows, Cn = x.shape
+        y = torch.empty(rows, dtype=torch.float32, device=x.device)
+        L.check(self.lib.exg_rowdot(_p(x), _dt(x.dtype), _p(w), _p(bias), _p(y), rows, Cn, _stream()), "exg_rowdot")
+        return y
+
+    def outer_rows(self, g, w, out_dtype):
+        """[rows, C] (out_dtype) = g [rows] (fp32) outer w [C] (fp32)."""
+        _cuda(g, w)
+        out = torch.empty((g.numel(), w.numel()), dtype=out_dtype, device=g.device)
+        L.check(self.lib.exg_outer_rows(_p(g), _p(w), _p(out), _dt(out_dtype), g.numel(), w.numel(), _stream()),
+                "exg_outer_rows")
+        return out
+
     def cast(self, src, dtype, out=None):
         _cuda(src)
         if out is None:

@@ -53,6 +53,9 @@ _SIGS = {
     "exg_l2norm_bwd": (C.c_int, [vp, C.c_int, vp, C.c_int, vp, vp, C.c_int, RowMap, C.c_int, C.c_long,
                                  C.c_int, vp]),
     "exg_colsum": (C.c_int, [vp, C.c_int, C.c_long, C.c_long, C.c_long, vp, C.c_int, vp]),
+    "exg_wcolsum": (C.c_int, [vp, C.c_int, vp, C.c_long, C.c_long, C.c_long, vp, C.c_int, vp]),
+    "exg_rowdot": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_long, C.c_int, vp]),
+    "exg_outer_rows": (C.c_int, [vp, vp, vp, C.c_int, C.c_long, C.c_int, vp]),
     "exg_cast": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_long, vp]),
     "exg_stage_mean": (C.c_int, [vp, C.c_int, C.c_long, C.c_int, vp, vp, C.c_int, C.c_long, vp]),
     "exg_bcast_rows": (C.c_int, [vp, C.c_float, vp, C.c_int, C.c_long, C.c_int, C.c_long, vp]),

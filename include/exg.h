@@ -131,6 +131,14 @@ int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y_dtype, con
 /* out[n] (+)= sum_m x[m,n]  — bias gradients and broadcast-add gradients */
 int exg_colsum(const void* x, int x_dtype, long M, long N, long ldx, float* out, int accumulate,
                void* stream);
+/* out[n] (+)= sum_m row_w[m] * x[m,n]   (weight gradient of a one-output Linear) ; N, ldx multiples of 4 */
+int exg_wcolsum(const void* x, int x_dtype, const float* row_w, long M, long N, long ldx, float* out,
+                int accumulate, void* stream);
+/* y[r] = <x[r,:], w> (+ bias[0])   (nn.Linear(C, 1): the alignability head, model/tan_model.py:64-68) ; w fp32 [C] */
+int exg_rowdot(const void* x, int x_dtype, const float* w, const float* bias, float* y, long rows, int C,
+               void* stream);
+/* out[r,:] = g[r] * w   (input gradient of exg_rowdot) */
+int exg_outer_rows(const float* g, const float* w, void* out, int out_dtype, long rows, int C, void* stream);
 /* elementwise dtype conversion of n elements (fp32 master weights -> bf16 shadow copies) */
 int exg_cast(const void* src, int src_dtype, void* dst, int dst_dtype, long n, void* stream);
 /* mean over `S` stage slabs: out[r] = (1/S) sum_s x[s*stage_stride + r]   (exo_ground_model.py:153-154) */

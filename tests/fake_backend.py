@@ -138,6 +138,20 @@ class TorchBackend:
             return out
         return x.float().sum(0)
 
+    def wcolsum(self, x, row_w, out=None):
+        r = (x.float() * row_w[:, None]).sum(0)
+        if out is not None:
+            out += r
+            return out
+        return r
+
+    def rowdot(self, x, w, bias=None):
+        y = x.float() @ w.float()
+        return y + bias[0] if bias is not None else y
+
+    def outer_rows(self, g, w, out_dtype):
+        return (g.float()[:, None] * w.float()[None, :]).to(out_dtype)
+
     def cast(self, src, dtype, out=None):
         if out is None:
             return src.to(dtype)

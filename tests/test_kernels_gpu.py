@@ -401,3 +401,19 @@ def test_ground_loss(K, use_cd, M):
     assert torch.equal(stats[3:], rs[3:]), (stats, rs)
     _check(iou, ri, torch.float32, "iou")
     _check(dp, rd, torch.float32, "dpreds")
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_rowdot_outer_wcolsum(K, dt):
+    rows, C = 1037, 512
+    x = _rand((rows, C), dt, 1)
+    w = _rand((C,), torch.float32, 2)
+    b = _rand((1,), torch.float32, 3)
+    _check(K.rowdot(x, w, b), REF.rowdot(x, w, b), torch.float32, "rowdot", scale=math.sqrt(C))
+    _check(K.rowdot(x, w), REF.rowdot(x, w), torch.float32, "rowdot nobias", scale=math.sqrt(C))
+    g = _rand((rows,), torch.float32, 4)
+    _check(K.outer_rows(g, w, dt), REF.outer_rows(g, w, dt), dt, "outer_rows")
+    _check(K.wcolsum(x, g), REF.wcolsum(x, g), torch.float32, "wcolsum", scale=math.sqrt(rows))
+    acc = _rand((C,), torch.float32, 5)
+    acc2 = acc.clone()
+    _check(K.wcolsum(x, g, out=acc), REF.wcolsum(x, g, out=acc2), torch.float32, "wcolsum acc", scale=math.sqrt(rows))
