@@ -77,49 +77,67 @@ ln_fwd_kernel(const void* __restrict__ x, int xd, const float* __restrict__ gamm
 constexpr int kLnBwdThreads = 256;  // 8 warps
 
 template <int NCH>
-__global__ void __launch_bounds__(kLnBwdThreads)
+__global__ void __launch_bounds__(kLnBwdThreads, 2)
 ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* __restrict__ dy2, int d2,
               exg_rowmap m2, const void* __restrict__ x, int xd, const float* __restrict__ gamma,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
               const float* __restrict__ dres, float* __restrict__ dx, void* __restrict__ dxT, int dxTd,
               float* __restrict__ dgamma, float* __restrict__ dbeta, long rows, int C, float eps) {
+  // One warp per row, software-pipelined: the loads of the warp's next row (x, dy, residual gradient) are issued
+  // before the reductions of the current one, so every warp keeps two rows of HBM traffic in flight.  The
+  // dgamma / dbeta column partials live in this warp's slice of shared memory (conflict-free float4 RMW), which
+  // is what leaves the registers for the prefetch.
   extern __shared__ float red[];  // [warps][2*C]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nwarps = blockDim.x / 32;
-  float4 ag[NCH], ab[NCH];
-#pragma unroll
-  for (int j = 0; j < NCH; ++j) ag[j] = ab[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-  float4 g[NCH];
-#pragma unroll
-  for (int j = 0; j < NCH; ++j) {
-    int col = (j * 32 + lane) * 4;
-    g[j] = col < C ? *reinterpret_cast<const float4*>(gamma + col) : make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  for (long row = (long)blockIdx.x * nwarps + warp; row < rows; row += (long)gridDim.x * nwarps) {
-    float4 xv[NCH], dv[NCH];
-    const long r1 = exg_map_row(m1, row);
-    const long r2 = dy2 ? exg_map_row(m2, row) : 0;
-    float s = 0.f;
+  const bool want_cols = dgamma || dbeta;
+  float* rg = red + (size_t)warp * 2 * C;
+  if (want_cols) {
 #pragma unroll
     for (int j = 0; j < NCH; ++j) {
-      int col = (j * 32 + lane) * 4;
+      const int col = (j * 32 + lane) * 4;
       if (col < C) {
-        xv[j] = load4(x, xd, row * C + col);
-        dv[j] = load4(dy1, d1, r1 * C + col);
-        if (dy2) {
-          float4 t = load4(dy2, d2, r2 * C + col);
-          dv[j].x += t.x; dv[j].y += t.y; dv[j].z += t.z; dv[j].w += t.w;
-        }
-        s += xv[j].x + xv[j].y + xv[j].z + xv[j].w;
-      } else {
-        xv[j] = dv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(rg + col) = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(rg + C + col) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
+  }
+  const long stride = (long)gridDim.x * nwarps;
+  long row = (long)blockIdx.x * nwarps + warp;
+  float4 nx[NCH], nd[NCH], nr[NCH];
+  auto fetch = [&](long r) {
+    const long r1 = exg_map_row(m1, r);
+    const long r2 = dy2 ? exg_map_row(m2, r) : 0;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+      const int col = (j * 32 + lane) * 4;
+      if (col < C) {
+        nx[j] = load4(x, xd, r * C + col);
+        nd[j] = load4(dy1, d1, r1 * C + col);
+        if (dy2) {
+          const float4 t = load4(dy2, d2, r2 * C + col);
+          nd[j].x += t.x; nd[j].y += t.y; nd[j].z += t.z; nd[j].w += t.w;
+        }
+        nr[j] = dres ? *reinterpret_cast<const float4*>(dres + r * C + col) : make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        nx[j] = nd[j] = nr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  };
+  if (row < rows) fetch(row);
+  for (; row < rows; row += stride) {
+    float4 xv[NCH], dv[NCH], rv[NCH];
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) { xv[j] = nx[j]; dv[j] = nd[j]; rv[j] = nr[j]; }
+    if (row + stride < rows) fetch(row + stride);
     float mean, rstd;
     if (mean_in && rstd_in) {
       mean = mean_in[row];
       rstd = rstd_in[row];
     } else {
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < NCH; ++j) s += xv[j].x + xv[j].y + xv[j].z + xv[j].w;
       mean = warp_sum(s) / (float)C;
       float q = 0.f;
 #pragma unroll
@@ -138,12 +156,17 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
       // xv <- xhat ; accumulate dgamma/dbeta ; dv <- dy*gamma
       xv[j].x = (xv[j].x - mean) * rstd; xv[j].y = (xv[j].y - mean) * rstd;
       xv[j].z = (xv[j].z - mean) * rstd; xv[j].w = (xv[j].w - mean) * rstd;
-      int col = (j * 32 + lane) * 4;
-      if (col >= C) xv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-      ag[j].x += dv[j].x * xv[j].x; ag[j].y += dv[j].y * xv[j].y;
-      ag[j].z += dv[j].z * xv[j].z; ag[j].w += dv[j].w * xv[j].w;
-      ab[j].x += dv[j].x; ab[j].y += dv[j].y; ab[j].z += dv[j].z; ab[j].w += dv[j].w;
-      dv[j].x *= g[j].x; dv[j].y *= g[j].y; dv[j].z *= g[j].z; dv[j].w *= g[j].w;
+      const int col = (j * 32 + lane) * 4;
+      if (col >= C) { xv[j] = make_float4(0.f, 0.f, 0.f, 0.f); continue; }
+      if (want_cols) {
+        float4 a = *reinterpret_cast<float4*>(rg + col), b = *reinterpret_cast<float4*>(rg + C + col);
+        a.x += dv[j].x * xv[j].x; a.y += dv[j].y * xv[j].y; a.z += dv[j].z * xv[j].z; a.w += dv[j].w * xv[j].w;
+        b.x += dv[j].x; b.y += dv[j].y; b.z += dv[j].z; b.w += dv[j].w;
+        *reinterpret_cast<float4*>(rg + col) = a;
+        *reinterpret_cast<float4*>(rg + C + col) = b;
+      }
+      const float4 g = *reinterpret_cast<const float4*>(gamma + col);
+      dv[j].x *= g.x; dv[j].y *= g.y; dv[j].z *= g.z; dv[j].w *= g.w;
       c1 += dv[j].x + dv[j].y + dv[j].z + dv[j].w;
       c2 += dv[j].x * xv[j].x + dv[j].y * xv[j].y + dv[j].z * xv[j].z + dv[j].w * xv[j].w;
     }
@@ -154,30 +177,17 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
       int col = (j * 32 + lane) * 4;
       if (col < C) {
         float4 o;
-        o.x = (dv[j].x - c1 - xv[j].x * c2) * rstd;
-        o.y = (dv[j].y - c1 - xv[j].y * c2) * rstd;
-        o.z = (dv[j].z - c1 - xv[j].z * c2) * rstd;
-        o.w = (dv[j].w - c1 - xv[j].w * c2) * rstd;
-        if (dres) {
-          float4 r = *reinterpret_cast<const float4*>(dres + row * C + col);
-          o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
-        }
+        o.x = (dv[j].x - c1 - xv[j].x * c2) * rstd + rv[j].x;
+        o.y = (dv[j].y - c1 - xv[j].y * c2) * rstd + rv[j].y;
+        o.z = (dv[j].z - c1 - xv[j].z * c2) * rstd + rv[j].z;
+        o.w = (dv[j].w - c1 - xv[j].w * c2) * rstd + rv[j].w;
         if (dx) *reinterpret_cast<float4*>(dx + row * C + col) = o;
         if (dxT) store4(dxT, dxTd, row * C + col, o);
       }
     }
   }
-  if (!dgamma && !dbeta) return;
-  // cross-warp reduction of the per-lane column partials, then one atomic per column per CTA
-  float* rg = red + (size_t)warp * 2 * C;
-#pragma unroll
-  for (int j = 0; j < NCH; ++j) {
-    int col = (j * 32 + lane) * 4;
-    if (col < C) {
-      *reinterpret_cast<float4*>(rg + col) = ag[j];
-      *reinterpret_cast<float4*>(rg + C + col) = ab[j];
-    }
-  }
+  if (!want_cols) return;
+  // cross-warp reduction of the per-warp column partials, then one atomic per column per CTA
   __syncthreads();
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
     float t = 0.f;

@@ -93,7 +93,8 @@ def test_prefetch_pipeline_matches_plain_steps():
     for prefetch in (False, True):
         m = _model(torch.bfloat16)
         m.random_pos_start = 0
-        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, use_graph=True)
+        # eps raised for the same reason as in test_step_matches_torch_adamw_fp32 (noise-level gradients)
+        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, eps=1e-4, use_graph=True)
         tr.load_batch(batches[0])
         tr.prepare()
         out = []
@@ -101,6 +102,8 @@ def test_prefetch_pipeline_matches_plain_steps():
             nb = batches[i + 1] if (prefetch and i + 1 < len(batches)) else None
             out.append(tr.step(b, next_batch=nb))
         runs.append(out)
-    # fp32 atomics (NCE sums, split-K reduce-add) make the last bits order-dependent
-    assert np.allclose(runs[0], runs[1], rtol=1e-5), runs
-    assert len(set(runs[0])) == len(batches)          # the batches really differ
+    # fp32 atomics (NCE sums, split-K reduce-add, column sums) make the last bits order-dependent and a bf16
+    # rounding flip downstream turns that into ~1e-5..1e-4 on the loss after a few updates (run-to-run, with or
+    # without prefetch: scripts/check_determinism.py); a wrong / stale batch would be off by > 1e-2
+    assert np.allclose(runs[0], runs[1], rtol=2e-3), runs
+    assert min(abs(a - b) for i, a in enumerate(runs[0]) for b in runs[0][i + 1:]) > 1e-2   # the batches really differ
