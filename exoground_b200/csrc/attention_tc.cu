@@ -191,12 +191,18 @@ __global__ void __launch_bounds__(128)
 attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
                    const __grid_constant__ CUtensorMap tmdQ, const __grid_constant__ CUtensorMap tmdK,
-                   const __grid_constant__ CUtensorMap tmdV, const void* __restrict__ o, long ldo, AtcArgs p) {
+                   const __grid_constant__ CUtensorMap tmdV, const void* __restrict__ o, long ldo, AtcArgs p,
+                   int ps_tiles) {
+  // smem: [P][dS][Q][K][V][dO].  P and dS are 128 x 128 (two 64-key blocks) in general; with <= 64 keys only
+  // block 0 is ever written and ps_tiles = 1: the MN-major descriptors of the dV / dK MMAs then read the NEXT tile
+  // as "keys 64..127" (dS for P, Q for dS - valid memory, finite or not), which only produces accumulator rows
+  // >= 64 that the clipped TMA stores never write.  96 KB instead of 128 KB: two CTAs per SM.
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* Qs = smem; uint8_t* Ks = smem + kTile; uint8_t* Vs = smem + 2 * kTile; uint8_t* dOs = smem + 3 * kTile;
-  uint8_t* Ps = smem + 4 * kTile; uint8_t* dSs = smem + 6 * kTile;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * kTile);
+  uint8_t* Ps = smem; uint8_t* dSs = smem + ps_tiles * kTile;
+  uint8_t* Qs = smem + 2 * ps_tiles * kTile; uint8_t* Ks = Qs + kTile; uint8_t* Vs = Qs + 2 * kTile;
+  uint8_t* dOs = Qs + 3 * kTile;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(Qs + 4 * kTile);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
   uint32_t* maskw = tmem_slot + 1;
 
@@ -373,7 +379,8 @@ int seq_map(CUtensorMap* out, const void* base, int B, int S, int cols, long ld)
 bool a16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 constexpr size_t kFwdSmem = 5 * kTile + 1024 + 64;
-constexpr size_t kBwdSmem = 8 * kTile + 1024 + 64;
+constexpr size_t bwd_smem(int ps_tiles) { return (size_t)(4 + 2 * ps_tiles) * kTile + 1024 + 64; }
+constexpr size_t kBwdSmem = bwd_smem(2);
 
 }  // namespace
 
@@ -432,7 +439,9 @@ int exg_attn_tc_bwd(const void* q, const void* k, const void* v, const void* o, 
   }
   AtcArgs a = {B, H, Sq, Sk, scale, key_pad, const_cast<float*>(lse)};
   dim3 grid(1, H, B);
-  attn_tc_bwd_kernel<<<grid, 128, kBwdSmem, (cudaStream_t)stream>>>(mq, mk, mv, mdo, mdq, mdk, mdv, o, ldo, a);
+  const int ps_tiles = Sk <= 64 ? 1 : 2;
+  attn_tc_bwd_kernel<<<grid, 128, bwd_smem(ps_tiles), (cudaStream_t)stream>>>(mq, mk, mv, mdo, mdq, mdk, mdv, o, ldo, a,
+                                                                            ps_tiles);
   EXG_LAUNCH_CHECK("attn_tc_bwd");
   return 0;
 }
