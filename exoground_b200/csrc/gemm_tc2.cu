@@ -7,6 +7,10 @@
 //                                 TMEM lane quarter (= per SM sub-partition) take alternate 64-column chunks, so each
 //                                 scheduler has a second warp to issue from while one waits on TMEM / MUFU / TMA.
 //
+// With NCTA = 2 the kernel runs as clusters of two CTAs on the two SMs of a TPC (cta_group::2): the pair computes a
+// 256 x BN tile, each CTA stages its own 128 rows of A and HALF of the B tile, the leader CTA issues
+// tcgen05.mma.cta_group::2 for both, and each CTA's epilogue drains its own 128 accumulator lanes.  Per SM that is
+// 2/3 of the L2 -> SM operand traffic of two independent 128 x BN tiles, which is what bounds these GEMMs.
 // One CTA per SM loops over output tiles (static round-robin).  The fp32 accumulator is double-buffered in
 // TMEM (2 x BN columns), so the epilogue of tile i overlaps the MMAs of tile i+1, and every global access is a
 // TMA transfer (no per-thread global loads or stores in the kernel).  Operands may be K-major or MN-major in
@@ -36,30 +40,37 @@ struct Tc2Args {
   float alpha;
   int tiles_m, tiles_n, splits, kblocks_per_split, batch;
   int a_bcast, b_bcast;
+  int stages;        // depth of the operand ring (what fits beside the epilogue staging buffers)
   int has_aux_out;
   int has_aux_in;    // QGELU_BWD / RELU_BWD: bf16 aux tile streamed in by TMA, chunk by chunk, by the epilogue warps
 };
 
-template <int BN> struct Cfg2 {
-  static constexpr uint32_t kBBytes = BN * BK * 2;
+constexpr int kMaxStages = 6;
+constexpr uint32_t kMaxSmem = 232448;
+
+template <int BN, int NCTA> struct Cfg2 {
+  static constexpr uint32_t kBBytes = (BN / NCTA) * BK * 2;       // a CTA of a pair stages half of the B tile
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN == 256) ? 3 : 4;
   __host__ __device__ static constexpr uint32_t epi_bytes(int aux_in) { return kEpiWarps * (aux_in ? kAuxBufs : kOutBufs) * kStageBufBytes; }
+  __host__ __device__ static constexpr int stages(int aux_in) {
+    const int n = (int)((kMaxSmem - 1024 - 512 - epi_bytes(aux_in)) / kStageBytes);
+    return n > kMaxStages ? kMaxStages : n;
+  }
   __host__ __device__ static constexpr uint32_t smem_bytes(int aux_in) {
-    return kStages * kStageBytes + epi_bytes(aux_in) + 1024 /*align*/ + 256 /*barriers*/;
+    return stages(aux_in) * kStageBytes + epi_bytes(aux_in) + 1024 /*align*/ + 512 /*barriers*/;
   }
 };
 
 struct TileCoord { int m0, n0, z, kb0, nkb; };
 
-__device__ __forceinline__ TileCoord tile_coord(const Tc2Args& p, int tile, int BN) {
+__device__ __forceinline__ TileCoord tile_coord(const Tc2Args& p, int tile, int BN, int bm_tile, int cta_rank) {
   // order: n fastest, then m, then split, then batch -> CTAs running concurrently share A row blocks in L2
   TileCoord t;
   const int tn = tile % p.tiles_n; tile /= p.tiles_n;
   const int tm = tile % p.tiles_m; tile /= p.tiles_m;
   const int sp = tile % p.splits;
   t.z = tile / p.splits;
-  t.m0 = tm * BM; t.n0 = tn * BN;
+  t.m0 = tm * bm_tile + cta_rank * BM; t.n0 = tn * BN;
   const int kbt = (p.K + BK - 1) / BK;
   t.kb0 = sp * p.kblocks_per_split;
   const int kb1 = min(kbt, t.kb0 + p.kblocks_per_split);
@@ -67,18 +78,21 @@ __device__ __forceinline__ TileCoord tile_coord(const Tc2Args& p, int tile, int 
   return t;
 }
 
-template <int BN>
+template <int BN, int NCTA>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmAux,
                 const __grid_constant__ CUtensorMap tmAuxIn, Tc2Args p) {
-  using C_ = Cfg2<BN>;
+  using C_ = Cfg2<BN, NCTA>;
+  const int cta_rank = NCTA == 2 ? (int)cluster_ctarank() : 0;
+  const int unit = (int)blockIdx.x / NCTA, n_units = (int)gridDim.x / NCTA;     // CTA (pair) index / count
+  const int n_stages = p.stages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* epi_smem = smem + C_::kStages * C_::kStageBytes;
+  uint8_t* epi_smem = smem + (size_t)n_stages * C_::kStageBytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C_::epi_bytes(p.has_aux_in));
-  uint64_t* empty = full + C_::kStages;
-  uint64_t* tmem_full = empty + C_::kStages;     // [2]
+  uint64_t* empty = full + kMaxStages;
+  uint64_t* tmem_full = empty + kMaxStages;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
   uint64_t* aux_bar = tmem_empty + 2;            // [kEpiWarps][2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 2 * kEpiWarps);
@@ -87,8 +101,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits * p.batch;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < C_::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], kEpiWarps); }
+    for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], kEpiWarps * NCTA); }
     for (int s = 0; s < 2 * kEpiWarps; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
@@ -97,59 +111,68 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (p.has_aux_out) tma_prefetch_desc(&tmAux);
     if (p.has_aux_in) tma_prefetch_desc(&tmAuxIn);
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  if (warp == 1) { if (NCTA == 2) tmem_alloc_2sm(tmem_slot, 2 * BN); else tmem_alloc(tmem_slot, 2 * BN); }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();      // the peer's barriers are initialised before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const TileCoord t = tile_coord(p, tile, BN);
+      int s = 0; uint32_t ph = 0;
+      // a pair's loads all signal the LEADER's full barrier, which expects both CTAs' bytes
+      uint32_t full_addr[kMaxStages];
+#pragma unroll
+      for (int i = 0; i < kMaxStages; ++i)
+        full_addr[i] = NCTA == 2 ? mapa_u32(smem_u32(&full[i]), 0) : smem_u32(&full[i]);
+      constexpr int BNL = BN / NCTA;              // B rows staged by this CTA
+      for (int tile = unit; tile < total_tiles; tile += n_units) {
+        const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
         const int za = p.a_bcast ? 0 : t.z, zb = p.b_bcast ? 0 : t.z;
-        for (int i = 0; i < t.nkb; ++i, ++it) {
-          const int s = it % C_::kStages;
-          const uint32_t ph = (it / C_::kStages) & 1;
+        const int nb0 = t.n0 + cta_rank * BNL;
+        for (int i = 0; i < t.nkb; ++i) {
           mbar_wait(&empty[s], ph ^ 1);
           uint8_t* sa = smem + (size_t)s * C_::kStageBytes;
           uint8_t* sb = sa + kABytes;
           const int k0 = (t.kb0 + i) * BK;
-          mbar_arrive_expect_tx(&full[s], C_::kStageBytes);
+          if (cta_rank == 0) mbar_arrive_expect_tx(&full[s], C_::kStageBytes * NCTA);
+          auto load = [&](void* dst, const CUtensorMap* m, int c0, int c1, int c2) {
+            if (NCTA == 2) tma_load_3d_2sm(dst, m, full_addr[s], c0, c1, c2);
+            else tma_load_3d(dst, m, &full[s], c0, c1, c2);
+          };
           if (!p.a_mn) {
-            tma_load_3d(sa, &tmA, &full[s], k0, t.m0, za);
+            load(sa, &tmA, k0, t.m0, za);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j) tma_load_3d(sa + j * 8192, &tmA, &full[s], t.m0 + j * 64, k0, za);
+            for (int j = 0; j < BM / 64; ++j) load(sa + j * 8192, &tmA, t.m0 + j * 64, k0, za);
           }
           if (!p.b_mn) {
-            tma_load_3d(sb, &tmB, &full[s], k0, t.n0, zb);
+            load(sb, &tmB, k0, nb0, zb);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j) tma_load_3d(sb + j * 8192, &tmB, &full[s], t.n0 + j * 64, k0, zb);
+            for (int j = 0; j < BNL / 64; ++j) load(sb + j * 8192, &tmB, nb0 + j * 64, k0, zb);
           }
+          if (++s == n_stages) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+    // ===================== MMA issuer (the leader CTA of a pair issues for both) =====================
+    if (lane == 0 && cta_rank == 0) {
+      const uint32_t idesc = umma_idesc_bf16(BM * NCTA, BN, p.a_mn, p.b_mn);
       const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
       const uint32_t a_kstep = p.a_mn ? (UK * 128u) : (UK * 2u);
       const uint32_t b_kstep = p.b_mn ? (UK * 128u) : (UK * 2u);
-      uint32_t it = 0, ti = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
-        const TileCoord t = tile_coord(p, tile, BN);
+      int s = 0; uint32_t ph = 0, ti = 0;
+      for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
+        const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
         const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
-        mbar_wait(&tmem_empty[as], aph ^ 1);          // epilogue has drained this accumulator stage
+        mbar_wait(&tmem_empty[as], aph ^ 1);          // every epilogue warp (of both CTAs) has drained this stage
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int i = 0; i < t.nkb; ++i, ++it) {
-          const int s = it % C_::kStages;
-          const uint32_t ph = (it / C_::kStages) & 1;
+        for (int i = 0; i < t.nkb; ++i) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)s * C_::kStageBytes);
@@ -158,11 +181,13 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           for (int k = 0; k < BK / UK; ++k) {
             const uint64_t ad = umma_smem_desc(sa + k * a_kstep, a_lbo, 1024u);
             const uint64_t bd = umma_smem_desc(sb + k * b_kstep, b_lbo, 1024u);
-            umma_bf16(d_tmem, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            if (NCTA == 2) umma_bf16_2sm(d_tmem, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+            else umma_bf16(d_tmem, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty[s]);
+          if (NCTA == 2) umma_commit_2sm(&empty[s], 3); else umma_commit(&empty[s]);
+          if (++s == n_stages) { s = 0; ph ^= 1; }
         }
-        umma_commit(&tmem_full[as]);
+        if (NCTA == 2) umma_commit_2sm(&tmem_full[as], 3); else umma_commit(&tmem_full[as]);
       }
     }
   } else {
@@ -180,13 +205,15 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int c_first = half * cols_per_chunk, c_step = 2 * cols_per_chunk;
     uint64_t* my_aux_bar = aux_bar + 2 * ew;
     uint32_t ci = 0;                              // running chunk index of this warp (aux ring position)
-    if (p.has_aux_in && lane == 0 && (int)blockIdx.x < total_tiles) {
-      const TileCoord t0 = tile_coord(p, blockIdx.x, BN);
+    const uint32_t tmem_empty_addr[2] = {NCTA == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u,
+                                         NCTA == 2 ? mapa_u32(smem_u32(&tmem_empty[1]), 0) : 0u};
+    if (p.has_aux_in && lane == 0 && unit < total_tiles) {
+      const TileCoord t0 = tile_coord(p, unit, BN, BM * NCTA, cta_rank);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
       tma_load_3d(stage + 1 * kStageBufBytes, &tmAuxIn, &my_aux_bar[0], t0.n0 + c_first, t0.m0 + lg * 32, t0.z);
     }
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++ti) {
-      const TileCoord t = tile_coord(p, tile, BN);
+    for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
+      const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
       const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
       mbar_wait(&tmem_full[as], aph);
       tc_fence_after();
@@ -203,9 +230,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           // prefetch the aux chunk after this one (same tile, or first chunk of this CTA's next tile) ...
           if (lane == 0) {
             int nt = tile, nc = c0 + c_step;
-            if (nc >= BN) { nt = tile + gridDim.x; nc = c_first; }
+            if (nc >= BN) { nt = tile + n_units; nc = c_first; }
             if (nt < total_tiles) {
-              const TileCoord tn = tile_coord(p, nt, BN);
+              const TileCoord tn = tile_coord(p, nt, BN, BM * NCTA, cta_rank);
               const uint32_t nb = (ci + 1) & 1;
               mbar_arrive_expect_tx(&my_aux_bar[nb], kStageBufBytes);
               tma_load_3d(stage + (1 + nb) * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
@@ -232,7 +259,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           // all TMEM reads of this tile are done: hand the accumulator stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty[as]);
+          if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
         }
         if (!live) continue;
         // ---- math in the thread = row layout
@@ -325,9 +352,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
+  if (NCTA == 2) cluster_sync_all();      // the peer may still be reading this CTA's smem / signalling its barriers
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 2 * BN);
+    if (NCTA == 2) tmem_dealloc_2sm(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN);
   }
 }
 
@@ -371,22 +399,39 @@ int make_map(CUtensorMap* out, const void* base, int f32, uint64_t inner, uint64
   return 0;
 }
 
-template <int BN>
+template <int BN, int NCTA>
 int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
-            const CUtensorMap& ti, const Tc2Args& a, cudaStream_t s) {
+            const CUtensorMap& ti, Tc2Args a, cudaStream_t s) {
+  using C_ = Cfg2<BN, NCTA>;
   static bool attr_set = false;
-  auto kfn = gemm_tc2_kernel<BN>;
-  const uint32_t smem = Cfg2<BN>::smem_bytes(a.has_aux_in);
-  if (smem > 232448u) { exg_set_error("gemm_tc2: %u bytes of shared memory (BN=%d aux_in=%d)", smem, BN, a.has_aux_in); return EXG_EINVAL; }
+  auto kfn = gemm_tc2_kernel<BN, NCTA>;
+  a.stages = C_::stages(a.has_aux_in);
+  const uint32_t smem = C_::smem_bytes(a.has_aux_in);
+  if (a.stages < 2 || smem > kMaxSmem) {
+    exg_set_error("gemm_tc2: %u bytes of shared memory (BN=%d NCTA=%d aux_in=%d)", smem, BN, NCTA, a.has_aux_in);
+    return EXG_EINVAL;
+  }
   if (!attr_set) {
-    const uint32_t mx = Cfg2<BN>::smem_bytes(1) <= 232448u ? Cfg2<BN>::smem_bytes(1) : Cfg2<BN>::smem_bytes(0);
+    const uint32_t mx = C_::smem_bytes(0) > C_::smem_bytes(1) ? C_::smem_bytes(0) : C_::smem_bytes(1);
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx);
     if (e != cudaSuccess) { exg_set_error("gemm_tc2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
     attr_set = true;
   }
   const long total = (long)a.tiles_m * a.tiles_n * a.splits * a.batch;
-  const int grid = (int)(total < exg_num_sms() ? total : exg_num_sms());
-  kfn<<<grid, kThreads, smem, s>>>(ta, tb, tc, tx, ti, a);
+  const long units = exg_num_sms() / NCTA;
+  const int grid = (int)(total < units ? total : units) * NCTA;
+  if (NCTA == 1) {
+    kfn<<<grid, kThreads, smem, s>>>(ta, tb, tc, tx, ti, a);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = NCTA; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kfn, ta, tb, tc, tx, ti, a);
+    if (e != cudaSuccess) { exg_set_error("gemm_tc2: cluster launch failed: %s", cudaGetErrorString(e)); return (int)e; }
+  }
   EXG_LAUNCH_CHECK("gemm_tc2");
   return 0;
 }
@@ -434,27 +479,46 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.has_aux_in = (q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD) ? 1 : 0;
 
   const int kblocks = (q->K + BK - 1) / BK;
-  const long tm = (q->M + BM - 1) / BM;
-  // tile width: 256 halves the smem traffic per flop; prefer it unless 128 fills the machine much better
-  int bn = 256;
-  {
-    const long t256 = tm * ((q->N + 255) / 256) * q->batch, t128 = tm * ((q->N + 127) / 128) * q->batch;
-    const double e256 = wave_eff(t256), e128 = 0.85 * wave_eff(t128);
-    if (q->N <= 128 || (e128 > e256 && t256 >= exg_num_sms() / 2)) bn = 128;
-    if (a.has_aux_in) bn = 128;      // 3 staging buffers per epilogue warp only fit beside the 4 x 32 KB ring
+  const long tm1 = (q->M + BM - 1) / BM;
+  // tile width: 256 everywhere it exists -- measured (scripts/bench_gemm.py, EXG_GEMM_BN / EXG_GEMM_NCTA sweeps) the
+  // 128-wide tile loses on every shape of the step even where it fills the last wave better: these GEMMs are bound
+  // by L2 -> SM operand bytes (48 KB per k-block for 128 x 256 vs 2 x 32 KB for two 128 x 128 tiles)
+  int bn = q->N <= 128 ? 128 : 256;
+  // CTA pairs (256 x BN tiles over two SMs): two thirds of the operand bytes per flop.  Measured gain: 17 % on long-K
+  // square GEMMs, 5-13 % on plain-epilogue GEMMs of the step; a loss (lock-step of the two epilogues) when the
+  // epilogue carries bias / activation / aux traffic or split-K reduce-adds, so those stay single-CTA.
+  static const int no_pair = getenv("EXG_NO_GEMM_PAIR") ? atoi(getenv("EXG_NO_GEMM_PAIR")) : 0;
+  const bool splittable = q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && kblocks >= 8;
+  int ncta = 1;
+  if (!no_pair && q->M > BM && q->epilogue == EXG_EPI_NONE && !q->bias && !q->aux_out) {
+    const long tn = (q->N + bn - 1) / bn;
+    const long t1 = tm1 * tn * q->batch, t2 = ((q->M + 2 * BM - 1) / (2 * BM)) * tn * q->batch;
+    const long sms = exg_num_sms(), pairs = sms / 2;
+    const double r1 = (double)((t1 + sms - 1) / sms), r2 = (double)((t2 + pairs - 1) / pairs);
+    const bool will_split = splittable && t1 * 2 <= sms;
+    if (!will_split && r2 * 2.0 <= r1 * 3.0 + 1e-9) ncta = 2;
   }
+  if (a.has_aux_in && ncta == 1) bn = 128;   // 3 staging buffers per epilogue warp leave a 128-wide ring 4 stages
+  {  // tuning overrides (scripts/bench_gemm.py)
+    static const int f_bn = getenv("EXG_GEMM_BN") ? atoi(getenv("EXG_GEMM_BN")) : 0;
+    static const int f_ncta = getenv("EXG_GEMM_NCTA") ? atoi(getenv("EXG_GEMM_NCTA")) : 0;
+    if (f_ncta == 1 || (f_ncta == 2 && q->M > BM)) ncta = f_ncta;
+    if ((f_bn == 128 || f_bn == 256) && q->N > 128) bn = f_bn;
+    if (a.has_aux_in && ncta == 1) bn = 128;
+  }
+  const long tm = (q->M + BM * ncta - 1) / (BM * ncta);
   a.tiles_m = (int)tm; a.tiles_n = (q->N + bn - 1) / bn;
   const long tiles = tm * a.tiles_n * q->batch;
+  const long units = exg_num_sms() / ncta;
   a.splits = 1;
-  if (q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && tiles * 2 <= exg_num_sms() &&
-      kblocks >= 8) {
+  if (splittable && tiles * 2 <= units) {
     // pick the split count with the shortest critical path: rounds x (k-blocks per item + fixed per-item cost)
     const int maxs = kblocks / 4 < 64 ? kblocks / 4 : 64;
     double best = 1e30;
     for (int sp = 1; sp <= maxs; ++sp) {
       const long kb = (kblocks + sp - 1) / sp;
       const long items = tiles * ((kblocks + kb - 1) / kb);
-      const long rounds = (items + exg_num_sms() - 1) / exg_num_sms();
+      const long rounds = (items + units - 1) / units;
       const double cost = (double)rounds * ((double)kb + 6.0);
       if (cost < best - 1e-9) { best = cost; a.splits = sp; }
     }
@@ -475,7 +539,7 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   if (!q->transA) rc = make_map(&ta, q->A, 0, q->K, q->M, ba, q->lda, q->strideA, 64, BM);
   else            rc = make_map(&ta, q->A, 0, q->M, q->K, ba, q->lda, q->strideA, 64, BK);
   if (rc) return rc;
-  if (!q->transB) rc = make_map(&tb, q->B, 0, q->K, q->N, bb, q->ldb, q->strideB, 64, bn);
+  if (!q->transB) rc = make_map(&tb, q->B, 0, q->K, q->N, bb, q->ldb, q->strideB, 64, bn / ncta);
   else            rc = make_map(&tb, q->B, 0, q->N, q->K, bb, q->ldb, q->strideB, 64, BK);
   if (rc) return rc;
   rc = make_map(&tc, q->C, a.out_f32, q->N, q->M, q->batch, q->ldc, q->strideC, a.out_f32 ? 32 : 64, 32);
@@ -490,5 +554,6 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
     rc = make_map(&ti, q->aux, 0, q->N, q->M, q->batch, q->ldaux, q->strideAux, 64, 32);
     if (rc) return rc;
   }
-  return bn == 256 ? launch2<256>(ta, tb, tc, tx, ti, a, s) : launch2<128>(ta, tb, tc, tx, ti, a, s);
+  if (ncta == 2) return bn == 256 ? launch2<256, 2>(ta, tb, tc, tx, ti, a, s) : launch2<128, 2>(ta, tb, tc, tx, ti, a, s);
+  return bn == 256 ? launch2<256, 1>(ta, tb, tc, tx, ti, a, s) : launch2<128, 1>(ta, tb, tc, tx, ti, a, s);
 }

@@ -19,7 +19,17 @@ SHAPES = [  # (M, N, K, tA, tB, epilogue, bias, out_f32, tag)
     (8192, 4096, 512, 0, 0, L.EPI_NONE, 0, 0, "sim (1 stage)"),
     (8192, 8192, 8192, 0, 0, L.EPI_NONE, 0, 0, "square 8192"),
 ]
-impls = [("tc", L.GEMM_TC), ("tc2", L.GEMM_TC2)]
+impls = [("tc2", L.GEMM_TC2)]
+SHAPES += [
+    (8192, 2048, 512, 0, 0, L.EPI_QGELU, 1, 0, "c_fc 8192"),
+    (8192, 512, 2048, 0, 0, L.EPI_NONE, 1, 0, "c_proj 8192"),
+    (12288, 512, 2048, 0, 1, L.EPI_NONE, 0, 0, "dh = du @ Wfc"),
+    (12288, 512, 1536, 0, 1, L.EPI_NONE, 0, 0, "dxn = dqkv @ Win"),
+    (512, 2048, 12288, 1, 1, L.EPI_NONE, 0, 1, "dW_proj splitK"),
+    (1536, 512, 12288, 1, 1, L.EPI_NONE, 0, 1, "dW_in splitK"),
+    (12288, 512, 512, 0, 0, L.EPI_NONE, 1, 0, "out_proj 12288"),
+]
+NOCUBLAS = bool(__import__("os").environ.get("NOCUBLAS"))
 for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
     A = torch.randn((Kd, M) if tA else (M, Kd), device="cuda").bfloat16()
     B = torch.randn((Kd, N) if tB else (N, Kd), device="cuda").bfloat16()
@@ -42,6 +52,9 @@ for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
             line += f"{name} {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s | "
         except Exception as ex:
             line += f"{name} ERR {str(ex)[:60]} | "
+    if NOCUBLAS:
+        print(line, flush=True)
+        continue
     a = A.float().t() if tA else A.float()
     torch.matmul(a[:8].bfloat16(), a[:8].bfloat16().t())
     Ab = (A.t() if tA else A).contiguous(); Bb = (B if tB else B.t()).contiguous()
