@@ -287,9 +287,17 @@ def run_ours(a):
         tv = prof[top]
         tensor = top.startswith("gemm") or top.startswith("attn")
         ach = tv["work"] / (tv["ms"] * 1e-3) / (1e12 if tensor else 1e9)
+        traffic, traffic_src = None, None
+        try:      # DRAM bytes per launch of this kernel class from the committed `ncu --set full` capture
+            nt = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))
+            traffic = round(nt[top]["dram_bytes_per_launch"])
+            traffic_src = nt["source"]
+        except Exception:
+            pass
         roof = {"kernel": top, "bound": "tensor" if tensor else "hbm", "achieved": round(ach, 2),
                 "peak": tf_peak if tensor else hbm_peak, "unit": "TFLOP/s" if tensor else "GB/s",
-                "frac": round(ach / (tf_peak if tensor else hbm_peak), 4), "traffic": None, "peak_source": src,
+                "frac": round(ach / (tf_peak if tensor else hbm_peak), 4), "traffic": traffic,
+                "traffic_source": traffic_src, "peak_source": src,
                 "launches": tv["launches"], "avg_launch_ms": round(tv["ms"] / tv["launches"], 5),
                 "how": "sum of algorithmic work / sum of CUDA-event durations of every launch of this kernel "
                        "class in one profiled eager step"}

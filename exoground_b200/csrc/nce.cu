@@ -20,6 +20,7 @@ constexpr int LDB = 8;        // rows whose loads are issued back to back before
 struct NceArgs {
   const void* L; int dtype;
   const uint8_t* tgt; const uint8_t* col_valid;
+  const uint8_t* own_row_mask;   // optional [R]: rows whose OWN-clip block entries count as -inf (loss.py:101-106 in-place fill)
   float *row_all, *row_pos, *col_all, *col_pos;
   const float *wr, *wc;
   void* G; int g_dtype;
@@ -128,7 +129,8 @@ __global__ void __launch_bounds__(NT, 2) nce_fwd_kernel(NceArgs p) {
 #pragma unroll
           for (int j = 0; j < CPT; ++j) {
             if (!cv[j]) continue;
-            const float e = exp2f(fmaf(v[j], k1, -k1));
+            float e = exp2f(fmaf(v[j], k1, -k1));
+            if (own && cb[j] == a && p.own_row_mask && p.own_row_mask[r]) e = 0.f;
             ra[i] += e; ca[j] += e;
             if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) { rp[i] += e; cp[j] += e; }
           }
@@ -227,7 +229,8 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
       const bool own = cb[0] == a || cb[CPT - 1] == a;
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
-        const float e = exp2f(fmaf(v[j], k1, -k1));
+        float e = exp2f(fmaf(v[j], k1, -k1));
+        if (own && cb[j] == a && p.own_row_mask && p.own_row_mask[r]) e = 0.f;
         float coef = ra + ka[j];
         if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) coef -= rp + kp[j];
         g[j] = cv[j] ? e * coef : 0.f;
@@ -250,10 +253,11 @@ __global__ void own_max_kernel(const void* __restrict__ L, int dtype, float* __r
 }
 
 }  // namespace
-int exg_nce_tma_fwd(const void*, int, const uint32_t*, const uint8_t*, float*, float*, float*, float*, int, int, int,
-                    int, float, cudaStream_t);
-int exg_nce_tma_bwd(const void*, int, const uint32_t*, const uint8_t*, const float*, const float*, const float*,
-                    const float*, const float*, const float*, void*, int, int, int, int, int, float, cudaStream_t);
+int exg_nce_tma_fwd(const void*, int, const uint32_t*, const uint8_t*, const uint8_t*, float*, float*, float*, float*,
+                    int, int, int, int, float, cudaStream_t);
+int exg_nce_tma_bwd(const void*, int, const uint32_t*, const uint8_t*, const uint8_t*, const float*, const float*,
+                    const float*, const float*, const float*, const float*, void*, int, int, int, int, int, float,
+                    cudaStream_t);
 namespace {
 
 int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid, int S, int B, int T,
@@ -267,13 +271,14 @@ int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* 
 }  // namespace
 
 extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits,
-                           const uint8_t* col_valid, float* row_all, float* row_pos, float* col_all, float* col_pos, int S, int B, int T,
+                           const uint8_t* col_valid, const uint8_t* own_row_mask, float* row_all, float* row_pos, float* col_all, float* col_pos, int S, int B, int T,
                            int N, float inv_temp, void* stream) {
   int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N);
   if (rc) return rc;
   EXG_CHECK_ARG(row_all && row_pos && col_all && col_pos, "nce_fwd: null output");
   NceArgs a = {};
-  a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid; a.row_all = row_all; a.row_pos = row_pos;
+  a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid; a.own_row_mask = own_row_mask;
+  a.row_all = row_all; a.row_pos = row_pos;
   a.col_all = col_all; a.col_pos = col_pos; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
   const long R = (long)B * T, Cc = (long)B * N;
   cudaStream_t st = (cudaStream_t)stream;
@@ -284,7 +289,7 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
   EXG_CUDA(cudaMemsetAsync(col_pos, 0, (size_t)S * Cc * 4, st));
   dim3 grid((unsigned)((R + FWD_ROWS - 1) / FWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
   ExgProfScope prof(EXG_PC_NCE_FWD, (double)S * R * B * N * exg_dtype_size(dtype), stream);
-  rc = exg_nce_tma_fwd(logits, dtype, tgt_bits, col_valid, row_all, row_pos, col_all, col_pos, S, B, T, N, inv_temp, st);
+  rc = exg_nce_tma_fwd(logits, dtype, tgt_bits, col_valid, own_row_mask, row_all, row_pos, col_all, col_pos, S, B, T, N, inv_temp, st);
   if (rc) return rc == 1 ? 0 : rc;
   nce_fwd_kernel<<<grid, NT, 0, st>>>(a);
   EXG_LAUNCH_CHECK("nce_fwd");
@@ -292,7 +297,7 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
 }
 
 extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits,
-                           const uint8_t* col_valid, const float* row_all, const float* row_pos, const float* col_all,
+                           const uint8_t* col_valid, const uint8_t* own_row_mask, const float* row_all, const float* row_pos, const float* col_all,
                            const float* col_pos, const float* wr, const float* wc, void* G, int g_dtype, int S,
                            int B, int T, int N, float inv_temp, void* stream) {
   int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N);
@@ -300,14 +305,14 @@ extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, co
   EXG_CHECK_ARG(row_all && row_pos && col_all && col_pos && wr && wc && G && exg_valid_dtype(g_dtype),
                 "nce_bwd: bad argument");
   NceArgs a = {};
-  a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid;
+  a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid; a.own_row_mask = own_row_mask;
   a.row_all = const_cast<float*>(row_all); a.row_pos = const_cast<float*>(row_pos);
   a.col_all = const_cast<float*>(col_all); a.col_pos = const_cast<float*>(col_pos);
   a.wr = wr; a.wc = wc; a.G = G; a.g_dtype = g_dtype; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
   const long R = (long)B * T, Cc = (long)B * N;
   dim3 grid((unsigned)((R + BWD_ROWS - 1) / BWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
   ExgProfScope prof(EXG_PC_NCE_BWD, (double)S * R * B * N * (exg_dtype_size(dtype) + exg_dtype_size(g_dtype)), stream);
-  rc = exg_nce_tma_bwd(logits, dtype, tgt_bits, col_valid, row_all, row_pos, col_all, col_pos, wr, wc, G, g_dtype, S, B, T,
+  rc = exg_nce_tma_bwd(logits, dtype, tgt_bits, col_valid, own_row_mask, row_all, row_pos, col_all, col_pos, wr, wc, G, g_dtype, S, B, T,
                        N, inv_temp, (cudaStream_t)stream);
   if (rc) return rc == 1 ? 0 : rc;
   nce_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);

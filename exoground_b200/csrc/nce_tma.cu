@@ -29,7 +29,7 @@ constexpr int STAGE_BYTES = UROWS * WCOLS * 2;          // 4096
 constexpr size_t SMEM_BYTES = (size_t)WARPS * STAGES * STAGE_BYTES + WARPS * STAGES * 8 + 1024;
 
 struct NceT {
-  const uint32_t* bits; const uint8_t* col_valid;   // bits: packed positives [R][W] (exg_nce_pack_targets)
+  const uint32_t* bits; const uint8_t* col_valid; const uint8_t* own_row_mask;   // bits: packed positives [R][W] (exg_nce_pack_targets)
   float *row_all, *row_pos, *col_all, *col_pos;
   const float *wr, *wc;
   int S, B, T, N, W;
@@ -127,6 +127,14 @@ __device__ __forceinline__ uint32_t pos_mask(const NceT& p, long c0, int a, long
   return (run & ((1u << len) - 1u)) << (int)(lo - c0);
 }
 
+// bit j = 1 iff column c0 + j belongs to clip a
+__device__ __forceinline__ uint32_t own_cols(const NceT& p, long c0, int a) {
+  const long base = (long)a * p.N;
+  const long lo = max(c0, base), hi = min(c0 + 8, base + p.N);
+  if (lo >= hi) return 0u;
+  return ((1u << (int)(hi - lo)) - 1u) << (int)(lo - c0);
+}
+
 // Positive masks of the unit's 8 rows (0 when the warp's chunk holds no column of the row's clip); returns whether
 // any row of the unit can have positives in this chunk (warp-uniform).
 __device__ __forceinline__ bool unit_masks(const NceT& p, const ColState& c, int a, int t, int r0, int nrows,
@@ -138,6 +146,9 @@ __device__ __forceinline__ bool unit_masks(const NceT& p, const ColState& c, int
 #pragma unroll
   for (int i = 0; i < UROWS; ++i) {
     m[i] = (i < nrows && ai >= c.wb_lo && ai <= c.wb_hi) ? pos_mask(p, c.c0, ai, (long)r0 + i) : 0u;
+    // bits 8..15: own-clip columns whose entries are dropped on this row (reference's in-place -6e4 fill)
+    if (p.own_row_mask && i < nrows && ai >= c.wb_lo && ai <= c.wb_hi && p.own_row_mask[r0 + i])
+      m[i] |= own_cols(p, c.c0, ai) << 8;
     if (++ti == p.T) { ti = 0; ++ai; }
   }
   return true;
@@ -268,6 +279,10 @@ nce_fwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, NceT p) {
         cvt8(q, v);
 #pragma unroll
         for (int j = 0; j < 8; ++j) e[j] = ex2f(fmaf(v[j], k1, cs.kb[j]));
+        if (unit_own && (m[i] >> 8)) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) if ((m[i] >> (8 + j)) & 1u) e[j] = 0.f;
+        }
         if (i < nrows) {
           ra[i] = ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
 #pragma unroll
@@ -429,6 +444,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               if ((m[i] >> j) & 1u) g[j] = ex2f(fmaf(v[j], k1, cs.kb[j])) * (rA + ka[j] - rP - kp[j]);
+              if ((m[i] >> (8 + j)) & 1u) g[j] = 0.f;
             }
           }
         }
@@ -539,7 +555,8 @@ bool enabled() {
 
 // Both return 1 when the TMA path took the call, 0 when the caller must use the generic kernels, < 0 / a CUDA error
 // code on failure.  Outputs of the forward must have been zeroed by the caller.
-int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const uint8_t* col_valid, float* row_all,
+int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const uint8_t* col_valid,
+                    const uint8_t* own_row_mask, float* row_all,
                     float* row_pos, float* col_all, float* col_pos, int S, int B, int T, int N, float inv_temp,
                     cudaStream_t st) {
   const long R = (long)B * T, Cc = (long)B * N;
@@ -555,7 +572,7 @@ int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const u
     EXG_CUDA(cudaFuncSetAttribute(nce_bwd_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     attr = true;
   }
-  t.bits = bits; t.W = (N + 31) / 32; t.col_valid = col_valid; t.row_all = row_all; t.row_pos = row_pos; t.col_all = col_all;
+  t.bits = bits; t.W = (N + 31) / 32; t.col_valid = col_valid; t.own_row_mask = own_row_mask; t.row_all = row_all; t.row_pos = row_pos; t.col_all = col_all;
   t.col_pos = col_pos; t.S = S; t.B = B; t.T = T; t.N = N; t.inv_temp = inv_temp;
   nce_fwd_tma_kernel<<<grid, NTHREADS, SMEM_BYTES, st>>>(mL, t);
   EXG_LAUNCH_CHECK("nce_fwd_tma");
@@ -563,7 +580,7 @@ int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const u
 }
 
 int exg_nce_tma_bwd(const void* logits, int dtype, const uint32_t* bits, const uint8_t* col_valid,
-                    const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
+                    const uint8_t* own_row_mask, const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
                     const float* wr, const float* wc, void* G, int g_dtype, int S, int B, int T, int N,
                     float inv_temp, cudaStream_t st) {
   const long R = (long)B * T, Cc = (long)B * N;
@@ -579,7 +596,7 @@ int exg_nce_tma_bwd(const void* logits, int dtype, const uint32_t* bits, const u
     EXG_CUDA(cudaFuncSetAttribute(nce_bwd_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
     attr = true;
   }
-  t.bits = bits; t.W = (N + 31) / 32; t.col_valid = col_valid;
+  t.bits = bits; t.W = (N + 31) / 32; t.col_valid = col_valid; t.own_row_mask = own_row_mask;
   t.row_all = const_cast<float*>(row_all); t.row_pos = const_cast<float*>(row_pos);
   t.col_all = const_cast<float*>(col_all); t.col_pos = const_cast<float*>(col_pos);
   t.wr = wr; t.wc = wc; t.S = S; t.B = B; t.T = T; t.N = N; t.inv_temp = inv_temp;

@@ -332,29 +332,32 @@ class CudaBackend:
         L.check(self.lib.exg_nce_pack_targets(_p(tgt), _p(bits), B, T, N, _stream()), "exg_nce_pack_targets")
         return bits
 
-    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None):
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None, own_row_mask=None):
         """logits [S, B*T, B*N] contiguous (T); tgt uint8 [B,N,T]; col_valid uint8 [B*N]; tgt_bits: optional
         nce_pack_targets(tgt) (packed here when omitted).
         Returns fp32 (row_all [S,R], row_pos [S,R], col_all [S,Cc], col_pos [S,Cc]) exp-sums."""
-        _cuda(logits, tgt, col_valid, tgt_bits)
+        _cuda(logits, tgt, col_valid, tgt_bits, own_row_mask)
         if tgt_bits is None:
             tgt_bits = self.nce_pack_targets(tgt)
         S = logits.shape[0]
         rows = torch.empty((2, S, B * T), dtype=torch.float32, device=logits.device)
         cols = torch.zeros((2, S, B * N), dtype=torch.float32, device=logits.device)
-        L.check(self.lib.exg_nce_fwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(tgt_bits), _p(col_valid), _p(rows[0]), _p(rows[1]),
+        L.check(self.lib.exg_nce_fwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(tgt_bits), _p(col_valid), _p(own_row_mask),
+                                     _p(rows[0]), _p(rows[1]),
                                      _p(cols[0]), _p(cols[1]), S, B, T, N, float(inv_temp), _stream()), "exg_nce_fwd")
         return rows[0], rows[1], cols[0], cols[1]
 
-    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None):
+    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None,
+                own_row_mask=None):
         """G [S,R,Cc] = d(sum_r wr*(log row_all-log row_pos) + sum_c wc*(log col_all-log col_pos)) / d logits."""
-        _cuda(logits, tgt, col_valid, wr, wc, tgt_bits)
+        _cuda(logits, tgt, col_valid, wr, wc, tgt_bits, own_row_mask)
         if tgt_bits is None:
             tgt_bits = self.nce_pack_targets(tgt)
         S = logits.shape[0]
         G = torch.empty(logits.shape, dtype=g_dtype or logits.dtype, device=logits.device)
         ra, rp, ca, cp = sums
-        L.check(self.lib.exg_nce_bwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(tgt_bits), _p(col_valid), _p(ra), _p(rp), _p(ca),
+        L.check(self.lib.exg_nce_bwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(tgt_bits), _p(col_valid), _p(own_row_mask),
+                                     _p(ra), _p(rp), _p(ca),
                                      _p(cp), _p(wr), _p(wc), _p(G), _dt(G.dtype), S, B, T, N, float(inv_temp),
                                      _stream()), "exg_nce_bwd")
         return G

@@ -175,16 +175,19 @@ int exg_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
  *   Rows are read with 16-byte loads when B*N is a multiple of 8 (element-wise otherwise).
  * bwd: G[s,r,c] = inv_temp * ( wr[r]*(e/row_all - pos*e/row_pos) + wc[c]*(e/col_all - pos*e/col_pos) )
  *   written in g_dtype; invalid columns get 0.  wr/wc: fp32 per-row / per-column weights (0 = unused).
+ * own_row_mask (optional, uint8 [B*T]): rows r = (a,t) with own_row_mask[r] != 0 drop their OWN-clip block
+ *   (columns (a,k)) from every sum, i.e. those logits count as -inf.  This reproduces the in-place -6e4 fill of the
+ *   padded video seconds that the reference's self-labelling branch leaves in the logits (train/loss.py:100-106).
  * tgt_bits (optional): the same targets packed by exg_nce_pack_targets as [B*T, ceil(N/32)] uint32 rows
  *   (bit n of row (b,t) = tgt[b,n,t]); with it, bf16 logits and B*N % 8 == 0 the calls take the TMA streaming
  *   kernels (nce_tma.cu), otherwise the generic ones.
  */
 int exg_nce_pack_targets(const uint8_t* tgt, uint32_t* tgt_bits, int B, int T, int N, void* stream);
 int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits, const uint8_t* col_valid,
-                float* row_all, float* row_pos, float* col_all, float* col_pos,
+                const uint8_t* own_row_mask, float* row_all, float* row_pos, float* col_all, float* col_pos,
                 int S, int B, int T, int N, float inv_temp, void* stream);
 int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits, const uint8_t* col_valid,
-                const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
+                const uint8_t* own_row_mask, const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
                 const float* wr, const float* wc, void* G, int g_dtype,
                 int S, int B, int T, int N, float inv_temp, void* stream);
 /* own_max[b,k] = max_t L[stage, (b,t), (b,k)]   (train/loss.py:283-286) */

@@ -261,12 +261,16 @@ class TorchBackend:
         dk.copy_((ds.transpose(-1, -2) @ qf).transpose(1, 2).reshape(B * Sk, H * d).to(dk.dtype))
         dv.copy_((p.transpose(-1, -2) @ dof).transpose(1, 2).reshape(B * Sk, H * d).to(dv.dtype))
 
-    def _nce_common(self, logits, tgt, col_valid, B, T, N, inv_temp):
+    def _nce_common(self, logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask=None):
         S = logits.shape[0]
         e = torch.exp(logits.float() * inv_temp - inv_temp)                     # [S,R,Cc]
         valid = col_valid.bool().view(1, 1, B * N)
         e = torch.where(valid, e, torch.zeros_like(e))
         eye = torch.eye(B, dtype=torch.bool, device=logits.device)
+        if own_row_mask is not None:       # own-clip block of the masked rows counts as -inf
+            own = eye[:, None, :, None].expand(B, T, B, N).reshape(B * T, B * N)
+            drop = own & own_row_mask.bool().view(B * T, 1)
+            e = torch.where(drop[None], torch.zeros_like(e), e)
         pos = (tgt.bool().permute(0, 2, 1)[:, :, None, :] & eye[:, None, :, None]).reshape(B * T, B * N)
         pos = pos & col_valid.bool().view(1, B * N)
         return e, pos
@@ -281,13 +285,14 @@ class TorchBackend:
         words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)     # two's complement int32
         return words.permute(0, 2, 1).reshape(B * T, W).to(torch.int32)
 
-    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None):
-        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp)
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None, own_row_mask=None):
+        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask)
         ep = e * pos[None]
         return e.sum(-1), ep.sum(-1), e.sum(-2), ep.sum(-2)
 
-    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None):
-        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp)
+    def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None,
+                own_row_mask=None):
+        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask)
         ra, rp, ca, cp = sums
         safe = lambda w, s: torch.where((w != 0) & (s > 0), w / s.clamp(min=1e-38), torch.zeros_like(s))
         a_r = safe(wr[None, :].expand_as(ra), ra)[..., None]

@@ -285,6 +285,15 @@ def test_nce(K, dt, S, B, T, N):
     Gr = REF.nce_bwd(Lg, tgt, cv, ref, wr, wc, B, T, N, it)
     _check(G, Gr, dt, "nce G")
     _check(K.own_max(Lg, S - 1, B, T, N), REF.own_max(Lg, S - 1, B, T, N), torch.float32, "own_max")
+    # own-clip block of masked rows dropped (the self-labelling branch's in-place -6e4 fill, loss.py:100-106)
+    rm = (torch.rand((B * T,), generator=_g(8)) < 0.3).to(torch.uint8).to(DEV)
+    got = K.nce_fwd(Lg, tgt, cv, B, T, N, it, own_row_mask=rm)
+    ref = REF.nce_fwd(Lg, tgt, cv, B, T, N, it, own_row_mask=rm)
+    for a, r, n in zip(got, ref, ("row_all", "row_pos", "col_all", "col_pos")):
+        _check(a, r, torch.float32, "nce masked " + n)
+    wr2, wc2 = wr * (ref[1][0] > 0), wc * (ref[3][0] > 0)
+    G = K.nce_bwd(Lg, tgt, cv, ref, wr2, wc2, B, T, N, it, own_row_mask=rm)
+    _check(G, REF.nce_bwd(Lg, tgt, cv, ref, wr2, wc2, B, T, N, it, own_row_mask=rm), dt, "nce masked G")
 
 
 # ------------------------------------------------------------------------------------------- optimizer
