@@ -167,15 +167,28 @@ __global__ void __launch_bounds__(NT, 2) nce_fwd_kernel(NceArgs p) {
 
 // Backward: G = inv_temp * e * (wr/row_all + wc/col_all - pos * (wr/row_pos + wc/col_pos)); one streaming pass.
 __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
-  __shared__ float ra_s[BWD_ROWS], rp_s[BWD_ROWS];
+  __shared__ float ra_s[BWD_ROWS], rp_s[BWD_ROWS], rl_s[BWD_ROWS];
+  __shared__ int ncols_s;
   const int s = blockIdx.z;
   const long R = (long)p.B * p.T, Cc = (long)p.B * p.N;
   const long r0 = (long)blockIdx.x * BWD_ROWS;
   const int nrows = (int)min((long)BWD_ROWS, R - r0);
   const size_t base = (size_t)s * R * Cc;
   const float k1 = p.inv_temp * 1.4426950408889634f;
+  // Own-row mask only: positives the mask removed still receive the reference's gradient when NO positive of
+  // their weighted row (column) survives -- its positive LSE then runs over -6e4 fills alone and spreads 1/#entries
+  // over them (loss.py:101-106 fills under no_grad, so autograd treats the filled logits as the originals).
+  if (p.own_row_mask) {
+    if (threadIdx.x == 0) ncols_s = 0;
+    __syncthreads();
+    int n = 0;
+    for (long c = threadIdx.x; c < Cc; c += NT) n += p.col_valid[c] != 0;
+    n = (int)warp_sum((float)n);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(&ncols_s, n);
+    __syncthreads();
+  }
   if (threadIdx.x < BWD_ROWS) {
-    float a = 0.f, b = 0.f;
+    float a = 0.f, b = 0.f, l = 0.f;
     if (threadIdx.x < nrows) {
       const long r = r0 + threadIdx.x;
       const float w = p.wr[r];
@@ -183,26 +196,28 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
         a = w / p.row_all[(size_t)s * R + r];
         const float rp = p.row_pos[(size_t)s * R + r];
         b = rp > 0.f ? w / rp : 0.f;
+        if (p.own_row_mask && !(rp > 0.f)) l = w / (float)ncols_s;
       }
     }
-    ra_s[threadIdx.x] = a * p.inv_temp; rp_s[threadIdx.x] = b * p.inv_temp;
+    ra_s[threadIdx.x] = a * p.inv_temp; rp_s[threadIdx.x] = b * p.inv_temp; rl_s[threadIdx.x] = l * p.inv_temp;
   }
   __syncthreads();
   const long c0 = (long)blockIdx.y * CB + (long)threadIdx.x * CPT;
   if (c0 >= Cc) return;
   const bool vec = (Cc % CPT) == 0;
   const int nvalid = (int)min((long)CPT, Cc - c0);
-  int cb[CPT]; bool cv[CPT]; float ka[CPT], kp[CPT];
+  int cb[CPT]; bool cv[CPT]; float ka[CPT], kp[CPT], kl[CPT];
 #pragma unroll
   for (int j = 0; j < CPT; ++j) {
     cb[j] = j < nvalid ? (int)((c0 + j) / p.N) : -1;
     cv[j] = j < nvalid && p.col_valid[c0 + j] != 0;
     const float w = j < nvalid ? p.wc[c0 + j] : 0.f;
-    ka[j] = kp[j] = 0.f;
+    ka[j] = kp[j] = kl[j] = 0.f;
     if (cv[j] && w != 0.f) {
       ka[j] = p.inv_temp * w / p.col_all[(size_t)s * Cc + c0 + j];
       const float cpv = p.col_pos[(size_t)s * Cc + c0 + j];
       kp[j] = cpv > 0.f ? p.inv_temp * w / cpv : 0.f;
+      if (p.own_row_mask && !(cpv > 0.f)) kl[j] = p.inv_temp * w / (float)R;
     }
   }
   const bool fast = vec && p.dtype == EXG_BF16;
@@ -230,10 +245,14 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
 #pragma unroll
       for (int j = 0; j < CPT; ++j) {
         float e = exp2f(fmaf(v[j], k1, -k1));
-        if (own && cb[j] == a && p.own_row_mask && p.own_row_mask[r]) e = 0.f;
-        float coef = ra + ka[j];
-        if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) coef -= rp + kp[j];
-        g[j] = cv[j] ? e * coef : 0.f;
+        const bool dropped = own && cb[j] == a && p.own_row_mask && p.own_row_mask[r];
+        if (dropped) e = 0.f;
+        float coef = ra + ka[j], leak = 0.f;
+        if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) {
+          coef -= rp + kp[j];
+          if (dropped) leak = rl_s[i] + kl[j];
+        }
+        g[j] = cv[j] ? e * coef - leak : 0.f;
       }
       store8_any(p.G, p.g_dtype, base + (size_t)r * Cc + c0, g, vec, nvalid);
     }

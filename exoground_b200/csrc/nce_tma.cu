@@ -344,6 +344,16 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
   }
   __syncwarp();
   const float k1 = p.inv_temp * 1.4426950408889634f;
+  // leak terms of the own-row mask (see nce.cu nce_bwd_kernel): 1/#valid columns per row, 1/#rows per column
+  float leak_r = 0.f, leak_c = 0.f;
+  if (p.own_row_mask) {
+    int n = 0;
+    for (long c = lane; c < Cc; c += 32) n += p.col_valid[c] != 0;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    leak_r = p.inv_temp / (float)max(n, 1);
+    leak_c = p.inv_temp / (float)R;
+  }
 
   Cursor cur, pre;
   cur.first(vg, VG);
@@ -363,7 +373,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
   pre_item = __shfl_sync(0xffffffffu, pre_item, 0);
 
   ColState cs;
-  float ka[8], kp[8];
+  float ka[8], kp[8], kl[8];
   int cs_cb = -1, cs_s = -1;
   int st = 0; uint32_t ph = 0;
   int a = 0, t = 0;
@@ -373,7 +383,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
       col_setup(cs, p, cur.cb, chunk, lane, Cc, k1);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        ka[j] = kp[j] = 0.f;
+        ka[j] = kp[j] = kl[j] = 0.f;
         const long col = cs.c0 + j;
         if (col < Cc) {
           const float w = p.wc[col];
@@ -382,6 +392,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
             ka[j] = qa > 0.f ? p.inv_temp * w / qa : 0.f;
             const float q = p.col_pos[(size_t)cur.s * Cc + col];
             kp[j] = q > 0.f ? p.inv_temp * w / q : 0.f;
+            kl[j] = q > 0.f ? 0.f : leak_c * w;
           }
         }
       }
@@ -391,7 +402,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
     t = r0 - a * p.T;
     const int nrows = min(UROWS, R - r0);
     // row coefficients of the unit's 8 rows: lane i computes row i, broadcast below
-    float rowA = 0.f, rowP = 0.f;
+    float rowA = 0.f, rowP = 0.f, rowL = 0.f;
     if (lane < nrows) {
       const float w = p.wr[r0 + lane];
       if (w != 0.f) {
@@ -399,6 +410,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
         rowA = qa > 0.f ? p.inv_temp * w / qa : 0.f;
         const float q = p.row_pos[(size_t)cur.s * R + r0 + lane];
         rowP = q > 0.f ? p.inv_temp * w / q : 0.f;
+        rowL = q > 0.f ? 0.f : leak_r * w;
       }
     }
     uint32_t m[8];
@@ -440,11 +452,13 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
         for (int j = 0; j < 8; ++j) g[j] = ex2f(fmaf(v[j], k1, cs.kb[j])) * (rA + ka[j]);
         if (i < nrows && ai >= cs.wb_lo && ai <= cs.wb_hi) {
           const float rP = __shfl_sync(0xffffffffu, rowP, i);
+          const float rL = __shfl_sync(0xffffffffu, rowL, i);
           if (m[i]) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               if ((m[i] >> j) & 1u) g[j] = ex2f(fmaf(v[j], k1, cs.kb[j])) * (rA + ka[j] - rP - kp[j]);
-              if ((m[i] >> (8 + j)) & 1u) g[j] = 0.f;
+              // dropped entry: zero, except a dropped positive of a row / column left without any positive
+              if ((m[i] >> (8 + j)) & 1u) g[j] = ((m[i] >> j) & 1u) && cs.kb[j] != -INFINITY ? -(rL + kl[j]) : 0.f;
             }
           }
         }

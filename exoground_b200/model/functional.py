@@ -222,6 +222,24 @@ class SimLogitsFn(torch.autograd.Function):
         return da, db
 
 
+def nce_value(sums, wr, wc, col_valid=None, inv_temp=0.0, masked=False):
+    """sum_r wr (log row_all - log row_pos) + sum_c wc (log col_all - log col_pos) from the exp-sums.
+    masked=True (self-labelling branch): a weighted row / column whose positives were ALL removed by the own-row
+    mask gets what the reference computes there — its positive LSE is over -6e4 fills only, i.e.
+    -6e4 + log(#entries) (train/loss.py:100-106 + :247-256), so the term is LSE_all + 6e4 - log(#entries)."""
+    ra, rp, ca, cp = sums
+    tiny = 1e-38
+    v = torch.log(ra) - torch.log(rp.clamp(min=tiny))
+    t = torch.log(ca.clamp(min=tiny)) - torch.log(cp.clamp(min=tiny))
+    if masked:
+        n_cols = col_valid.float().sum()
+        n_rows = float(ra.shape[-1])
+        v = torch.where(rp > 0, v, torch.log(ra) + inv_temp + 6e4 - torch.log(n_cols))
+        t = torch.where(cp > 0, t, torch.log(ca.clamp(min=tiny)) + inv_temp + 6e4 - torch.log(torch.tensor(n_rows)))
+    z = torch.zeros((), device=ra.device)
+    return torch.where(wr != 0, v * wr, z).sum() + torch.where(wc != 0, t * wc, z).sum()
+
+
 class NceLossFn(torch.autograd.Function):
     """loss = sum_{s,r} wr[r] (log row_all - log row_pos) + sum_{s,c} wc[c] (log col_all - log col_pos)
     over logits [S,R,Cc]; the exp-sums come from exg_nce_fwd (train/loss.py:251-258), the gradient from
@@ -229,21 +247,18 @@ class NceLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, logits, sums, tgt, col_valid, wr, wc, dims, inv_temp):
-        ra, rp, ca, cp = sums
-        tiny = 1e-38
-        v = torch.log(ra) - torch.log(rp.clamp(min=tiny))
-        t = torch.log(ca.clamp(min=tiny)) - torch.log(cp.clamp(min=tiny))
-        loss = (torch.where(wr != 0, v * wr, torch.zeros_like(v))).sum() + \
-               (torch.where(wc != 0, t * wc, torch.zeros_like(t))).sum()
+        loss = nce_value(sums, wr, wc, col_valid, inv_temp,
+                         masked=isinstance(tgt, tuple) and len(tgt) > 2 and tgt[2] is not None)
         ctx.saved = (logits, sums, tgt, col_valid, wr, wc, dims, inv_temp)
         return loss
 
     @staticmethod
     def backward(ctx, g):
         logits, sums, tgt, col_valid, wr, wc, (B, T, N), inv_temp = ctx.saved
-        tgt, bits = tgt if isinstance(tgt, tuple) else (tgt, None)     # (uint8 mask, nce_pack_targets(mask))
+        # (uint8 mask, nce_pack_targets(mask), optional own-row mask of the self-labelling branch)
+        tgt, bits, orm = (tuple(tgt) + (None, None))[:3] if isinstance(tgt, tuple) else (tgt, None, None)
         G = ops.get().nce_bwd(logits, tgt, col_valid, sums, (wr * g).contiguous(), (wc * g).contiguous(),
-                              B, T, N, inv_temp, tgt_bits=bits)
+                              B, T, N, inv_temp, tgt_bits=bits, own_row_mask=orm)
         return G, None, None, None, None, None, None, None
 
 

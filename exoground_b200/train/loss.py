@@ -12,7 +12,7 @@ import torch.nn.functional as F
 from torch.nn.utils.rnn import pad_sequence
 
 from .. import ops
-from ..model.functional import NceLossFn
+from ..model.functional import NceLossFn, nce_value
 
 INV_TEMP = 1.0 / 0.07      # train/loss.py:68-69 (logits / 0.07 for args.sim == 'cos')
 
@@ -60,15 +60,6 @@ def _stage_major(lg):
     return x.view(S, B * T, B * N)
 
 
-def _nce_value(sums, wr, wc):
-    ra, rp, ca, cp = sums
-    tiny = 1e-38
-    v = torch.log(ra) - torch.log(rp.clamp(min=tiny))
-    t = torch.log(ca.clamp(min=tiny)) - torch.log(cp.clamp(min=tiny))
-    z = torch.zeros((), device=ra.device)
-    return torch.where(wr != 0, v * wr, z).sum() + torch.where(wc != 0, t * wc, z).sum()
-
-
 def _weights(row_mask, col_mask, S):
     """wr/wc such that sum_s,r wr*v + sum_s,c wc*t == (v[:, rows].mean() + t[:, cols].mean()) / 2."""
     rm, cm = row_mask.float(), col_mask.float()
@@ -99,11 +90,8 @@ def get_loss(input_data, video_seq, text_embed, video_padding_mask, text_padding
              abs_text_pos=None):
     """Same contract as reference train/loss.py::get_loss for args.model == 'init'
     (returns the loss dict; 'loss' is differentiable)."""
-    if args.model not in ('init',):
-        raise NotImplementedError("get_loss: only args.model='init' is implemented on the CUDA path "
-                                  "(cotrain / learn_agreement: see exoground_b200.train.agreement)")
-    if getattr(args, 'learn_agreement', 0):
-        raise NotImplementedError("learn_agreement branch not built yet")
+    if args.model not in ('init', 'cotrain'):
+        raise NotImplementedError("get_loss: args.model must be 'init' or 'cotrain'")
     if args.sim != 'cos':
         raise NotImplementedError("only args.sim == 'cos' is supported")
     device = logits['logits_dual'].device
@@ -114,16 +102,35 @@ def get_loss(input_data, video_seq, text_embed, video_padding_mask, text_padding
     else:
         tgt, _, _ = get_mask_from_time(input_data['start'], input_data['end'], num_timestamp=T, num_text=N,
                                        device=device)                               # bool [B,N,T]
-    return loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N)
+    return loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video_padding_mask)
 
 
-def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N):
+def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video_padding_mask=None):
     """Device part of get_loss: everything after the host-built target mask (static shapes, no host sync)."""
     K = ops.get()
     ld, lj = _stage_major(logits['logits_dual']), _stage_major(logits['logits_joint'])
     E, D = ld.shape[0], lj.shape[0]
     loss_dict = {}
     valid = ~text_padding_mask.bool()                                               # [B,N]
+    own_row_mask = None
+    if getattr(args, 'learn_agreement', 0):
+        # self-labelling (loss.py:91-232): targets re-derived from the (EMA) model's own last-stage logits
+        from . import agreement
+        if video_padding_mask is None:
+            raise ValueError("learn_agreement needs video_padding_mask")
+        with torch.no_grad():
+            if args.model == 'cotrain':
+                src_j, src_d = _stage_major(logits['ema-logits_joint']), _stage_major(logits['ema-logits_dual'])
+            else:
+                src_j, src_d = lj, ld
+                # the reference fills the padded seconds / sentences of the own-clip blocks with -6e4 IN PLACE in
+                # the logits it then trains on (loss.py:100-106,157-159); the NCE kernels reproduce that
+                own_row_mask = video_padding_mask.reshape(-1).to(torch.uint8).contiguous()
+            oj = agreement.own_block(src_j.detach(), src_j.shape[0] - 1, B, T, N) * INV_TEMP
+            od = agreement.own_block(src_d.detach(), src_d.shape[0] - 1, B, T, N) * INV_TEMP
+            tgt, stats = agreement.self_label_targets(oj, od, tgt, video_padding_mask, text_padding_mask,
+                                                      args.temporal_agreement_type)
+        loss_dict.update(stats)
     tgt = tgt & valid[:, :, None]
     tgt_u8 = tgt.to(torch.uint8).contiguous()
     col_valid = valid.reshape(-1).to(torch.uint8).contiguous()
@@ -131,9 +138,9 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N):
     colp = tgt.any(dim=2).reshape(-1)                                               # [B*N]
 
     tgt_bits = K.nce_pack_targets(tgt_u8)          # per-(clip, second) bit rows, shared by the 4 NCE launches
-    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits)
-    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits)
-    tgt_u8 = (tgt_u8, tgt_bits)
+    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits, own_row_mask=own_row_mask)
+    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits, own_row_mask=own_row_mask)
+    tgt_u8 = (tgt_u8, tgt_bits, own_row_mask)
     wr_d, wc_d = _weights(rowp, colp, E)
     wr_j, wc_j = _weights(rowp, colp, D)
     use_th = args.loss_threshold > 0
@@ -144,8 +151,8 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N):
         loss_joint = NceLossFn.apply(lj, sums_j, tgt_u8, col_valid, wr_j, wc_j, (B, T, N), INV_TEMP)
     else:
         with torch.no_grad():
-            loss_dual = _nce_value(sums_d, wr_d, wc_d)
-            loss_joint = _nce_value(sums_j, wr_j, wc_j)
+            loss_dual = nce_value(sums_d, wr_d, wc_d, col_valid, INV_TEMP, masked=own_row_mask is not None)
+            loss_joint = nce_value(sums_j, wr_j, wc_j, col_valid, INV_TEMP, masked=own_row_mask is not None)
     loss_dict['loss-dual'] = loss_dual.detach()
     loss_dict['loss-joint'] = loss_joint.detach()
 

@@ -11,12 +11,13 @@ import torch
 
 
 def tan_batch(B=8, T=64, N=32, d_video=4096, d_text=4096, seed=888, zero_pad_text=True,
-              min_video=None, min_text=None, dtype=torch.float32):
+              min_video=None, min_text=None, dtype=torch.float32, annot_inside_video=False):
     """One TAN training batch.
 
     video [B,T,Dv], text [B,N,Dt] ~ N(0,1); video valid length U{T/2..T} (sample 0 full),
     text valid count U{N/2..N} (sample 0 = N, as loss.get_mask_from_time needs max(len)==N,
-    train/loss.py:32-42); start ~ sort U(0,T-8), end = start + U(2,8)."""
+    train/loss.py:32-42); start ~ sort U(0,T-8), end = start + U(2,8); with annot_inside_video the annotations
+    stay inside the un-padded part of each clip (as in real data)."""
     g = torch.Generator().manual_seed(seed)
     rs = np.random.RandomState(seed)
     min_video = T // 2 if min_video is None else min_video
@@ -31,8 +32,11 @@ def tan_batch(B=8, T=64, N=32, d_video=4096, d_text=4096, seed=888, zero_pad_tex
     for b in range(B):
         vmask[b, vlen[b]:] = True
         tmask[b, nlen[b]:] = True
-        s = np.sort(rs.uniform(0, max(T - 8, 1), size=nlen[b])).astype(np.float32)
+        lim = int(vlen[b]) if annot_inside_video else T
+        s = np.sort(rs.uniform(0, max(lim - 8, 1), size=nlen[b])).astype(np.float32)
         e = (s + rs.uniform(2, 8, size=nlen[b])).astype(np.float32)
+        if annot_inside_video:
+            e = np.minimum(e, np.float32(lim))
         start.append([float(x) for x in s]); end.append([float(x) for x in e])
     if zero_pad_text:
         text[tmask] = 0.0

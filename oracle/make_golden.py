@@ -96,6 +96,43 @@ def tan_case(r, name, E, D, B, T, N, d_in, np_seed, losses, sub_logits=None):
     print(name, {k: float(v) for k, v in store.items() if k.endswith("/loss")})
 
 
+def agree_case(r, name, E=2, D=3, B=5, T=16, N=8, d_in=32, np_seed=5):
+    """Self-labelling branch (train/loss.py:91-232): loss dicts of the four temporal_agreement_type modes on an
+    'init' model (the reference's in-place -6e4 fill of the own-clip blocks included), gradients of 'keep', and
+    one 'cotrain' call fed with separate EMA logits."""
+    m = build_tan(r, E, D, d_in, 1)
+    b = synth.tan_batch(B=B, T=T, N=N, d_video=d_in, d_text=d_in, seed=4242, annot_inside_video=True)
+    store = {"meta": np.array([E, D, B, T, N, d_in, np_seed], dtype=np.int64)}
+    inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
+    for mode in ("keep", "i", "u", "keep-joint"):
+        m.zero_grad()
+        np.random.seed(np_seed)
+        out = m(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
+        args = synth.tan_args(learn_agreement=1, temporal_agreement_type=mode)
+        with ref_import.quiet():
+            L = r.loss.get_loss(inp, b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], out,
+                                args, None)
+        _scalars(L, f"loss_{mode}", store)
+        if mode == "keep":
+            L["loss"].backward()
+            _grads(m, store, "grad_keep")
+    # cotrain: targets from EMA logits (here: the same model at another positional offset), loss on the online ones
+    m.zero_grad()
+    np.random.seed(np_seed)
+    out = m(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
+    np.random.seed(np_seed + 1)
+    with torch.no_grad():
+        ema = m(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
+    out["ema-logits_dual"], out["ema-logits_joint"] = ema["logits_dual"], ema["logits_joint"]
+    args = synth.tan_args(model="cotrain", learn_agreement=1, temporal_agreement_type="keep")
+    with ref_import.quiet():
+        L = r.loss.get_loss(inp, b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], out, args,
+                            None)
+    _scalars(L, "loss_cotrain", store)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **store)
+    print(name, {k: float(v) for k, v in store.items() if k.endswith("/loss")})
+
+
 def sim_case(r, name):
     m = build_tan(r, 2, 2, 32, 1)
     m.eval()
@@ -174,6 +211,7 @@ def main():
     tan_case(r, "tan_small", 2, 3, 3, 16, 8, 32, 5,
              [(0.0, 0, 0), (0.3, 0, 0), (0.0, 1, 1), (0.5, 1, 0)])
     sim_case(r, "tan_sim")
+    agree_case(r, "tan_agree")
     exo_case(r, "exo_small")
     tan_case(r, "tan_cfg1", 6, 6, 8, 64, 32, 1024, 888, [(0.0, 0, 0), (0.5, 1, 0)], sub_logits=(8, 4))
 

@@ -300,7 +300,19 @@ class TorchBackend:
         a_c = safe(wc[None, :].expand_as(ca), ca)[:, None, :]
         b_c = safe(wc[None, :].expand_as(cp), cp)[:, None, :]
         coef = a_r + a_c - pos[None].float() * (b_r + b_c)
-        return (inv_temp * e * coef).to(g_dtype or logits.dtype)
+        G = inv_temp * e * coef
+        if own_row_mask is not None:
+            # positives removed by the own-row mask: where ALL positives of a weighted row (column) are gone, the
+            # reference's positive LSE runs over -6e4 fills only and leaks -1/#entries through each of them
+            eye = torch.eye(B, dtype=torch.bool, device=logits.device)
+            own = eye[:, None, :, None].expand(B, T, B, N).reshape(B * T, B * N)
+            mpos = (pos & own & own_row_mask.bool().view(B * T, 1))[None].float()
+            n_cols = col_valid.float().sum()
+            lr_ = torch.where((rp <= 0) & (wr[None, :] != 0), wr[None, :].expand_as(rp) / n_cols, torch.zeros_like(rp))
+            lc_ = torch.where((cp <= 0) & (wc[None, :] != 0), wc[None, :].expand_as(cp) / float(B * T),
+                              torch.zeros_like(cp))
+            G = G - inv_temp * mpos * (lr_[..., None] + lc_[:, None, :])
+        return G.to(g_dtype or logits.dtype)
 
     def own_max(self, logits, stage, B, T, N):
         lg = logits[stage].float().view(B, T, B, N)

@@ -109,3 +109,8 @@ def test_exo_loss_dispatch_and_errors():
     assert any(k.startswith("Rank ") for k in L)
     L["loss"].backward()
     assert m.grounding_head.weight.grad is not None
+
+
+def test_tan_self_labelling_agreement_host_logic(golden_dir):
+    from tests.tan_cases import run_agree_case
+    run_agree_case(_load(golden_dir, "tan_agree"), "cpu", torch.float32)

@@ -294,6 +294,11 @@ def test_nce(K, dt, S, B, T, N):
     wr2, wc2 = wr * (ref[1][0] > 0), wc * (ref[3][0] > 0)
     G = K.nce_bwd(Lg, tgt, cv, ref, wr2, wc2, B, T, N, it, own_row_mask=rm)
     _check(G, REF.nce_bwd(Lg, tgt, cv, ref, wr2, wc2, B, T, N, it, own_row_mask=rm), dt, "nce masked G")
+    # weighted rows / columns whose every positive was dropped: the dropped positives carry -w/#entries
+    G = K.nce_bwd(Lg, tgt, cv, ref, wr, wc, B, T, N, it, own_row_mask=rm)
+    Gr = REF.nce_bwd(Lg, tgt, cv, ref, wr, wc, B, T, N, it, own_row_mask=rm)
+    assert (wr * (ref[1][0] <= 0)).any(), "case does not exercise the leak term"
+    _check(G, Gr, dt, "nce masked leak G")
 
 
 # ------------------------------------------------------------------------------------------- optimizer

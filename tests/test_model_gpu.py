@@ -61,3 +61,9 @@ def test_keystep_small(golden_dir, dt):
 def test_vi_mlp_grads(dt):
     from tests.exo_cases import run_vi_mlp_grad_case
     run_vi_mlp_grad_case("cuda", dt)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_tan_self_labelling_agreement(golden_dir, dt):
+    from tests.tan_cases import run_agree_case
+    run_agree_case(load_golden(golden_dir, "tan_agree"), "cuda", dt)
