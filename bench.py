@@ -153,7 +153,17 @@ def time_cpu(B, steps, warmup, kind_pref="auto"):
             "ms_per_step": sec * 1e3}
 
 
-def workload_config(n_gpus):
+def workload_config(n_gpus, xneg=False, batch=0):
+    global PER_GPU_BATCH
+    if batch:
+        PER_GPU_BATCH = batch
+    cfg = _workload_config(n_gpus)
+    if xneg and n_gpus > 1:
+        cfg["parallelism"] = f"dp{n_gpus} + cross-GPU negatives (text features all-gathered; NCE over the global batch)"
+    return cfg
+
+
+def _workload_config(n_gpus):
     return {"workload": f"TAN E6D6 full train step (fwd + MIL-NCE/alignability loss + bwd + AdamW), T={T}, "
                         f"N={N} sentences, D_in={D_IN}, batch {PER_GPU_BATCH}/GPU (BASELINE.json configs[1])",
             "global_batch": PER_GPU_BATCH * n_gpus, "per_gpu_batch": PER_GPU_BATCH, "seq_len": T,
@@ -198,14 +208,15 @@ def run_ours(a):
         dist.init_process_group("nccl", device_id=torch.device(dev))
         pg = dist.group.WORLD
     assert ops.get().name == "cuda"
-    B = PER_GPU_BATCH
+    B = a.batch or PER_GPU_BATCH
 
     torch.manual_seed(888)
     np.random.seed(888 + rank)
     model = TemporalAligner(E_LAYERS, D_LAYERS, use_alignability_head=1, video_embed_dim=D_IN,
                             text_embed_dim=D_IN, compute_dtype=torch.bfloat16)
     args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
-    tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg)
+    tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg,
+                      cross_gpu_negatives=a.xneg)
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
@@ -306,7 +317,7 @@ def run_ours(a):
         gf = train_gflop_per_clip(B)
         line = {"metric": METRIC, "value": round(value, 1), "unit": "clips/s", "n_gpus": world, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world),
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world, a.xneg, a.batch),
                 "e2e": {"value": round(gb / (ms_e2e * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_e2e, 4),
                         "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last},
                 "gpu_launches": int(launches_per_step * a.steps),
@@ -321,6 +332,8 @@ def run_ours(a):
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
+        del graph
+        tr.close()              # graphs that captured NCCL kernels must go before their communicator
         dist.destroy_process_group()
 
 
@@ -332,6 +345,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--xneg", action="store_true",
+                    help="N > 1: cross-GPU negatives (text features all-gathered, NCE over the global batch; "
+                         "train/xneg.py) instead of the DDP-equivalent local negatives")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: BASELINE configs[1], 128)")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
     if a.impl == "reference":

@@ -25,6 +25,8 @@ struct NceArgs {
   const float *wr, *wc;
   void* G; int g_dtype;
   int S, B, T, N; float inv_temp;
+  int Bc, clip0;   // column clips (== B unless the columns are all-gathered over ranks) and the column clip that
+                   // row clip 0 owns: logits are [S, B*T, Bc*N] and row clip a's positives sit in column clip a + clip0
 };
 
 // 8 consecutive logits of one row as fp32 (16-byte load for bf16, 2 x 16-byte for fp32)
@@ -81,20 +83,21 @@ __device__ __forceinline__ void store8(void* p, int dtype, size_t i, const float
 __global__ void __launch_bounds__(NT, 2) nce_fwd_kernel(NceArgs p) {
   __shared__ float red[NT / 32][2 * SUB];
   const int s = blockIdx.z;
-  const long R = (long)p.B * p.T, Cc = (long)p.B * p.N;
+  const long R = (long)p.B * p.T, Cc = (long)p.Bc * p.N;
   const long rbeg = (long)blockIdx.x * FWD_ROWS;
   const long rend = min(R, rbeg + FWD_ROWS);
   const long c0 = (long)blockIdx.y * CB + (long)threadIdx.x * CPT;
   const size_t base = (size_t)s * R * Cc;
   const float k1 = p.inv_temp * 1.4426950408889634f;
   const bool act = c0 < Cc;
+  const long coff = (long)p.clip0 * p.N;
   const bool vec = (Cc % CPT) == 0;
   const int nvalid = act ? (int)min((long)CPT, Cc - c0) : 0;
   int cb[CPT]; bool cv[CPT];
   float ca[CPT], cp[CPT];
 #pragma unroll
   for (int j = 0; j < CPT; ++j) {
-    cb[j] = j < nvalid ? (int)((c0 + j) / p.N) : -1;
+    cb[j] = j < nvalid ? (int)((c0 + j) / p.N) - p.clip0 : -1 - p.clip0;
     cv[j] = j < nvalid && p.col_valid[c0 + j] != 0;
     ca[j] = cp[j] = 0.f;
   }
@@ -132,7 +135,7 @@ __global__ void __launch_bounds__(NT, 2) nce_fwd_kernel(NceArgs p) {
             float e = exp2f(fmaf(v[j], k1, -k1));
             if (own && cb[j] == a && p.own_row_mask && p.own_row_mask[r]) e = 0.f;
             ra[i] += e; ca[j] += e;
-            if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) { rp[i] += e; cp[j] += e; }
+            if (own && cb[j] == a && p.tgt[((size_t)(c0 + j - coff)) * p.T + t]) { rp[i] += e; cp[j] += e; }
           }
         }
       }
@@ -170,7 +173,7 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
   __shared__ float ra_s[BWD_ROWS], rp_s[BWD_ROWS], rl_s[BWD_ROWS];
   __shared__ int ncols_s;
   const int s = blockIdx.z;
-  const long R = (long)p.B * p.T, Cc = (long)p.B * p.N;
+  const long R = (long)p.B * p.T, Cc = (long)p.Bc * p.N;
   const long r0 = (long)blockIdx.x * BWD_ROWS;
   const int nrows = (int)min((long)BWD_ROWS, R - r0);
   const size_t base = (size_t)s * R * Cc;
@@ -204,12 +207,13 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
   __syncthreads();
   const long c0 = (long)blockIdx.y * CB + (long)threadIdx.x * CPT;
   if (c0 >= Cc) return;
+  const long coff = (long)p.clip0 * p.N;
   const bool vec = (Cc % CPT) == 0;
   const int nvalid = (int)min((long)CPT, Cc - c0);
   int cb[CPT]; bool cv[CPT]; float ka[CPT], kp[CPT], kl[CPT];
 #pragma unroll
   for (int j = 0; j < CPT; ++j) {
-    cb[j] = j < nvalid ? (int)((c0 + j) / p.N) : -1;
+    cb[j] = j < nvalid ? (int)((c0 + j) / p.N) - p.clip0 : -1 - p.clip0;
     cv[j] = j < nvalid && p.col_valid[c0 + j] != 0;
     const float w = j < nvalid ? p.wc[c0 + j] : 0.f;
     ka[j] = kp[j] = kl[j] = 0.f;
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
       ka[j] = p.inv_temp * w / p.col_all[(size_t)s * Cc + c0 + j];
       const float cpv = p.col_pos[(size_t)s * Cc + c0 + j];
       kp[j] = cpv > 0.f ? p.inv_temp * w / cpv : 0.f;
-      if (p.own_row_mask && !(cpv > 0.f)) kl[j] = p.inv_temp * w / (float)R;
+      if (p.own_row_mask && !(cpv > 0.f)) kl[j] = p.inv_temp * w / (float)((long)p.Bc * p.T);
     }
   }
   const bool fast = vec && p.dtype == EXG_BF16;
@@ -248,7 +252,7 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
         const bool dropped = own && cb[j] == a && p.own_row_mask && p.own_row_mask[r];
         if (dropped) e = 0.f;
         float coef = ra + ka[j], leak = 0.f;
-        if (own && cb[j] == a && p.tgt[((size_t)(c0 + j)) * p.T + t]) {
+        if (own && cb[j] == a && p.tgt[((size_t)(c0 + j - coff)) * p.T + t]) {
           coef -= rp + kp[j];
           if (dropped) leak = rl_s[i] + kl[j];
         }
@@ -260,30 +264,31 @@ __global__ void __launch_bounds__(NT) nce_bwd_kernel(NceArgs p) {
 }
 
 __global__ void own_max_kernel(const void* __restrict__ L, int dtype, float* __restrict__ out, int stage,
-                               int B, int T, int N) {
+                               int B, int T, int N, int Bc, int clip0) {
   const int b = blockIdx.x;
-  const long R = (long)B * T, Cc = (long)B * N;
+  const long R = (long)B * T, Cc = (long)Bc * N;
   for (int k = threadIdx.x; k < N; k += blockDim.x) {
     float m = -INFINITY;
     for (int t = 0; t < T; ++t)
-      m = fmaxf(m, load1(L, dtype, (size_t)stage * R * Cc + ((size_t)b * T + t) * Cc + (size_t)b * N + k));
+      m = fmaxf(m, load1(L, dtype, (size_t)stage * R * Cc + ((size_t)b * T + t) * Cc + (size_t)(b + clip0) * N + k));
     out[(size_t)b * N + k] = m;
   }
 }
 
 }  // namespace
 int exg_nce_tma_fwd(const void*, int, const uint32_t*, const uint8_t*, const uint8_t*, float*, float*, float*, float*,
-                    int, int, int, int, float, cudaStream_t);
+                    int, int, int, int, int, int, float, cudaStream_t);
 int exg_nce_tma_bwd(const void*, int, const uint32_t*, const uint8_t*, const uint8_t*, const float*, const float*,
-                    const float*, const float*, const float*, const float*, void*, int, int, int, int, int, float,
-                    cudaStream_t);
+                    const float*, const float*, const float*, const float*, void*, int, int, int, int, int, int, int,
+                    float, cudaStream_t);
 namespace {
 
 int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* col_valid, int S, int B, int T,
-              int N) {
+              int N, int Bc, int clip0) {
   EXG_CHECK_ARG(logits && tgt && col_valid, "nce: null pointer");
   EXG_CHECK_ARG(exg_valid_dtype(dtype), "nce: bad dtype");
   EXG_CHECK_ARG(S > 0 && B > 0 && T > 0 && N > 0 && S <= 65535, "nce: bad sizes");
+  EXG_CHECK_ARG(clip0 >= 0 && clip0 + B <= Bc, "nce: own column block [clip0, clip0 + B) outside the %d column clips", Bc);
   return 0;
 }
 
@@ -291,15 +296,15 @@ int nce_check(const void* logits, int dtype, const uint8_t* tgt, const uint8_t* 
 
 extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits,
                            const uint8_t* col_valid, const uint8_t* own_row_mask, float* row_all, float* row_pos, float* col_all, float* col_pos, int S, int B, int T,
-                           int N, float inv_temp, void* stream) {
-  int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N);
+                           int N, int Bc, int clip0, float inv_temp, void* stream) {
+  int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N, Bc, clip0);
   if (rc) return rc;
   EXG_CHECK_ARG(row_all && row_pos && col_all && col_pos, "nce_fwd: null output");
   NceArgs a = {};
   a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid; a.own_row_mask = own_row_mask;
   a.row_all = row_all; a.row_pos = row_pos;
-  a.col_all = col_all; a.col_pos = col_pos; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
-  const long R = (long)B * T, Cc = (long)B * N;
+  a.col_all = col_all; a.col_pos = col_pos; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp; a.Bc = Bc; a.clip0 = clip0;
+  const long R = (long)B * T, Cc = (long)Bc * N;
   cudaStream_t st = (cudaStream_t)stream;
   // the kernel accumulates with atomics: zero the four outputs here (captured as memset nodes under a graph)
   EXG_CUDA(cudaMemsetAsync(row_all, 0, (size_t)S * R * 4, st));
@@ -307,8 +312,8 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
   EXG_CUDA(cudaMemsetAsync(col_all, 0, (size_t)S * Cc * 4, st));
   EXG_CUDA(cudaMemsetAsync(col_pos, 0, (size_t)S * Cc * 4, st));
   dim3 grid((unsigned)((R + FWD_ROWS - 1) / FWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
-  ExgProfScope prof(EXG_PC_NCE_FWD, (double)S * R * B * N * exg_dtype_size(dtype), stream);
-  rc = exg_nce_tma_fwd(logits, dtype, tgt_bits, col_valid, own_row_mask, row_all, row_pos, col_all, col_pos, S, B, T, N, inv_temp, st);
+  ExgProfScope prof(EXG_PC_NCE_FWD, (double)S * R * Cc * exg_dtype_size(dtype), stream);
+  rc = exg_nce_tma_fwd(logits, dtype, tgt_bits, col_valid, own_row_mask, row_all, row_pos, col_all, col_pos, S, B, T, N, Bc, clip0, inv_temp, st);
   if (rc) return rc == 1 ? 0 : rc;
   nce_fwd_kernel<<<grid, NT, 0, st>>>(a);
   EXG_LAUNCH_CHECK("nce_fwd");
@@ -318,8 +323,8 @@ extern "C" int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, co
 extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits,
                            const uint8_t* col_valid, const uint8_t* own_row_mask, const float* row_all, const float* row_pos, const float* col_all,
                            const float* col_pos, const float* wr, const float* wc, void* G, int g_dtype, int S,
-                           int B, int T, int N, float inv_temp, void* stream) {
-  int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N);
+                           int B, int T, int N, int Bc, int clip0, float inv_temp, void* stream) {
+  int rc = nce_check(logits, dtype, tgt, col_valid, S, B, T, N, Bc, clip0);
   if (rc) return rc;
   EXG_CHECK_ARG(row_all && row_pos && col_all && col_pos && wr && wc && G && exg_valid_dtype(g_dtype),
                 "nce_bwd: bad argument");
@@ -327,12 +332,12 @@ extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, co
   a.L = logits; a.dtype = dtype; a.tgt = tgt; a.col_valid = col_valid; a.own_row_mask = own_row_mask;
   a.row_all = const_cast<float*>(row_all); a.row_pos = const_cast<float*>(row_pos);
   a.col_all = const_cast<float*>(col_all); a.col_pos = const_cast<float*>(col_pos);
-  a.wr = wr; a.wc = wc; a.G = G; a.g_dtype = g_dtype; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp;
-  const long R = (long)B * T, Cc = (long)B * N;
+  a.wr = wr; a.wc = wc; a.G = G; a.g_dtype = g_dtype; a.S = S; a.B = B; a.T = T; a.N = N; a.inv_temp = inv_temp; a.Bc = Bc; a.clip0 = clip0;
+  const long R = (long)B * T, Cc = (long)Bc * N;
   dim3 grid((unsigned)((R + BWD_ROWS - 1) / BWD_ROWS), (unsigned)((Cc + CB - 1) / CB), (unsigned)S);
-  ExgProfScope prof(EXG_PC_NCE_BWD, (double)S * R * B * N * (exg_dtype_size(dtype) + exg_dtype_size(g_dtype)), stream);
+  ExgProfScope prof(EXG_PC_NCE_BWD, (double)S * R * Cc * (exg_dtype_size(dtype) + exg_dtype_size(g_dtype)), stream);
   rc = exg_nce_tma_bwd(logits, dtype, tgt_bits, col_valid, own_row_mask, row_all, row_pos, col_all, col_pos, wr, wc, G, g_dtype, S, B, T,
-                       N, inv_temp, (cudaStream_t)stream);
+                       N, Bc, clip0, inv_temp, (cudaStream_t)stream);
   if (rc) return rc == 1 ? 0 : rc;
   nce_bwd_kernel<<<grid, NT, 0, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("nce_bwd");
@@ -340,11 +345,11 @@ extern "C" int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, co
 }
 
 extern "C" int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B, int T, int N,
-                           void* stream) {
-  EXG_CHECK_ARG(logits && own_max && exg_valid_dtype(dtype) && B > 0 && T > 0 && N > 0 && stage >= 0,
-                "own_max: bad argument");
+                           int Bc, int clip0, void* stream) {
+  EXG_CHECK_ARG(logits && own_max && exg_valid_dtype(dtype) && B > 0 && T > 0 && N > 0 && stage >= 0 &&
+                clip0 >= 0 && clip0 + B <= Bc, "own_max: bad argument");
   ExgProfScope prof(EXG_PC_ROWWISE, (double)B * T * N * exg_dtype_size(dtype), stream);
-  own_max_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(logits, dtype, own_max, stage, B, T, N);
+  own_max_kernel<<<B, 128, 0, (cudaStream_t)stream>>>(logits, dtype, own_max, stage, B, T, N, Bc, clip0);
   EXG_LAUNCH_CHECK("own_max");
   return 0;
 }

@@ -33,6 +33,7 @@ struct NceT {
   float *row_all, *row_pos, *col_all, *col_pos;
   const float *wr, *wc;
   int S, B, T, N, W;
+  int Bc, clip0;        // column clips and the column clip owned by row clip 0 (see nce.cu NceArgs)
   int k, g, ncb;        // chunks per column block, row groups per CTA, column blocks
   float inv_temp;
 };
@@ -110,14 +111,14 @@ __device__ __forceinline__ void col_setup(ColState& c, const NceT& p, int cb, in
     const bool ok = col < Cc && p.col_valid[col] != 0;
     c.kb[j] = ok ? -k1 : -INFINITY;
   }
-  c.wb_lo = (int)(w0 / p.N);
-  c.wb_hi = (int)(min(w0 + WCOLS - 1, Cc - 1) / p.N);
+  c.wb_lo = (int)(w0 / p.N) - p.clip0;               // in row-clip numbering
+  c.wb_hi = (int)(min(w0 + WCOLS - 1, Cc - 1) / p.N) - p.clip0;
 }
 
 // bit j = 1 iff column c0 + j is a positive of (clip a, row r): the lane's 8 columns meet the clip's N columns in
 // one contiguous run, i.e. at most two words of the packed row.
 __device__ __forceinline__ uint32_t pos_mask(const NceT& p, long c0, int a, long r) {
-  const long base = (long)a * p.N;
+  const long base = (long)(a + p.clip0) * p.N;
   const long lo = max(c0, base), hi = min(c0 + 8, base + p.N);
   if (lo >= hi) return 0u;
   const int n_lo = (int)(lo - base), len = (int)(hi - lo), sh = n_lo & 31;
@@ -129,7 +130,7 @@ __device__ __forceinline__ uint32_t pos_mask(const NceT& p, long c0, int a, long
 
 // bit j = 1 iff column c0 + j belongs to clip a
 __device__ __forceinline__ uint32_t own_cols(const NceT& p, long c0, int a) {
-  const long base = (long)a * p.N;
+  const long base = (long)(a + p.clip0) * p.N;
   const long lo = max(c0, base), hi = min(c0 + 8, base + p.N);
   if (lo >= hi) return 0u;
   return ((1u << (int)(hi - lo)) - 1u) << (int)(lo - c0);
@@ -188,7 +189,7 @@ nce_fwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, NceT p) {
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.B * p.T, U = (R + UROWS - 1) / UROWS;
-  const long Cc = (long)p.B * p.N;
+  const long Cc = (long)p.Bc * p.N;
   int chunk, vg, VG;
   const long lo = 0, hi = warp_items(p, warp, U, Cc, chunk, vg, VG);
   if (hi == 0) return;
@@ -331,7 +332,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.B * p.T, U = (R + UROWS - 1) / UROWS;
-  const long Cc = (long)p.B * p.N;
+  const long Cc = (long)p.Bc * p.N;
   int chunk, vg, VG;
   const long lo = 0, hi = warp_items(p, warp, U, Cc, chunk, vg, VG);
   if (hi == 0) return;
@@ -352,7 +353,7 @@ nce_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constan
 #pragma unroll
     for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
     leak_r = p.inv_temp / (float)max(n, 1);
-    leak_c = p.inv_temp / (float)R;
+    leak_c = p.inv_temp / (float)((long)p.Bc * p.T);
   }
 
   Cursor cur, pre;
@@ -545,8 +546,8 @@ int num_sms() {
   return n;
 }
 
-bool plan(NceT& t, int S, int B, int T, int N, unsigned& grid) {
-  const long R = (long)B * T, Cc = (long)B * N;
+bool plan(NceT& t, int S, int B, int T, int N, int Bc, unsigned& grid) {
+  const long R = (long)B * T, Cc = (long)Bc * N;
   if (R >= (1L << 31) - 16 || Cc >= (1L << 31) - 512) return false;
   const int chunks = (int)((Cc + WCOLS - 1) / WCOLS);
   t.ncb = (chunks + WARPS - 1) / WARPS;
@@ -571,13 +572,13 @@ bool enabled() {
 // code on failure.  Outputs of the forward must have been zeroed by the caller.
 int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const uint8_t* col_valid,
                     const uint8_t* own_row_mask, float* row_all,
-                    float* row_pos, float* col_all, float* col_pos, int S, int B, int T, int N, float inv_temp,
-                    cudaStream_t st) {
-  const long R = (long)B * T, Cc = (long)B * N;
+                    float* row_pos, float* col_all, float* col_pos, int S, int B, int T, int N, int Bc, int clip0,
+                    float inv_temp, cudaStream_t st) {
+  const long R = (long)B * T, Cc = (long)Bc * N;
   if (!enabled() || !bits || dtype != EXG_BF16 || Cc % 8 || !a16(logits)) return 0;
   NceT t = {};
   unsigned grid;
-  if (!plan(t, S, B, T, N, grid)) return 0;
+  if (!plan(t, S, B, T, N, Bc, grid)) return 0;
   CUtensorMap mL;
   if (logits_map(&mL, logits, S, R, Cc)) return 0;
   static bool attr = false;
@@ -587,7 +588,7 @@ int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const u
     attr = true;
   }
   t.bits = bits; t.W = (N + 31) / 32; t.col_valid = col_valid; t.own_row_mask = own_row_mask; t.row_all = row_all; t.row_pos = row_pos; t.col_all = col_all;
-  t.col_pos = col_pos; t.S = S; t.B = B; t.T = T; t.N = N; t.inv_temp = inv_temp;
+  t.col_pos = col_pos; t.S = S; t.B = B; t.T = T; t.N = N; t.inv_temp = inv_temp; t.Bc = Bc; t.clip0 = clip0;
   nce_fwd_tma_kernel<<<grid, NTHREADS, SMEM_BYTES, st>>>(mL, t);
   EXG_LAUNCH_CHECK("nce_fwd_tma");
   return 1;
@@ -596,12 +597,12 @@ int exg_nce_tma_fwd(const void* logits, int dtype, const uint32_t* bits, const u
 int exg_nce_tma_bwd(const void* logits, int dtype, const uint32_t* bits, const uint8_t* col_valid,
                     const uint8_t* own_row_mask, const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
                     const float* wr, const float* wc, void* G, int g_dtype, int S, int B, int T, int N,
-                    float inv_temp, cudaStream_t st) {
-  const long R = (long)B * T, Cc = (long)B * N;
+                    int Bc, int clip0, float inv_temp, cudaStream_t st) {
+  const long R = (long)B * T, Cc = (long)Bc * N;
   if (!enabled() || !bits || dtype != EXG_BF16 || g_dtype != EXG_BF16 || Cc % 8 || !a16(logits) || !a16(G)) return 0;
   NceT t = {};
   unsigned grid;
-  if (!plan(t, S, B, T, N, grid)) return 0;
+  if (!plan(t, S, B, T, N, Bc, grid)) return 0;
   CUtensorMap mL, mG;
   if (logits_map(&mL, logits, S, R, Cc) || logits_map(&mG, G, S, R, Cc)) return 0;
   static bool attr = false;
@@ -613,7 +614,7 @@ int exg_nce_tma_bwd(const void* logits, int dtype, const uint32_t* bits, const u
   t.bits = bits; t.W = (N + 31) / 32; t.col_valid = col_valid; t.own_row_mask = own_row_mask;
   t.row_all = const_cast<float*>(row_all); t.row_pos = const_cast<float*>(row_pos);
   t.col_all = const_cast<float*>(col_all); t.col_pos = const_cast<float*>(col_pos);
-  t.wr = wr; t.wc = wc; t.S = S; t.B = B; t.T = T; t.N = N; t.inv_temp = inv_temp;
+  t.wr = wr; t.wc = wc; t.S = S; t.B = B; t.T = T; t.N = N; t.inv_temp = inv_temp; t.Bc = Bc; t.clip0 = clip0;
   nce_bwd_tma_kernel<<<grid, NTHREADS, SMEM_BYTES, st>>>(mL, mG, t);
   EXG_LAUNCH_CHECK("nce_bwd_tma");
   return 1;

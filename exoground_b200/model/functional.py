@@ -222,7 +222,7 @@ class SimLogitsFn(torch.autograd.Function):
         return da, db
 
 
-def nce_value(sums, wr, wc, col_valid=None, inv_temp=0.0, masked=False):
+def nce_value(sums, wr, wc, col_valid=None, inv_temp=0.0, masked=False, n_rows=None):
     """sum_r wr (log row_all - log row_pos) + sum_c wc (log col_all - log col_pos) from the exp-sums.
     masked=True (self-labelling branch): a weighted row / column whose positives were ALL removed by the own-row
     mask gets what the reference computes there — its positive LSE is over -6e4 fills only, i.e.
@@ -233,7 +233,7 @@ def nce_value(sums, wr, wc, col_valid=None, inv_temp=0.0, masked=False):
     t = torch.log(ca.clamp(min=tiny)) - torch.log(cp.clamp(min=tiny))
     if masked:
         n_cols = col_valid.float().sum()
-        n_rows = float(ra.shape[-1])
+        n_rows = float(ra.shape[-1] if n_rows is None else n_rows)    # rows of the GLOBAL logits
         v = torch.where(rp > 0, v, torch.log(ra) + inv_temp + 6e4 - torch.log(n_cols))
         t = torch.where(cp > 0, t, torch.log(ca.clamp(min=tiny)) + inv_temp + 6e4 - torch.log(torch.tensor(n_rows)))
     z = torch.zeros((), device=ra.device)
@@ -246,20 +246,27 @@ class NceLossFn(torch.autograd.Function):
     exg_nce_bwd.  wr / wc already hold the 1/(S*count)/2 factors of the masked means."""
 
     @staticmethod
-    def forward(ctx, logits, sums, tgt, col_valid, wr, wc, dims, inv_temp):
-        loss = nce_value(sums, wr, wc, col_valid, inv_temp,
-                         masked=isinstance(tgt, tuple) and len(tgt) > 2 and tgt[2] is not None)
+    def forward(ctx, logits, sums, tgt, col_valid, wr, wc, dims, inv_temp, own_cols=None):
+        # dims = (B, T, N) or (B, T, N, Bc, clip0).  own_cols (cross-GPU negatives, train/xneg.py): 0/1 over the
+        # global columns; the VALUE counts only this rank's columns (shares add up to the global loss over ranks),
+        # the GRADIENT is that of the global loss with respect to this rank's row block (all columns).
+        T_, N_ = dims[1], dims[2]
+        Bc = dims[3] if len(dims) > 3 else dims[0]
+        loss = nce_value(sums, wr, wc if own_cols is None else wc * own_cols, col_valid, inv_temp,
+                         masked=isinstance(tgt, tuple) and len(tgt) > 2 and tgt[2] is not None, n_rows=Bc * T_)
         ctx.saved = (logits, sums, tgt, col_valid, wr, wc, dims, inv_temp)
         return loss
 
     @staticmethod
     def backward(ctx, g):
-        logits, sums, tgt, col_valid, wr, wc, (B, T, N), inv_temp = ctx.saved
+        logits, sums, tgt, col_valid, wr, wc, dims, inv_temp = ctx.saved
+        B, T, N = dims[:3]
+        Bc, clip0 = (dims[3], dims[4]) if len(dims) > 3 else (B, 0)
         # (uint8 mask, nce_pack_targets(mask), optional own-row mask of the self-labelling branch)
         tgt, bits, orm = (tuple(tgt) + (None, None))[:3] if isinstance(tgt, tuple) else (tgt, None, None)
         G = ops.get().nce_bwd(logits, tgt, col_valid, sums, (wr * g).contiguous(), (wc * g).contiguous(),
-                              B, T, N, inv_temp, tgt_bits=bits, own_row_mask=orm)
-        return G, None, None, None, None, None, None, None
+                              B, T, N, inv_temp, tgt_bits=bits, own_row_mask=orm, Bc=Bc, clip0=clip0)
+        return G, None, None, None, None, None, None, None, None
 
 
 class StageMeanFn(torch.autograd.Function):

@@ -20,6 +20,7 @@ from .. import ops
 from . import functional as Fn
 from .params import ExgModule
 from .tfm_model import TemporalEncoder, get_position_embedding_sine, interp_rows
+from ..train.xneg import gather_rows
 
 C = 512
 
@@ -37,6 +38,7 @@ class TemporalAligner(ExgModule):
         self.sim, self.pos_enc, self.language_model = sim, pos_enc, language_model
         self.use_text_pos_enc = use_text_pos_enc
         self.return_dual_feature = return_dual_feature
+        self.xneg = None          # train.xneg.Group: all-gather the text features for cross-GPU negatives
         self.random_pos_start = random_pos_start
         self.use_alignability_head = use_alignability_head
 
@@ -167,15 +169,18 @@ class TemporalAligner(ExgModule):
         st_v = self._video_stages(xv, B, T, vmask, pv, interpolate_from, wT)       # [E, B*T, C]
         vn = Fn.L2NormFn.apply(st_v, Tc)                                           # [E, B*T, C]
         tn = Fn.L2NormFn.apply(xt, Tc)                                             # [B*N, C]
-        logits_dual = Fn.SimLogitsFn.apply(vn, tn)                                 # [E, B*T, B*N]
+        # cross-GPU negatives (train/xneg.py): columns = the text features of ALL ranks, rows stay local
+        xg = self.xneg if self.xneg is not None and self.xneg.world > 1 else None
+        Bg = B * (xg.world if xg is not None else 1)
+        logits_dual = Fn.SimLogitsFn.apply(vn, gather_rows(tn, xg))                # [E, B*T, Bg*N]
 
         xt_time = self._text_with_time(xt, B, N, pt, interpolate_from) if self.use_text_pos_enc else xt
         st_j = self._joint_stages(xv, xt_time, B, T, N, vmask, tmask, pj, interpolate_from, wT)
         jvn, jtn = Fn.SplitL2NormFn.apply(st_j, B, T, N)                           # [D,B*T,C], [D,B*N,C]
-        logits_joint = Fn.SimLogitsFn.apply(jvn, jtn)                              # [D, B*T, B*N]
+        logits_joint = Fn.SimLogitsFn.apply(jvn, gather_rows(jtn, xg))             # [D, B*T, Bg*N]
 
-        out = {'logits_dual': logits_dual.view(E, B, T, B, N).permute(1, 0, 2, 3, 4),
-               'logits_joint': logits_joint.view(D, B, T, B, N).permute(1, 0, 2, 3, 4)}
+        out = {'logits_dual': logits_dual.view(E, B, T, Bg, N).permute(1, 0, 2, 3, 4),
+               'logits_joint': logits_joint.view(D, B, T, Bg, N).permute(1, 0, 2, 3, 4)}
         if self.return_dual_feature:
             out['dual_feature_video'] = vn.view(E, B, T, C).permute(1, 0, 2, 3)
             out['dual_feature_text'] = tn.view(B, N, C)

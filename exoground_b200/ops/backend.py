@@ -332,23 +332,28 @@ class CudaBackend:
         L.check(self.lib.exg_nce_pack_targets(_p(tgt), _p(bits), B, T, N, _stream()), "exg_nce_pack_targets")
         return bits
 
-    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None, own_row_mask=None):
-        """logits [S, B*T, B*N] contiguous (T); tgt uint8 [B,N,T]; col_valid uint8 [B*N]; tgt_bits: optional
-        nce_pack_targets(tgt) (packed here when omitted).
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None, own_row_mask=None, Bc=None,
+                clip0=0):
+        """logits [S, B*T, Bc*N] contiguous (T); tgt uint8 [B,N,T]; col_valid uint8 [Bc*N]; tgt_bits: optional
+        nce_pack_targets(tgt) (packed here when omitted).  Bc / clip0: column clips and the column clip owned by
+        row clip 0 (cross-GPU negatives: Bc = world * B, clip0 = rank * B; default Bc = B, clip0 = 0).
         Returns fp32 (row_all [S,R], row_pos [S,R], col_all [S,Cc], col_pos [S,Cc]) exp-sums."""
         _cuda(logits, tgt, col_valid, tgt_bits, own_row_mask)
         if tgt_bits is None:
             tgt_bits = self.nce_pack_targets(tgt)
         S = logits.shape[0]
+        Bc = B if Bc is None else Bc
+        assert logits.shape[1] == B * T and logits.shape[2] == Bc * N and col_valid.numel() == Bc * N
         rows = torch.empty((2, S, B * T), dtype=torch.float32, device=logits.device)
-        cols = torch.zeros((2, S, B * N), dtype=torch.float32, device=logits.device)
+        cols = torch.zeros((2, S, Bc * N), dtype=torch.float32, device=logits.device)
         L.check(self.lib.exg_nce_fwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(tgt_bits), _p(col_valid), _p(own_row_mask),
                                      _p(rows[0]), _p(rows[1]),
-                                     _p(cols[0]), _p(cols[1]), S, B, T, N, float(inv_temp), _stream()), "exg_nce_fwd")
+                                     _p(cols[0]), _p(cols[1]), S, B, T, N, Bc, clip0, float(inv_temp), _stream()),
+                "exg_nce_fwd")
         return rows[0], rows[1], cols[0], cols[1]
 
     def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None,
-                own_row_mask=None):
+                own_row_mask=None, Bc=None, clip0=0):
         """G [S,R,Cc] = d(sum_r wr*(log row_all-log row_pos) + sum_c wc*(log col_all-log col_pos)) / d logits."""
         _cuda(logits, tgt, col_valid, wr, wc, tgt_bits, own_row_mask)
         if tgt_bits is None:
@@ -358,14 +363,16 @@ class CudaBackend:
         ra, rp, ca, cp = sums
         L.check(self.lib.exg_nce_bwd(_p(logits), _dt(logits.dtype), _p(tgt), _p(tgt_bits), _p(col_valid), _p(own_row_mask),
                                      _p(ra), _p(rp), _p(ca),
-                                     _p(cp), _p(wr), _p(wc), _p(G), _dt(G.dtype), S, B, T, N, float(inv_temp),
+                                     _p(cp), _p(wr), _p(wc), _p(G), _dt(G.dtype), S, B, T, N, B if Bc is None else Bc,
+                                     clip0, float(inv_temp),
                                      _stream()), "exg_nce_bwd")
         return G
 
-    def own_max(self, logits, stage, B, T, N):
+    def own_max(self, logits, stage, B, T, N, Bc=None, clip0=0):
         _cuda(logits)
         out = torch.empty((B, N), dtype=torch.float32, device=logits.device)
-        L.check(self.lib.exg_own_max(_p(logits), _dt(logits.dtype), _p(out), int(stage), B, T, N, _stream()),
+        L.check(self.lib.exg_own_max(_p(logits), _dt(logits.dtype), _p(out), int(stage), B, T, N,
+                                     B if Bc is None else Bc, clip0, _stream()),
                 "exg_own_max")
         return out
 

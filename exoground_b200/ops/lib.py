@@ -73,10 +73,10 @@ _SIGS = {
                                vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]),
     "exg_nce_pack_targets": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "exg_nce_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
-                              C.c_float, vp]),
-    "exg_nce_bwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int,
                               C.c_int, C.c_int, C.c_float, vp]),
-    "exg_own_max": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "exg_nce_bwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int,
+                              C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]),
+    "exg_own_max": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
     "exg_adamw": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, C.c_float, C.c_float, C.c_float, C.c_float,
                             C.c_float, C.c_int, C.c_float, vp]),
     "exg_ema": (C.c_int, [vp, vp, C.c_long, C.c_float, vp]),

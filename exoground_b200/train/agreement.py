@@ -19,9 +19,9 @@ import torch
 NEG = -6e4
 
 
-def own_block(logits_sm, stage, B, T, N):
-    """[B, T, N] fp32 = logits[stage, (b, t), (b, n)] of stage-major logits [S, B*T, B*N]."""
-    blk = logits_sm[stage].view(B, T, B, N)
+def own_block(logits_sm, stage, B, T, N, clip0=0):
+    """[B, T, N] fp32 = logits[stage, (b, t), (b + clip0, n)] of stage-major logits [S, B*T, Bc*N]."""
+    blk = logits_sm[stage].view(B, T, -1, N)[:, :, clip0:clip0 + B]
     return torch.diagonal(blk, dim1=0, dim2=2).permute(2, 0, 1).float()
 
 

@@ -52,18 +52,22 @@ def get_text_pos(start_list, end_list, device='cuda'):
 
 
 def _stage_major(lg):
-    """[B,S,T,B,N] (any strides) -> contiguous [S, B*T, B*N]; zero-copy for exoground_b200 outputs."""
-    B, S, T, _, N = lg.shape
+    """[B,S,T,Bc,N] (any strides) -> contiguous [S, B*T, Bc*N]; zero-copy for exoground_b200 outputs."""
+    B, S, T, Bc, N = lg.shape
     x = lg.permute(1, 0, 2, 3, 4)
     if not x.is_contiguous():
         x = x.contiguous()
-    return x.view(S, B * T, B * N)
+    return x.view(S, B * T, Bc * N)
 
 
-def _weights(row_mask, col_mask, S):
-    """wr/wc such that sum_s,r wr*v + sum_s,c wc*t == (v[:, rows].mean() + t[:, cols].mean()) / 2."""
+def _weights(row_mask, col_mask, S, grp=None):
+    """wr/wc such that sum_s,r wr*v + sum_s,c wc*t == (v[:, rows].mean() + t[:, cols].mean()) / 2.
+    Cross-GPU negatives: row_mask is this rank's rows (their count is summed over ranks), col_mask is global."""
     rm, cm = row_mask.float(), col_mask.float()
-    return rm / (2.0 * S * rm.sum()), cm / (2.0 * S * cm.sum())
+    n_rows = rm.sum()
+    if grp is not None:
+        n_rows = grp.sum_(n_rows)
+    return rm / (2.0 * S * n_rows), cm / (2.0 * S * cm.sum())
 
 
 def _masked_quantile(x, mask, q):
@@ -105,13 +109,24 @@ def get_loss(input_data, video_seq, text_embed, video_padding_mask, text_padding
     return loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video_padding_mask)
 
 
-def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video_padding_mask=None):
-    """Device part of get_loss: everything after the host-built target mask (static shapes, no host sync)."""
+def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video_padding_mask=None, xneg=None):
+    """Device part of get_loss: everything after the host-built target mask (static shapes, no host sync).
+    xneg (train.xneg.Group, optional): cross-GPU negatives — `logits` are this rank's row blocks [B,S,T,Bg,N] of the
+    global logits; the returned 'loss' is this rank's share (own rows + own columns) of the GLOBAL loss, so the sum
+    over ranks equals the single-process loss on the concatenated batch; the logged entries are already summed."""
     K = ops.get()
+    grp = xneg if xneg is not None and xneg.world > 1 else None
     ld, lj = _stage_major(logits['logits_dual']), _stage_major(logits['logits_joint'])
     E, D = ld.shape[0], lj.shape[0]
+    Bc = ld.shape[2] // N
+    clip0 = grp.rank * B if grp is not None else 0
+    if Bc != (B * grp.world if grp is not None else B):
+        raise ValueError(f"logits cover {Bc} column clips, expected {B} x world size")
+    gather = (lambda x: grp.gather0(x)) if grp is not None else (lambda x: x)
+    shard = dict(Bc=Bc, clip0=clip0)
     loss_dict = {}
     valid = ~text_padding_mask.bool()                                               # [B,N]
+    valid_g = gather(valid)                                                         # [Bc,N]
     own_row_mask = None
     if getattr(args, 'learn_agreement', 0):
         # self-labelling (loss.py:91-232): targets re-derived from the (EMA) model's own last-stage logits
@@ -126,53 +141,68 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video
                 # the reference fills the padded seconds / sentences of the own-clip blocks with -6e4 IN PLACE in
                 # the logits it then trains on (loss.py:100-106,157-159); the NCE kernels reproduce that
                 own_row_mask = video_padding_mask.reshape(-1).to(torch.uint8).contiguous()
-            oj = agreement.own_block(src_j.detach(), src_j.shape[0] - 1, B, T, N) * INV_TEMP
-            od = agreement.own_block(src_d.detach(), src_d.shape[0] - 1, B, T, N) * INV_TEMP
+            oj = agreement.own_block(src_j.detach(), src_j.shape[0] - 1, B, T, N, clip0) * INV_TEMP
+            od = agreement.own_block(src_d.detach(), src_d.shape[0] - 1, B, T, N, clip0) * INV_TEMP
             tgt, stats = agreement.self_label_targets(oj, od, tgt, video_padding_mask, text_padding_mask,
                                                       args.temporal_agreement_type)
         loss_dict.update(stats)
     tgt = tgt & valid[:, :, None]
     tgt_u8 = tgt.to(torch.uint8).contiguous()
-    col_valid = valid.reshape(-1).to(torch.uint8).contiguous()
-    rowp = tgt.any(dim=1).reshape(-1)                                               # [B*T]
-    colp = tgt.any(dim=2).reshape(-1)                                               # [B*N]
+    col_valid = valid_g.reshape(-1).to(torch.uint8).contiguous()
+    rowp = tgt.any(dim=1).reshape(-1)                                               # [B*T]   local rows
+    colp = gather(tgt.any(dim=2)).reshape(-1)                                       # [Bc*N]  global columns
+    # this rank's own columns: the only column terms it counts in its share of the loss value
+    cidx = torch.arange(Bc * N, device=ld.device)
+    own_cols = ((cidx >= clip0 * N) & (cidx < (clip0 + B) * N)).float() if grp is not None else None
 
     tgt_bits = K.nce_pack_targets(tgt_u8)          # per-(clip, second) bit rows, shared by the 4 NCE launches
-    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits, own_row_mask=own_row_mask)
-    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits, own_row_mask=own_row_mask)
+    sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits,
+                       own_row_mask=own_row_mask, **shard)
+    sums_j = K.nce_fwd(lj.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits,
+                       own_row_mask=own_row_mask, **shard)
+    if grp is not None:                            # complete the column exp-sums over the ranks' row blocks
+        for t in (sums_d[2], sums_d[3], sums_j[2], sums_j[3]):
+            grp.sum_(t)
     tgt_u8 = (tgt_u8, tgt_bits, own_row_mask)
-    wr_d, wc_d = _weights(rowp, colp, E)
-    wr_j, wc_j = _weights(rowp, colp, D)
+    wr_d, wc_d = _weights(rowp, colp, E, grp)
+    wr_j, wc_j = _weights(rowp, colp, D, grp)
     use_th = args.loss_threshold > 0
     use_head = bool(args.use_alignability_head)
+    dims = (B, T, N, Bc, clip0)
+
+    def nce(lg, sums, wr, wc):
+        return NceLossFn.apply(lg, sums, tgt_u8, col_valid, wr, wc, dims, INV_TEMP, own_cols)
 
     if not use_th:
-        loss_dual = NceLossFn.apply(ld, sums_d, tgt_u8, col_valid, wr_d, wc_d, (B, T, N), INV_TEMP)
-        loss_joint = NceLossFn.apply(lj, sums_j, tgt_u8, col_valid, wr_j, wc_j, (B, T, N), INV_TEMP)
+        loss_dual = nce(ld, sums_d, wr_d, wc_d)
+        loss_joint = nce(lj, sums_j, wr_j, wc_j)
     else:
         with torch.no_grad():
-            loss_dual = nce_value(sums_d, wr_d, wc_d, col_valid, INV_TEMP, masked=own_row_mask is not None)
-            loss_joint = nce_value(sums_j, wr_j, wc_j, col_valid, INV_TEMP, masked=own_row_mask is not None)
+            mk = dict(masked=own_row_mask is not None, n_rows=Bc * T)
+            ow = (lambda w: w * own_cols) if grp is not None else (lambda w: w)
+            loss_dual = nce_value(sums_d, wr_d, ow(wc_d), col_valid, INV_TEMP, **mk)
+            loss_joint = nce_value(sums_j, wr_j, ow(wc_j), col_valid, INV_TEMP, **mk)
     loss_dict['loss-dual'] = loss_dual.detach()
     loss_dict['loss-joint'] = loss_joint.detach()
 
     if use_th or use_head:
         with torch.no_grad():
-            vflat = valid.reshape(-1)
+            vflat = valid_g.reshape(-1)                                              # global columns
             # the reference indexes per-text vectors compacted over *valid* columns with masks compacted over
             # columns *with positives* (loss.py:298,304,337-347): only consistent when they coincide.
-            md = K.own_max(ld.detach(), E - 1, B, T, N).reshape(-1) * INV_TEMP         # loss.py:283
-            mj = K.own_max(lj.detach(), D - 1, B, T, N).reshape(-1) * INV_TEMP         # loss.py:285
+            md = gather(K.own_max(ld.detach(), E - 1, B, T, N, **shard)).reshape(-1) * INV_TEMP    # loss.py:283
+            mj = gather(K.own_max(lj.detach(), D - 1, B, T, N, **shard)).reshape(-1) * INV_TEMP    # loss.py:285
             metric = -(_masked_standardise(md, vflat) + _masked_standardise(mj, vflat))
             keep = vflat & (metric <= _masked_quantile(metric, vflat, args.loss_threshold))
-            rowp_th = (tgt & keep.view(B, N, 1)).any(dim=1).reshape(-1)
+            keep_loc = keep.view(Bc, N)[clip0:clip0 + B]
+            rowp_th = (tgt & keep_loc.reshape(B, N, 1)).any(dim=1).reshape(-1)
         if use_th:
             loss_dict['loss-dual-all'] = loss_dual.detach()
             loss_dict['loss-joint-all'] = loss_joint.detach()
-            wr_dt, wc_dt = _weights(rowp_th, keep, E)
-            wr_jt, wc_jt = _weights(rowp_th, keep, D)
-            loss_dual_th = NceLossFn.apply(ld, sums_d, tgt_u8, col_valid, wr_dt, wc_dt, (B, T, N), INV_TEMP)
-            loss_joint_th = NceLossFn.apply(lj, sums_j, tgt_u8, col_valid, wr_jt, wc_jt, (B, T, N), INV_TEMP)
+            wr_dt, wc_dt = _weights(rowp_th, keep, E, grp)
+            wr_jt, wc_jt = _weights(rowp_th, keep, D, grp)
+            loss_dual_th = nce(ld, sums_d, wr_dt, wc_dt)
+            loss_joint_th = nce(lj, sums_j, wr_jt, wc_jt)
             loss_dict['loss-dual'] = loss_dual_th.detach()
             loss_dict['loss-joint'] = loss_joint_th.detach()
         if use_head:
@@ -182,18 +212,19 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video
                 lab = torch.where((md > qd) & (mj > qj), torch.ones_like(lab), lab)
                 lab = torch.where((md < qd) & (mj < qj), torch.zeros_like(lab), lab)
                 if abs_text_pos is not None:
-                    c = abs_text_pos.reshape(B * N, -1).float().mean(-1)
+                    c = gather(abs_text_pos.reshape(B, N, -1).float().mean(-1)).reshape(-1)
                     lab = torch.where((c < 0.2) | (c > 0.8), torch.zeros_like(lab), lab)
                 sel = vflat & (lab != 2)
-                selw = sel.float()
                 y = torch.where(sel, lab, torch.zeros_like(lab))
-                n_sel = selw.sum()
+                n_sel = sel.float().sum()
                 pos_weight = n_sel / y.sum() - 1.0                                    # 1/mean(y) - 1
+                selw = sel.float().view(Bc, N)[clip0:clip0 + B].reshape(-1)           # this rank's sentences
+                y_loc = y.view(Bc, N)[clip0:clip0 + B].reshape(-1)
             la_j = logits['joint_logits_alignability'][:, 2, :, 0].reshape(-1).float()   # 3rd stage hard-coded (:344)
-            bce = F.binary_cross_entropy_with_logits(la_j, y, pos_weight=pos_weight, reduction='none')
+            bce = F.binary_cross_entropy_with_logits(la_j, y_loc, pos_weight=pos_weight, reduction='none')
             loss_bce_joint = (bce * selw).sum() / n_sel
             loss_dict['loss-joint-bce'] = loss_bce_joint.detach()
-            loss_dict['alignability_top1'] = ((((la_j > 0).float() == y).float() * selw).sum() / n_sel).detach()
+            loss_dict['alignability_top1'] = ((((la_j > 0).float() == y_loc).float() * selw).sum() / n_sel).detach()
 
     nce_weight = 0 if args.optim_policy == 'bce' else 1
     if use_th:
@@ -203,5 +234,13 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video
         loss = (loss_dual + loss_joint) / 2
     if use_head:
         loss = loss * nce_weight + loss_bce_joint
+    if grp is not None:
+        # logged entries: per-rank shares -> global values, one small all-reduce
+        keys = [k for k in loss_dict if k not in ('confidence-ratio', 'iou-threshold')]
+        if keys:
+            packed = grp.sum_(torch.stack([loss_dict[k].float() for k in keys]))
+            for i, k in enumerate(keys):
+                loss_dict[k] = packed[i]
+        loss_dict['loss-global'] = grp.sum_(loss.detach().clone())
     loss_dict['loss'] = loss
     return loss_dict

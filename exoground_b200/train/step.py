@@ -8,6 +8,8 @@ B200 design:
     launches of exg_adamw (no-decay segment, decay segment) which also refresh the bf16 shadow weights;
   * the data-parallel replacement of DistributedDataParallel (train/main.py:413) is ONE NCCL all-reduce of the
     flat gradient buffer per step (sum; the 1/world_size of DDP's mean is folded into the AdamW kernel);
+    `cross_gpu_negatives=True` additionally all-gathers the text features so the NCE runs over the global batch
+    (train/xneg.py) -- the step is then numerically the single-process step on the concatenated batch;
   * host batches land in fp32 staging buffers (optionally on a copy stream while the previous step computes:
     `step(batch, next_batch=...)` / `prefetch()`), and one cast kernel per feature tensor moves them into the
     compute-dtype buffers the step reads, so the forward has no input cast and the PCIe copy overlaps compute;
@@ -25,7 +27,7 @@ from . import loss as exg_loss
 
 class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
-                 device="cuda", use_graph=True, process_group=None):
+                 device="cuda", use_graph=True, process_group=None, cross_gpu_negatives=False):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
@@ -36,6 +38,13 @@ class TanTrainStep:
         self.use_graph = use_graph and torch.device(device).type == "cuda"
         self.pg = process_group
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
+        # Mode B (train/xneg.py): negatives from every rank's sentences; the loss is then the GLOBAL mean, so
+        # parameter gradients are summed over ranks instead of averaged
+        self.xneg = None
+        if cross_gpu_negatives and self.world > 1:
+            from .xneg import Group
+            self.xneg = Group(process_group)
+            model.xneg = self.xneg
         self.step_count = 0
         self.graph = None
         dev = self.device
@@ -156,9 +165,9 @@ class TanTrainStep:
         out = m(self.video, self.text, self.vmask, self.tmask, None)
         L = exg_loss.loss_core(self.tgt, self.tmask, out, self.args,
                                self.abs_pos if getattr(self.args, "use_abs_text_pos", False) else None,
-                               self.B, self.T, self.N)
+                               self.B, self.T, self.N, xneg=self.xneg)
         L["loss"].backward()
-        self.loss_out.copy_(L["loss"].detach())
+        self.loss_out.copy_(L["loss-global" if self.xneg is not None else "loss"].detach())
 
     def _optimizer(self):
         fp = self.model.flat_params()
@@ -171,7 +180,7 @@ class TanTrainStep:
             if hi > lo:
                 K.adamw(fp.flat[lo:hi], fp.grad[lo:hi], self.m1[lo:hi], self.m2[lo:hi],
                         shadow[lo:hi] if shadow is not None else None, self.lr, b1, b2, self.eps, wd,
-                        self.step_count, grad_scale=1.0 / self.world)
+                        self.step_count, grad_scale=1.0 if self.xneg is not None else 1.0 / self.world)
 
     def _allreduce(self):
         if self.world > 1:
@@ -223,6 +232,15 @@ class TanTrainStep:
             torch.cuda.synchronize()
         g.zero_()
         self._prepared = True
+
+    def close(self):
+        """Release the captured graph.  Call before torch.distributed.destroy_process_group(): a CUDA graph that
+        captured NCCL kernels (cross_gpu_negatives) must not outlive its communicator."""
+        if self._on_cuda:
+            torch.cuda.synchronize()
+        self.graph = None
+        if self._on_cuda:
+            torch.cuda.synchronize()
 
     def run(self):
         """Device part of one step on the current static buffers.  Returns the 0-d loss tensor (device)."""

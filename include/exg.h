@@ -181,17 +181,22 @@ int exg_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
  * tgt_bits (optional): the same targets packed by exg_nce_pack_targets as [B*T, ceil(N/32)] uint32 rows
  *   (bit n of row (b,t) = tgt[b,n,t]); with it, bf16 logits and B*N % 8 == 0 the calls take the TMA streaming
  *   kernels (nce_tma.cu), otherwise the generic ones.
+ * Bc, clip0: column clips and the column clip owned by row clip 0.  Bc == B, clip0 == 0 is the single-GPU square
+ *   case above.  With the text features all-gathered over ranks (cross-GPU negatives) a rank holds the row block
+ *   L[S, B*T, Bc*N] of the global logits: its row clip a owns column clip a + clip0 (clip0 = rank * B), tgt /
+ *   tgt_bits / own_row_mask / wr / row sums stay LOCAL ([B,...]), col_valid / wc / column sums are GLOBAL ([Bc*N]);
+ *   the caller sums col_all / col_pos over ranks between fwd and bwd.
  */
 int exg_nce_pack_targets(const uint8_t* tgt, uint32_t* tgt_bits, int B, int T, int N, void* stream);
 int exg_nce_fwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits, const uint8_t* col_valid,
                 const uint8_t* own_row_mask, float* row_all, float* row_pos, float* col_all, float* col_pos,
-                int S, int B, int T, int N, float inv_temp, void* stream);
+                int S, int B, int T, int N, int Bc, int clip0, float inv_temp, void* stream);
 int exg_nce_bwd(const void* logits, int dtype, const uint8_t* tgt, const uint32_t* tgt_bits, const uint8_t* col_valid,
                 const uint8_t* own_row_mask, const float* row_all, const float* row_pos, const float* col_all, const float* col_pos,
                 const float* wr, const float* wc, void* G, int g_dtype,
-                int S, int B, int T, int N, float inv_temp, void* stream);
-/* own_max[b,k] = max_t L[stage, (b,t), (b,k)]   (train/loss.py:283-286) */
-int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B, int T, int N,
+                int S, int B, int T, int N, int Bc, int clip0, float inv_temp, void* stream);
+/* own_max[b,k] = max_t L[stage, (b,t), (b + clip0,k)]   (train/loss.py:283-286) */
+int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B, int T, int N, int Bc, int clip0,
                 void* stream);
 
 /* ---------------------------------------------------------------- ExoGround losses ------------

@@ -261,18 +261,24 @@ class TorchBackend:
         dk.copy_((ds.transpose(-1, -2) @ qf).transpose(1, 2).reshape(B * Sk, H * d).to(dk.dtype))
         dv.copy_((p.transpose(-1, -2) @ dof).transpose(1, 2).reshape(B * Sk, H * d).to(dv.dtype))
 
-    def _nce_common(self, logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask=None):
-        S = logits.shape[0]
+    @staticmethod
+    def _own(B, T, N, Bc, clip0, device):
+        """bool [B*T, Bc*N]: column (b', n) belongs to the clip of row (a, t), i.e. b' == a + clip0."""
+        rc = torch.arange(B, device=device).repeat_interleave(T) + clip0
+        cc = torch.arange(Bc, device=device).repeat_interleave(N)
+        return rc[:, None] == cc[None, :]
+
+    def _nce_common(self, logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask=None, Bc=None, clip0=0):
+        Bc = B if Bc is None else Bc
         e = torch.exp(logits.float() * inv_temp - inv_temp)                     # [S,R,Cc]
-        valid = col_valid.bool().view(1, 1, B * N)
+        valid = col_valid.bool().view(1, 1, Bc * N)
         e = torch.where(valid, e, torch.zeros_like(e))
-        eye = torch.eye(B, dtype=torch.bool, device=logits.device)
+        own = self._own(B, T, N, Bc, clip0, logits.device)
         if own_row_mask is not None:       # own-clip block of the masked rows counts as -inf
-            own = eye[:, None, :, None].expand(B, T, B, N).reshape(B * T, B * N)
             drop = own & own_row_mask.bool().view(B * T, 1)
             e = torch.where(drop[None], torch.zeros_like(e), e)
-        pos = (tgt.bool().permute(0, 2, 1)[:, :, None, :] & eye[:, None, :, None]).reshape(B * T, B * N)
-        pos = pos & col_valid.bool().view(1, B * N)
+        t_bt_n = tgt.bool().permute(0, 2, 1).reshape(B * T, N)                  # row (a,t) x sentence n
+        pos = own & t_bt_n.repeat(1, Bc) & col_valid.bool().view(1, Bc * N)
         return e, pos
 
     def nce_pack_targets(self, tgt):
@@ -285,14 +291,15 @@ class TorchBackend:
         words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)     # two's complement int32
         return words.permute(0, 2, 1).reshape(B * T, W).to(torch.int32)
 
-    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None, own_row_mask=None):
-        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask)
+    def nce_fwd(self, logits, tgt, col_valid, B, T, N, inv_temp, tgt_bits=None, own_row_mask=None, Bc=None, clip0=0):
+        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask, Bc, clip0)
         ep = e * pos[None]
         return e.sum(-1), ep.sum(-1), e.sum(-2), ep.sum(-2)
 
     def nce_bwd(self, logits, tgt, col_valid, sums, wr, wc, B, T, N, inv_temp, g_dtype=None, tgt_bits=None,
-                own_row_mask=None):
-        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask)
+                own_row_mask=None, Bc=None, clip0=0):
+        Bc = B if Bc is None else Bc
+        e, pos = self._nce_common(logits, tgt, col_valid, B, T, N, inv_temp, own_row_mask, Bc, clip0)
         ra, rp, ca, cp = sums
         safe = lambda w, s: torch.where((w != 0) & (s > 0), w / s.clamp(min=1e-38), torch.zeros_like(s))
         a_r = safe(wr[None, :].expand_as(ra), ra)[..., None]
@@ -304,19 +311,18 @@ class TorchBackend:
         if own_row_mask is not None:
             # positives removed by the own-row mask: where ALL positives of a weighted row (column) are gone, the
             # reference's positive LSE runs over -6e4 fills only and leaks -1/#entries through each of them
-            eye = torch.eye(B, dtype=torch.bool, device=logits.device)
-            own = eye[:, None, :, None].expand(B, T, B, N).reshape(B * T, B * N)
-            mpos = (pos & own & own_row_mask.bool().view(B * T, 1))[None].float()
+            mpos = (pos & own_row_mask.bool().view(B * T, 1))[None].float()
             n_cols = col_valid.float().sum()
             lr_ = torch.where((rp <= 0) & (wr[None, :] != 0), wr[None, :].expand_as(rp) / n_cols, torch.zeros_like(rp))
-            lc_ = torch.where((cp <= 0) & (wc[None, :] != 0), wc[None, :].expand_as(cp) / float(B * T),
+            lc_ = torch.where((cp <= 0) & (wc[None, :] != 0), wc[None, :].expand_as(cp) / float(Bc * T),
                               torch.zeros_like(cp))
             G = G - inv_temp * mpos * (lr_[..., None] + lc_[:, None, :])
         return G.to(g_dtype or logits.dtype)
 
-    def own_max(self, logits, stage, B, T, N):
-        lg = logits[stage].float().view(B, T, B, N)
-        return torch.stack([lg[b, :, b, :].max(0).values for b in range(B)], 0)
+    def own_max(self, logits, stage, B, T, N, Bc=None, clip0=0):
+        Bc = B if Bc is None else Bc
+        lg = logits[stage].float().view(B, T, Bc, N)
+        return torch.stack([lg[b, :, b + clip0, :].max(0).values for b in range(B)], 0)
 
     def adamw(self, param, grad, m, v, shadow, lr, beta1, beta2, eps, wd, step, grad_scale=1.0):
         g = grad * grad_scale

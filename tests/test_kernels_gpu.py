@@ -301,6 +301,48 @@ def test_nce(K, dt, S, B, T, N):
     _check(G, Gr, dt, "nce masked leak G")
 
 
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("S,W,B,T,N", [(2, 2, 3, 16, 8), (3, 4, 16, 64, 32), (2, 3, 5, 7, 12), (1, 8, 16, 64, 32)])
+def test_nce_row_blocks(K, dt, S, W, B, T, N):
+    """Cross-GPU negatives: every rank holds the row block [S, B*T, W*B*N] of the global logits (Bc, clip0).  Row
+    sums are the global ones' slices, column sums add up over ranks, and with the summed column sums the backward
+    of a block is the slice of the global gradient."""
+    Bg = W * B
+    Lg = (torch.rand((S, Bg * T, Bg * N), generator=_g(1)) * 2 - 1).to(dt).to(DEV)
+    tgt = (torch.rand((Bg, N, T), generator=_g(2)) < 0.15).to(torch.uint8).to(DEV)
+    cv = (torch.rand((Bg * N,), generator=_g(3)) < 0.8).to(torch.uint8).to(DEV)
+    tgt = tgt * cv.view(Bg, N, 1)
+    rm = (torch.rand((Bg * T,), generator=_g(8)) < 0.2).to(torch.uint8).to(DEV)
+    it = 1 / 0.07
+    for mask in (None, rm):
+        ref = REF.nce_fwd(Lg, tgt, cv, Bg, T, N, it, own_row_mask=mask)
+        wr = (torch.rand((Bg * T,), generator=_g(4)) * (torch.rand((Bg * T,), generator=_g(5)) < 0.7)).to(DEV)
+        wc = (torch.rand((Bg * N,), generator=_g(6)) * (torch.rand((Bg * N,), generator=_g(7)) < 0.7)).to(DEV)
+        Gr = REF.nce_bwd(Lg, tgt, cv, ref, wr, wc, Bg, T, N, it, own_row_mask=mask)
+        mref = REF.own_max(Lg, S - 1, Bg, T, N)
+        ca, cp, parts = 0, 0, []
+        for r in range(W):
+            rows = slice(r * B * T, (r + 1) * B * T)
+            blk = Lg[:, rows].contiguous()
+            m_loc = mask[rows].contiguous() if mask is not None else None
+            got = K.nce_fwd(blk, tgt[r * B:(r + 1) * B].contiguous(), cv, B, T, N, it, own_row_mask=m_loc, Bc=Bg,
+                            clip0=r * B)
+            _check(got[0], ref[0][:, rows], torch.float32, "block row_all")
+            _check(got[1], ref[1][:, rows], torch.float32, "block row_pos")
+            ca, cp = ca + got[2], cp + got[3]
+            parts.append((blk, got, m_loc))
+            _check(K.own_max(blk, S - 1, B, T, N, Bc=Bg, clip0=r * B), mref[r * B:(r + 1) * B], torch.float32,
+                   "block own_max")
+        _check(ca, ref[2], torch.float32, "summed col_all")
+        _check(cp, ref[3], torch.float32, "summed col_pos")
+        for r, (blk, got, m_loc) in enumerate(parts):
+            rows = slice(r * B * T, (r + 1) * B * T)
+            G = K.nce_bwd(blk, tgt[r * B:(r + 1) * B].contiguous(), cv, (ref[0][:, rows].contiguous(),
+                          ref[1][:, rows].contiguous(), ref[2], ref[3]), wr[rows].contiguous(), wc, B, T, N, it,
+                          own_row_mask=m_loc, Bc=Bg, clip0=r * B)
+            _check(G, Gr[:, rows], dt, "block G")
+
+
 # ------------------------------------------------------------------------------------------- optimizer
 def test_adamw_and_ema(K):
     n = 100003

@@ -107,3 +107,89 @@ def test_two_rank_gradient_allreduce_gloo():
     for rank, status, info in res:
         assert status == "ok", f"rank {rank}: {info}"
     assert abs(res[0][2] - res[1][2]) > 0        # different batches -> different local losses
+
+
+# ----------------------------------------------------------------------------------------------- cross-GPU negatives
+def _cat_batches(bs):
+    out = {}
+    for k in bs[0]:
+        if torch.is_tensor(bs[0][k]):
+            out[k] = torch.cat([b[k] for b in bs], 0)
+        else:
+            out[k] = [x for b in bs for x in b[k]]
+    return out
+
+
+def _xneg_worker(rank, world, port, q, head, th):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from exoground_b200 import ops
+        from exoground_b200.model import TemporalAligner
+        from exoground_b200.train.step import TanTrainStep
+        from exoground_b200.utils import synth
+        from tests.fake_backend import TorchBackend
+        from tests.shapes import tan_shapes
+        ops.set_backend(TorchBackend())
+        E2, D2 = 2, 3
+        args = synth.tan_args(loss_threshold=th, use_alignability_head=head, use_abs_text_pos=bool(head))
+        kw = dict(lr=1e-3, wd=1e-2, device="cpu", use_graph=False)
+
+        def model():
+            m = TemporalAligner(E2, D2, use_alignability_head=head, video_embed_dim=DIN, text_embed_dim=DIN,
+                                random_pos_start=0, compute_dtype=torch.float32)
+            m.load_state_dict(synth.fill_state_dict(tan_shapes(E2, D2, DIN, head=head)))
+            return m
+
+        batches = [synth.tan_batch(B=B, T=T, N=N, d_video=DIN, d_text=DIN, seed=300 + r) for r in range(world)]
+        for b in batches:       # absolute sentence positions (loss.py:337-347 reads their mean)
+            g = torch.Generator().manual_seed(int(b["video"].abs().sum() * 1000) % 10007)
+            b["abs_text_pos"] = torch.rand(B, N, 2, generator=g)
+
+        # distributed: this rank's clips, negatives from both ranks
+        m = model()
+        st = TanTrainStep(m, args, B, T, N, DIN, DIN, process_group=dist.group.WORLD, cross_gpu_negatives=True, **kw)
+        st.load_batch(batches[rank], non_blocking=False)
+        st.prepare()
+        loss = float(st.run())
+        fp = m.flat_params()
+        g_dist = fp.grad[:fp.n_used].clone()
+
+        # single process on the concatenated batch
+        mr = model()
+        sr = TanTrainStep(mr, args, world * B, T, N, DIN, DIN, **kw)
+        sr.load_batch(_cat_batches(batches), non_blocking=False)
+        sr.prepare()
+        loss_ref = float(sr.run())
+        fr = mr.flat_params()
+        g_ref = fr.grad[:fr.n_used].clone()
+        assert abs(loss - loss_ref) <= 1e-5 * max(1.0, abs(loss_ref)), (loss, loss_ref)
+        err = (g_dist - g_ref).norm() / g_ref.norm()
+        assert err < 1e-4, f"gradient of the global loss: rel-L2 {err:.3e}"
+        # first Adam step ~ lr * sign(g): elements with |g| near eps amplify fp32 summation-order noise
+        assert ((fp.flat - fr.flat).abs() > 2e-4).float().mean() < 1e-3, (fp.flat - fr.flat).abs().max()
+        q.put((rank, "ok", loss))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, "fail", traceback.format_exc() + repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("head,th", [(0, 0.0), (1, 0.5)])
+def test_two_rank_cross_gpu_negatives_gloo(head, th):
+    """Mode B == the single-process step on the concatenated batch: loss, summed gradients, updated parameters."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_xneg_worker, args=(r, 2, port, q, head, th)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=500) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, status, info in res:
+        assert status == "ok", f"rank {rank}: {info}"
+    assert abs(res[0][2] - res[1][2]) < 1e-6      # both ranks report the same (global) loss
