@@ -307,6 +307,23 @@ int exg_attn_tc_bwd(const void* q, const void* k, const void* v, const void* o, 
                     long ldk, long ldv, long ldo, const uint8_t* key_pad, const float* lse, void* dq, void* dk,
                     void* dv, int B, int H, int Sq, int Sk, float scale, void* stream);
 
+int exg_attn_flash_ok(int dtype, long ldq, long ldk, long ldv, long ldo, int Sq, int Sk, int d, const void* q,
+                      const void* k, const void* v, const void* o);
+int exg_attn_flash_fwd(const void* q, const void* k, const void* v, long ldq, long ldk, long ldv,
+                       const uint8_t* key_pad, void* o, long ldo, float* lse, int B, int H, int Sq, int Sk,
+                       float scale, void* stream);
+int exg_attn_flash_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout, long ldq,
+                       long ldk, long ldv, long ldo, const uint8_t* key_pad, const float* lse, float* workspace,
+                       void* dq, void* dk, void* dv, int B, int H, int Sq, int Sk, float scale, void* stream);
+
+// fp32 elements of the `delta` workspace of exg_attn_bwd: [B,H,Sq] row statistics, plus (sequences longer than one
+// 128-row tile) the fp32 dQ accumulator [B*Sq, H*d] of the multi-tile tensor-core backward
+extern "C" long exg_attn_bwd_workspace(int B, int H, int Sq, int Sk, int d) {
+  long n = (((long)B * H * Sq + 31) / 32) * 32;
+  if (Sq > 128 || Sk > 128) n += (long)B * Sq * H * d;
+  return n;
+}
+
 extern "C" int exg_attn_fwd(const void* q, const void* k, const void* v, int dtype, long ldq, long ldk,
                             long ldv, const uint8_t* key_pad, void* o, long ldo, float* lse, int B, int H,
                             int Sq, int Sk, int d, float scale, void* stream) {
@@ -316,6 +333,10 @@ extern "C" int exg_attn_fwd(const void* q, const void* k, const void* v, int dty
   if (lse && exg_attn_tc_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, false, q, k, v, o)) {
     ExgProfScope prof(EXG_PC_ATTN_FWD, 4.0 * B * H * Sq * Sk * d, stream);
     return exg_attn_tc_fwd(q, k, v, ldq, ldk, ldv, key_pad, o, ldo, lse, B, H, Sq, Sk, scale, stream);
+  }
+  if (exg_attn_flash_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, q, k, v, o)) {
+    ExgProfScope prof(EXG_PC_ATTN_FWD, 4.0 * B * H * Sq * Sk * d, stream);
+    return exg_attn_flash_fwd(q, k, v, ldq, ldk, ldv, key_pad, o, ldo, lse, B, H, Sq, Sk, scale, stream);
   }
   AttnArgs a = {};
   a.q = q; a.k = k; a.v = v; a.out = o; a.dtype = dtype; a.ldq = ldq; a.ldk = ldk; a.ldv = ldv; a.ldo = ldo;
@@ -342,6 +363,12 @@ extern "C" int exg_attn_bwd(const void* q, const void* k, const void* v, const v
     ExgProfScope prof(EXG_PC_ATTN_BWD, 10.0 * B * H * Sq * Sk * d, stream);
     return exg_attn_tc_bwd(q, k, v, o, dout, ldq, ldk, ldv, ldo, key_pad, lse, dq, dk, dv, B, H, Sq, Sk, scale,
                            stream);
+  }
+  if ((Sq > 128 || Sk > 128) && exg_attn_flash_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, q, k, v, o) &&
+      exg_attn_flash_ok(dtype, ldq, ldk, ldv, ldo, Sq, Sk, d, dq, dk, dv, dout)) {
+    ExgProfScope prof(EXG_PC_ATTN_BWD, 10.0 * B * H * Sq * Sk * d, stream);
+    return exg_attn_flash_bwd(q, k, v, o, dout, ldq, ldk, ldv, ldo, key_pad, lse, delta, dq, dk, dv, B, H, Sq, Sk,
+                              scale, stream);
   }
   AttnArgs a = {};
   a.q = q; a.k = k; a.v = v; a.o = o; a.dout = dout; a.dq = dq; a.dk = dk; a.dv = dv; a.dtype = dtype;

@@ -318,7 +318,7 @@ class CudaBackend:
         _cuda(q, k, v, o, do, lse, key_pad, dq, dk, dv)
         if (_rows2d(dq), _rows2d(dk), _rows2d(dv)) != (_rows2d(q), _rows2d(k), _rows2d(v)) or _rows2d(do) != _rows2d(o):
             raise ValueError("attn_bwd: gradient views must use the strides of their primals")
-        delta = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+        delta = torch.empty((self.lib.exg_attn_bwd_workspace(B, H, Sq, Sk, 64),), dtype=torch.float32, device=q.device)
         L.check(self.lib.exg_attn_bwd(_p(q), _p(k), _p(v), _p(o), _p(do), _dt(q.dtype), _rows2d(q), _rows2d(k),
                                       _rows2d(v), _rows2d(o), _p(key_pad), _p(lse), _p(delta), _p(dq), _p(dk),
                                       _p(dv), B, H, Sq, Sk, 64, float(scale), _stream()), "exg_attn_bwd")

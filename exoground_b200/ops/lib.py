@@ -71,6 +71,7 @@ _SIGS = {
                                C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]),
     "exg_attn_bwd": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_long, C.c_long, C.c_long, C.c_long, vp, vp,
                                vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]),
+    "exg_attn_bwd_workspace": (C.c_long, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "exg_nce_pack_targets": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, vp]),
     "exg_nce_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                               C.c_int, C.c_int, C.c_float, vp]),

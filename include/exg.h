@@ -159,7 +159,10 @@ int exg_attn_fwd(const void* q, const void* k, const void* v, int dtype,
                  long ldq, long ldk, long ldv, const uint8_t* key_pad,
                  void* o, long ldo, float* lse, int B, int H, int Sq, int Sk, int d, float scale,
                  void* stream);
-/* delta: fp32 workspace [B,H,Sq].  dq/dk/dv use the same strides as q/k/v. */
+/* delta: fp32 workspace of exg_attn_bwd_workspace(B,H,Sq,Sk,d) elements ([B,H,Sq] row statistics, plus the fp32 dQ
+ * accumulator of the multi-tile tensor-core backward when Sq or Sk exceeds 128).  dq/dk/dv use the same strides as
+ * q/k/v. */
+long exg_attn_bwd_workspace(int B, int H, int Sq, int Sk, int d);
 int exg_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
                  int dtype, long ldq, long ldk, long ldv, long ldo, const uint8_t* key_pad,
                  const float* lse, float* delta, void* dq, void* dk, void* dv,

@@ -226,7 +226,9 @@ def test_cast_and_stage_mean(K):
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,Sq,Sk,masked", [(2, 64, 64, True), (3, 96, 96, True), (2, 100, 100, True),
                                             (2, 8, 200, True), (1, 300, 300, False), (4, 64, 64, False),
-                                            (2, 24, 120, True), (3, 128, 128, True), (2, 200, 72, True)])
+                                            (2, 24, 120, True), (3, 128, 128, True), (2, 200, 72, True),
+                                            (2, 1024, 1024, True), (1, 1100, 1100, True), (1, 64, 2080, True),
+                                            (2, 520, 130, False), (1, 129, 257, True)])
 def test_attention(K, dt, B, Sq, Sk, masked):
     H, d = 8, 64
     self_attn = Sq == Sk
