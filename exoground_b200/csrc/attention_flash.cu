@@ -129,17 +129,30 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       mbar_wait(bar_s, j & 1);
       tc_fence_after();
       const uint32_t* mw = maskw + j * 4;
-      float mt = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + lane_addr + c * 32, r);
-        tmem_ld_wait();
-        const uint32_t w = mw[c];
+      // pass 1: tile max.  TMEM loads double-buffered (the next chunk is in flight while this one is reduced);
+      // 4 independent running maxima instead of one 32-deep dependency chain; unmasked fast path
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32(tS + lane_addr, ra);
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if ((w >> i) & 1) mt = fmaxf(mt, __uint_as_float(r[i]));
+        for (int c = 0; c < 4; ++c) {
+          uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+          uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+          tmem_ld_wait();
+          if (c + 1 < 4) tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, nxt);
+          const uint32_t w = mw[c];
+          if (w == 0xffffffffu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if ((w >> i) & 1) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
+          }
+        }
       }
+      const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       const float m_new = fmaxf(m, mt);
       const float msafe = m_new == -INFINITY ? 0.f : m_new;
       const float alpha = ex2_approx((m - msafe) * sl2);          // m = -inf -> 0 (o and l are 0 then anyway)
@@ -155,24 +168,38 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
         for (int i = 0; i < HD; ++i) o[i] = (o[i] + __uint_as_float(r[i])) * alpha;
       }
       const float nb = -msafe * sl2;
-      float sum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tS + lane_addr + c * 32, r);
-        tmem_ld_wait();
-        const uint32_t w = mw[c];
-        float pv[32];
+      float sm4[4] = {0.f, 0.f, 0.f, 0.f};
+      {
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32(tS + lane_addr, ra);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float e = ((w >> i) & 1) ? ex2_approx(fmaf(__uint_as_float(r[i]), sl2, nb)) : 0.f;
-          pv[i] = e; sum += e;
+        for (int c = 0; c < 4; ++c) {
+          uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+          uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+          tmem_ld_wait();
+          if (c + 1 < 4) tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, nxt);
+          const uint32_t w = mw[c];
+          float pv[32];
+          if (w == 0xffffffffu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              pv[i] = ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb));
+              sm4[i & 3] += pv[i];
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              pv[i] = ((w >> i) & 1) ? ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb)) : 0.f;
+              sm4[i & 3] += pv[i];
+            }
+          }
+          uint8_t* blk = Ps + (c >> 1) * kTile;
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            *reinterpret_cast<uint4*>(blk + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
         }
-        uint8_t* blk = Ps + (c >> 1) * kTile;
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          *reinterpret_cast<uint4*>(blk + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
       }
+      const float sum = (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
       l = l * alpha + sum;
       fence_proxy_async();
       tc_fence_before();
@@ -363,25 +390,40 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       const float delta = row_ok ? fa.delta[sidx] : 0.f;
       mbar_wait(bar_s, i & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t rs[32], rd[32];
-        tmem_ld_32x32(tS + lane_addr + c * 32, rs);
-        tmem_ld_32x32(tdP + lane_addr + c * 32, rd);
-        tmem_ld_wait();
-        const uint32_t w = row_ok ? mw[c] : 0u;
-        float pv[32], ds[32];
+      {
+        uint32_t sa[32], da[32], sb2[32], db2[32];
+        tmem_ld_32x32(tS + lane_addr, sa);
+        tmem_ld_32x32(tdP + lane_addr, da);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float pr = ((w >> j) & 1) ? ex2_approx(fmaf(__uint_as_float(rs[j]), sl2, -lse_l2)) : 0.f;
-          pv[j] = pr;
-          ds[j] = pr * (__uint_as_float(rd[j]) - delta) * p.scale;
-        }
-        uint8_t* pb = Ps + (c >> 1) * kTile; uint8_t* db = dSs + (c >> 1) * kTile;
+        for (int c = 0; c < 4; ++c) {
+          uint32_t (&rs)[32] = (c & 1) ? sb2 : sa;
+          uint32_t (&rd)[32] = (c & 1) ? db2 : da;
+          tmem_ld_wait();
+          if (c + 1 < 4) {
+            tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, (c & 1) ? sa : sb2);
+            tmem_ld_32x32(tdP + lane_addr + (c + 1) * 32, (c & 1) ? da : db2);
+          }
+          const uint32_t w = row_ok ? mw[c] : 0u;
+          float pv[32], ds[32];
+          if (w == 0xffffffffu) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          *reinterpret_cast<uint4*>(pb + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
-          *reinterpret_cast<uint4*>(db + swz(tid, (c & 1) * 4 + u)) = pack8(&ds[u * 8]);
+            for (int j = 0; j < 32; ++j) {
+              pv[j] = ex2_approx(fmaf(__uint_as_float(rs[j]), sl2, -lse_l2));
+              ds[j] = pv[j] * ((__uint_as_float(rd[j]) - delta) * p.scale);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              pv[j] = ((w >> j) & 1) ? ex2_approx(fmaf(__uint_as_float(rs[j]), sl2, -lse_l2)) : 0.f;
+              ds[j] = pv[j] * ((__uint_as_float(rd[j]) - delta) * p.scale);
+            }
+          }
+          uint8_t* pb = Ps + (c >> 1) * kTile; uint8_t* db = dSs + (c >> 1) * kTile;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            *reinterpret_cast<uint4*>(pb + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
+            *reinterpret_cast<uint4*>(db + swz(tid, (c & 1) * 4 + u)) = pack8(&ds[u * 8]);
+          }
         }
       }
       fence_proxy_async();

@@ -113,3 +113,19 @@ def fill_state_dict(shapes, seed=888):
             t = 0.05 * torch.randn(shape, generator=g)
         out[name] = t
     return out
+
+
+def htm_align_item(vlen=200, K=40, d_video=1024, d_text=4096, seed=7, aligned_frac=0.3):
+    """One HTM-Align-shaped video (eval/eval_zeroshot_align.py:62-77: full-length features, all sentences with
+    [aligned, start, end]): video [1, vlen, Dv], sentence embeddings [K, Dt], sorted start seconds, end = start +
+    U(2, 8), `aligned` flags (sample 0 / the last sentence are non-alignable so every window has an anchor)."""
+    g = torch.Generator().manual_seed(seed)
+    rs = np.random.RandomState(seed)
+    video = torch.randn(1, vlen, d_video, generator=g)
+    text = torch.randn(K, d_text, generator=g)
+    start = np.sort(rs.uniform(0, max(vlen - 8, 1), size=K))
+    end = np.minimum(start + rs.uniform(2, 8, size=K), vlen - 1)
+    aligned = (rs.uniform(size=K) < aligned_frac).astype(np.int64)
+    aligned[0] = 0; aligned[-1] = 0
+    return {"video": video, "text": text, "start": [float(x) for x in start], "end": [float(x) for x in end],
+            "aligned": [int(x) for x in aligned]}

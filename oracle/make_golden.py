@@ -133,6 +133,61 @@ def agree_case(r, name, E=2, D=3, B=5, T=16, N=8, d_in=32, np_seed=5):
     print(name, {k: float(v) for k, v in store.items() if k.endswith("/loss")})
 
 
+def align_case(r, name, E=2, D=3, d_in=32, seq_len=16):
+    """Sliding-window alignment inference: the UNMODIFIED eval/eval_zeroshot_align.py::test_alignment_htm driven
+    by the closure of train/main.py:166-184 on synthetic HTM-Align-shaped videos (dataset class and loader patched
+    to serve them; sentence strings are indices into the synthetic embedding table)."""
+    import types
+    ref_root = ref_import.REF
+    if os.path.join(ref_root, "eval") not in sys.path:
+        sys.path.insert(0, os.path.join(ref_root, "eval"))
+    import eval_zeroshot_align as ez
+    model = build_tan(r, E, D, d_in, head=0)
+    model.random_pos_start = 0
+    model.eval()
+    recipe = [dict(vlen=70, K=18, seed=11), dict(vlen=45, K=9, seed=12), dict(vlen=130, K=40, seed=13)]
+    items = [synth.htm_align_item(d_video=d_in, d_text=d_in, **kw) for kw in recipe]
+
+    class FakeSet:
+        def __init__(self, *a, **k):
+            pass
+
+    def fake_loader(ds, **k):
+        out = []
+        for vi, it in enumerate(items):
+            out.append({"video": it["video"], "str": [(f"{vi}:{k_}",) for k_ in range(len(it["start"]))],
+                        "aligned": torch.tensor([it["aligned"]]), "vid": [f"v{vi}"],
+                        "start": torch.tensor([it["start"]]), "end": torch.tensor([it["end"]])})
+        return out
+
+    def get_text_visual_sim(video_embed, text_str, interpolate_from=None, abs_text_pos=None):
+        vi = int(text_str[0].split(":")[0])
+        idx = [int(s.split(":")[1]) for s in text_str]
+        te = items[vi]["text"][idx]
+        with torch.no_grad():
+            j = model.get_text_visual_sim_joint(video_embed, te[None], interpolate_from)
+            d = model.get_text_visual_sim_dual(video_embed, te[None], interpolate_from)
+        return {"sim": j.transpose(-1, -2) / 0.07, "dual-sim": d.transpose(-1, -2) / 0.07}
+
+    captured = {}
+    real_auc = ez.metrics.roc_auc_score
+
+    def spy_auc(tgt, sim):
+        captured["tgt"], captured["score"] = np.asarray(tgt), np.asarray(sim)
+        return real_auc(tgt, sim)
+
+    ez.HTM_Align, ez.DataLoaderFast = FakeSet, fake_loader
+    ez.metrics = types.SimpleNamespace(roc_auc_score=spy_auc)
+    args = types.SimpleNamespace(seq_len=seq_len, use_alignability_head=0)
+    with ref_import.quiet():
+        m = ez.test_alignment_htm(get_text_visual_sim, torch.device("cpu"), args)
+    store = {"recall": np.float64(m["Recall"]), "auc": np.float64(m["AUC"]), "score": captured["score"],
+             "tgt": captured["tgt"], "seq_len": np.int64(seq_len), "dims": np.array([E, D, d_in]),
+             "recipe": np.array([[kw["vlen"], kw["K"], kw["seed"]] for kw in recipe])}
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **store)
+    print(name, "Recall", m["Recall"], "AUC", m["AUC"], "sentences", len(captured["score"]))
+
+
 def sim_case(r, name):
     m = build_tan(r, 2, 2, 32, 1)
     m.eval()
@@ -212,6 +267,7 @@ def main():
              [(0.0, 0, 0), (0.3, 0, 0), (0.0, 1, 1), (0.5, 1, 0)])
     sim_case(r, "tan_sim")
     agree_case(r, "tan_agree")
+    align_case(r, "tan_align")
     exo_case(r, "exo_small")
     tan_case(r, "tan_cfg1", 6, 6, 8, 64, 32, 1024, 888, [(0.0, 0, 0), (0.5, 1, 0)], sub_logits=(8, 4))
 

@@ -114,3 +114,10 @@ def test_exo_loss_dispatch_and_errors():
 def test_tan_self_labelling_agreement_host_logic(golden_dir):
     from tests.tan_cases import run_agree_case
     run_agree_case(_load(golden_dir, "tan_agree"), "cpu", torch.float32)
+
+
+def test_sliding_window_alignment_host_logic(golden_dir):
+    """eval/eval_zeroshot_align.py::test_alignment_htm (reference run on synthetic HTM-Align videos) vs
+    exoground_b200.eval.align: per-sentence scores, Recall, AUC; batched windows == window loop."""
+    from tests.align_cases import run_align_case
+    run_align_case(_load(golden_dir, "tan_align"), "cpu", torch.float32, 2e-4)

@@ -67,3 +67,11 @@ def test_vi_mlp_grads(dt):
 def test_tan_self_labelling_agreement(golden_dir, dt):
     from tests.tan_cases import run_agree_case
     run_agree_case(load_golden(golden_dir, "tan_agree"), "cuda", dt)
+
+
+@pytest.mark.parametrize("dt,tol", [(torch.float32, 2e-4), (torch.bfloat16, 3e-2)])
+def test_sliding_window_alignment(golden_dir, dt, tol):
+    """eval/eval_zeroshot_align.py::test_alignment_htm on synthetic HTM-Align videos: per-sentence scores within
+    tolerance; fp32 Recall / AUC / predicted seconds exact; one batched forward == the window loop."""
+    from tests.align_cases import run_align_case
+    run_align_case(load_golden(golden_dir, "tan_align"), "cuda", dt, tol)
