@@ -7,6 +7,7 @@ exg_xview_nce_fwd/bwd: one warp per (clip, second)); the host code below only do
 """
 from collections import Counter
 
+import numpy as np
 import torch
 from torch.nn.utils.rnn import pad_sequence
 
@@ -160,14 +161,14 @@ def get_view_invariant_loss(input_data, logits, args):
                                        getattr(args, 'only_same_view_negative', False), INV_TEMP)
     loss_dict = {}
     # per-camera-rank bins (reference :173-187, one .item() per element there; one read-back here)
-    host = torch.stack((l1, pos_cos, neg_cos, nce.detach()), dim=0).reshape(4, -1).tolist()
-    for i, view_name in enumerate(flatten_list_of_lists(view_rank_names)):
-        for metric, vals in zip(("L1", "pos_cosine", "avg_neg_cosine", "InfoNCE"), host):
-            d = loss_dict.setdefault(f"Rank {view_name} {metric}", {'total': 0.0, 'count': 0})
-            d['total'] += vals[i]
-            d['count'] += 1
-    for key in loss_dict:
-        loss_dict[key]['mean'] = loss_dict[key]['total'] / loss_dict[key]['count']
+    host = torch.stack((l1, pos_cos, neg_cos, nce.detach()), dim=0).reshape(4, -1).double().cpu().numpy()
+    names, inverse = np.unique(np.asarray(flatten_list_of_lists(view_rank_names), dtype=object).astype(str),
+                               return_inverse=True)
+    counts = np.bincount(inverse, minlength=len(names))
+    for metric, vals in zip(("L1", "pos_cosine", "avg_neg_cosine", "InfoNCE"), host):
+        totals = np.bincount(inverse, weights=vals, minlength=len(names))        # float64 sums, as the reference's
+        for name, tot, cnt in zip(names, totals, counts):
+            loss_dict[f"Rank {name} {metric}"] = {'total': float(tot), 'count': int(cnt), 'mean': float(tot / cnt)}
     loss_dict["L1 loss"] = l1.mean()
     loss_dict["Pos cosine sim"] = pos_cos.mean()
     loss_dict["Avg neg cosine sim"] = neg_cos.mean()

@@ -1,0 +1,67 @@
+"""One ExoGround / keystep-grounding training step on one GPU (one process per GPU): the body of the reference's
+train() loop (train/main_egoexo4d_distributed.py:105-222: forward :145-153, get_loss :165-168, backward :175,
+clip + optimizer step :176-181) with DistributedDataParallel (:611-614) replaced by ONE NCCL all-reduce of the flat
+gradient buffer and torch.optim.AdamW by the fused kernel (train/flat.py).  The grounding / view-invariant losses
+have no cross-sample terms, so the data-parallel mode is DDP-equivalent: local loss, mean gradient.
+
+The step runs eagerly: the reference loss dictionary carries per-camera-rank host statistics (one read-back per
+loss here instead of one `.item()` per element), which keeps it out of a CUDA graph."""
+import torch
+
+from .. import ops
+from . import loss_egoexo4d as exo_loss
+from .flat import FlatAdamW
+
+_DEVICE_KEYS = ("video_features", "narration_features", "video_padding_mask", "narration_padding_mask",
+                "ego_video_features", "view_rank_label", "view_rank_neg_label", "same_view_neg_idxs",
+                "starts", "ends", "mean", "duration", "view_available_mask")
+
+
+class ExoTrainStep:
+    def __init__(self, model, args, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8, clip_grad=0.0, device="cuda",
+                 process_group=None):
+        if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
+            raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
+        self.device = torch.device(device)
+        self.model, self.args, self.clip_grad = model.to(device), args, clip_grad
+        self.opt = FlatAdamW(self.model, lr, wd, betas, eps, process_group)
+        self.h2d_bytes = 0
+
+    def to_device(self, batch):
+        out, n = dict(batch), 0
+        for k in _DEVICE_KEYS:
+            v = batch.get(k)
+            if torch.is_tensor(v):
+                out[k] = v.to(self.device, non_blocking=True)
+                n += v.numel() * v.element_size()
+        self.h2d_bytes = n
+        return out
+
+    def _fwd_bwd(self, b):
+        m, args = self.model, self.args
+        ego = b.get("ego_video_features") if getattr(args, "use_distill_nce_loss", False) else None
+        kw = {}
+        if ego is not None:
+            kw["egocentric_video_embed"] = ego[:, 0] if ego.dim() == 4 else ego
+        out = m(b["video_features"], b["narration_features"], b["video_padding_mask"].bool(),
+                b["narration_padding_mask"].bool(), **kw)
+        L, iou = exo_loss.get_loss(b, out, b["narration_padding_mask"], args)
+        L["loss"].backward()
+        return L, iou
+
+    def step(self, batch):
+        """Host batch (the collate dict of data/loader_egoexo4d.py:567-598) in, loss dict out."""
+        self.model.train()
+        b = self.to_device(batch)
+        if not self.opt.attached:
+            for p in self.model.parameters():
+                p.grad = None
+            self._fwd_bwd(b)                    # discovery pass: which parameters receive gradients
+            self.opt.attach()
+        self.opt.zero_grad()
+        L, _ = self._fwd_bwd(b)
+        self.opt.allreduce()
+        if self.clip_grad > 0:
+            self.opt.clip_per_param(self.clip_grad)
+        self.opt.step()
+        return L

@@ -193,3 +193,83 @@ def test_two_rank_cross_gpu_negatives_gloo(head, th):
     for rank, status, info in res:
         assert status == "ok", f"rank {rank}: {info}"
     assert abs(res[0][2] - res[1][2]) < 1e-6      # both ranks report the same (global) loss
+
+
+# ----------------------------------------------------------------------------------------------- ExoGround DDP replacement
+def _exo_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import numpy as np
+        from exoground_b200 import ops
+        from exoground_b200.model import ExoGroundingTransformer
+        from exoground_b200.train.step_exo import ExoTrainStep
+        from exoground_b200.utils import synth
+        from tests.fake_backend import TorchBackend
+        from tests.shapes import exo_shapes
+        ops.set_backend(TorchBackend())
+        Dv, Dt, Bx, Tx, Nx = 24, 40, 3, 16, 6
+        args = synth.exo_args(use_distill_nce_loss=True, same_view_negative=True)
+
+        def make():
+            m = ExoGroundingTransformer(1, 1, video_embed_dim=Dv, text_embed_dim=Dt, use_distill_nce_loss=True,
+                                        random_pos_start=0, compute_dtype=torch.float32)
+            m.load_state_dict(synth.fill_state_dict(exo_shapes(1, 1, Dv, Dt, distill=True)))
+            return m
+
+        batches = [synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=500 + r) for r in range(world)]
+        st = ExoTrainStep(make(), args, lr=1e-3, wd=1e-2, clip_grad=3.0, device="cpu", process_group=dist.group.WORLD)
+        L = st.step(batches[rank])
+        g_dist = st.opt.flat_grad().clone()            # all-reduced (sum) and clipped
+
+        # single-process restatement: mean of the two ranks' gradients, the reference's per-parameter clip, AdamW
+        grads, models = [], []
+        for r in range(world):
+            sr = ExoTrainStep(make(), args, lr=1e-3, wd=1e-2, device="cpu")
+            b = sr.to_device(batches[r])
+            for p in sr.model.parameters():
+                p.grad = None
+            sr._fwd_bwd(b)
+            sr.opt.attach()
+            sr._fwd_bwd(b)
+            grads.append(sr.opt.flat_grad().clone())
+            models.append(sr)
+        assert (grads[0] - grads[1]).abs().max() > 1e-7
+        ref = models[0]
+        ref.opt.flat_grad().copy_((grads[0] + grads[1]) / world)
+        for _, p in ref.model.named_parameters():      # utils/train_utils.py:3-13
+            if p.grad is not None:
+                n = p.grad.norm(2)
+                c = 3.0 / (n + 1e-6)
+                if c < 1:
+                    p.grad.mul_(c)
+        want = ref.opt.flat_grad().clone()
+        assert torch.allclose(g_dist / world, want, rtol=1e-5, atol=1e-7), (g_dist / world - want).abs().max()
+        ref.opt.step()
+        mine, theirs = st.model.flat_params().flat, ref.model.flat_params().flat
+        assert ((mine - theirs).abs() > 2e-4).float().mean() < 1e-3, (mine - theirs).abs().max()
+        both = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(both, mine.clone())
+        assert torch.equal(both[0], both[1])
+        q.put((rank, "ok", float(L["loss"])))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, "fail", traceback.format_exc() + repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_exo_step_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_exo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, status, info in res:
+        assert status == "ok", f"rank {rank}: {info}"
