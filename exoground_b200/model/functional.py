@@ -130,6 +130,34 @@ class JointConcatFn(torch.autograd.Function):
         return dxv, dpos, dxt, None, None, None
 
 
+class JointConcat3Fn(torch.autograd.Function):
+    """x0[b] = [xv[b] | xa[b] + pos | xt[b]]  -> fp32 [B*(2Tv+N), C]
+    (torch.cat((video, audio + ln_position_init(pos), lang), dim=1): exo_ground_model.py:347-350)."""
+
+    @staticmethod
+    def forward(ctx, xv, xa, pos, xt, B, Tv, N):
+        K = ops.get()
+        S = 2 * Tv + N
+        out = torch.empty((B * S, xv.shape[-1]), dtype=torch.float32, device=xv.device)
+        K.add_rows(xv, B * Tv, out=out, map_out=(Tv, S, 0))
+        K.add_rows(xa, B * Tv, add=pos, add_period=Tv, out=out, map_out=(Tv, S, Tv))
+        K.add_rows(xt, B * N, out=out, map_out=(N, S, 2 * Tv))
+        ctx.dims = (B, Tv, N)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        K = ops.get()
+        B, Tv, N = ctx.dims
+        S = 2 * Tv + N
+        dy = dy.contiguous()
+        dxv, _ = K.add_rows(dy, B * Tv, map_x=(Tv, S, 0))
+        dxa, _ = K.add_rows(dy, B * Tv, map_x=(Tv, S, Tv))
+        dxt, _ = K.add_rows(dy, B * N, map_x=(N, S, 2 * Tv))
+        dpos = K.colsum(dxa.view(B, -1)).view(Tv, -1)
+        return dxv, dxa, dpos, dxt, None, None, None
+
+
 class GatherRowsFn(torch.autograd.Function):
     """Contiguous copy of mapped rows of a [*, C] buffer (slicing the text rows / last stage out of a
     joint stage buffer: tan_model.py:203, exo_ground_model.py:165-166,172).  out dtype = out_dtype."""

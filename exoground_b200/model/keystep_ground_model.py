@@ -10,7 +10,7 @@ The reference's TwinExoGroundingTransformer (:411-448) references attributes tha
 import torch
 
 from . import functional as Fn
-from .exo_ground_model import ExoGroundingTransformer, info_nce_bmm
+from .exo_ground_model import ExoGroundingTransformer, info_nce_bmm, pairwise_info_nce
 
 
 class GroundingModel(ExoGroundingTransformer):
@@ -22,15 +22,17 @@ class GroundingModel(ExoGroundingTransformer):
 
     def forward(self, video_embed, lang_embed, video_padding_mask, lang_padding_mask, audio_embed=None,
                 audio_padding_mask=None, egocentric_video_embed=None, view_mask=None, interpolate_from=None):
-        if audio_embed is not None:
-            raise NotImplementedError("audio branch is not built")
-        self._check(video_embed, lang_embed)
+        self._check(video_embed, lang_embed, audio_embed)
         wT = self._weights()
         B, T, _ = video_embed.shape
         N = lang_embed.shape[1]
         vmask = video_padding_mask.to(torch.uint8).contiguous()
         tmask = lang_padding_mask.to(torch.uint8).contiguous()
         xt = self._text_proj(lang_embed, wT)
+        a_feat = amask = None
+        if audio_embed is not None:
+            a_feat = self._audio_proj(audio_embed, wT)
+            amask = audio_padding_mask.to(torch.uint8).contiguous()
         if self.use_text_pos_enc:
             p0 = 0 if interpolate_from else self._draw(N)
             xt = Fn.AddPosFn.apply(xt, self._pos_ln(self.text_temporal_pos_embed, p0, N, interpolate_from), B, N)
@@ -46,10 +48,12 @@ class GroundingModel(ExoGroundingTransformer):
         t_enc = self._text_unimodal_mean(xt, tmask, B, N, wT)
         distill = None
         if self.use_distill_nce_loss and egocentric_video_embed is not None:
-            proj = Fn.LinearFn.apply(Fn.CastFn.apply(v_enc, self.compute_dtype), self.exo_feature_proj.weight,
-                                     wT("exo_feature_proj.weight"), self.exo_feature_proj.bias, torch.float32)
-            distill = info_nce_bmm(proj.view(B, T, self.video_embed_dim), egocentric_video_embed, self.compute_dtype)
-        grounding = self._grounding(v_enc, t_enc, vmask, tmask, B, T, N, wT)
+            distill = info_nce_bmm(self._exo_proj(v_enc, B, T, wT), egocentric_video_embed, self.compute_dtype)
+        elif self.multi_view and self.use_pairwise_distill_nce_loss:          # reference :177-179
+            distill = pairwise_info_nce(self._exo_proj(v_enc, B, T, wT),
+                                        view_mask if self.pairwise_distill_mode == "all" else ~video_padding_mask,
+                                        self.num_max_views)
+        grounding = self._grounding(v_enc, t_enc, vmask, tmask, B, T, N, wT, a_feat, amask, interpolate_from)
         out = {'interval_preds': grounding}
         if self.use_distill_nce_loss or self.use_pairwise_distill_nce_loss:
             if distill is None:

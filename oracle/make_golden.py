@@ -256,6 +256,52 @@ def exo_case(r, name):
     print("keystep_small ok")
 
 
+def audio_pairwise_case(r, name):
+    """Audio branch without decoder (exo_ground_model.py:135-139,347-350; random positional start on, so the
+    draw order of np.random is pinned too) + the pairwise multi-view InfoNCE of GroundingModel
+    (keystep_ground_model.py:177-179,251-307), whose value and gradient are identically zero."""
+    Dv, Dt, Da, B, T, N, V = 48, 64, 40, 3, 16, 8, 2
+    b = synth.exo_batch(B=B, T=T, N=N, d_video=Dv, d_text=Dt)
+    g = torch.Generator().manual_seed(11)
+    audio = torch.randn(B, T, Da, generator=g)
+    amask = torch.zeros(B, T, dtype=torch.bool)
+    amask[1, T - 5:] = True
+    store = {"meta": np.array([2, 1, B, T, N, Dv, Dt, Da, V, 4], dtype=np.int64), "audio": _np(audio),
+             "amask": amask.numpy()}
+    with ref_import.quiet():
+        m = r.exo_ground_model.ExoGroundingTransformer(2, 1, use_decoder=False, use_audio=True, video_embed_dim=Dv,
+                                                       text_embed_dim=Dt, audio_embed_dim=Da, use_text_pos_enc=1)
+    m.load_state_dict(synth.fill_state_dict({k: v.shape for k, v in m.state_dict().items()}))
+    np.random.seed(4)
+    out = m(b["video_features"], b["narration_features"], b["video_padding_mask"], b["narration_padding_mask"],
+            audio_embed=audio, audio_padding_mask=amask)
+    for k, v in out.items():
+        store[f"out/{k}"] = _np(v)
+    w = torch.linspace(-1, 1, out["interval_preds"].numel()).view_as(out["interval_preds"])
+    ((out["interval_preds"] * w).sum() + out["low_dim_features"].square().mean()).backward()
+    _grads(m, store)
+    # pairwise InfoNCE through GroundingModel, both mask modes
+    view_mask = torch.ones(B, T, dtype=torch.bool)
+    view_mask[0, T // 2 + 3:] = False
+    store["view_mask"] = view_mask.numpy()
+    for mode in ("all", "unmasked"):
+        with ref_import.quiet():
+            gm = r.keystep_ground_model.GroundingModel(2, 1, video_embed_dim=Dv, text_embed_dim=Dt, multi_view=True,
+                                                       num_max_views=V, use_pairwise_distill_nce_loss=True,
+                                                       pairwise_distill_mode=mode, random_pos_start=0)
+        gm.load_state_dict(synth.fill_state_dict({k: v.shape for k, v in gm.state_dict().items()}))
+        out = gm(b["video_features"], b["narration_features"], b["video_padding_mask"],
+                 b["narration_padding_mask"], view_mask=view_mask)
+        store[f"pair_{mode}/interval_preds"] = _np(out["interval_preds"])
+        store[f"pair_{mode}/loss"] = _np(out["distill_infonce_loss"])
+        store[f"pair_{mode}/requires_grad"] = np.array(out["distill_infonce_loss"].requires_grad)
+        (out["interval_preds"].sum() + out["distill_infonce_loss"]).backward()
+        store[f"pair_{mode}/proj_grad_absmax"] = _np(gm.exo_feature_proj.weight.grad.abs().max())
+        store[f"pair_{mode}/head_grad"] = _np(gm.grounding_head.weight.grad)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), **store)
+    print(name, "ok", {k: float(v) for k, v in store.items() if k.endswith("/loss")})
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
@@ -269,6 +315,7 @@ def main():
     agree_case(r, "tan_agree")
     align_case(r, "tan_align")
     exo_case(r, "exo_small")
+    audio_pairwise_case(r, "exo_audio")
     tan_case(r, "tan_cfg1", 6, 6, 8, 64, 32, 1024, 888, [(0.0, 0, 0), (0.5, 1, 0)], sub_logits=(8, 4))
 
 

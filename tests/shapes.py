@@ -55,7 +55,7 @@ def tan_shapes(E, D, d_in=4096, head=0, pos_enc="learned"):
     return out
 
 
-def exo_shapes(E, D, d_video=4096, d_text=4096, distill=False, use_decoder=True):
+def exo_shapes(E, D, d_video=4096, d_text=4096, distill=False, use_decoder=True, d_audio=0):
     out = {"temporal_pos_embed": (1024, C), "text_temporal_pos_embed": (d_text, C)}
     _enc("multi_modal_encoder", E, out)
     if use_decoder:
@@ -71,6 +71,9 @@ def exo_shapes(E, D, d_video=4096, d_text=4096, distill=False, use_decoder=True)
     if distill:
         out["exo_feature_proj.weight"] = (d_video, C)
         out["exo_feature_proj.bias"] = (d_video,)
+    if d_audio:
+        _ln(["ln_audio_init"], out)
+        out["audio_pre_proj.weight"] = (C, d_audio)
     out["mlp.weight"] = (C, C)
     out["mlp.bias"] = (C,)
     return out

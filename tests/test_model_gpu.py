@@ -58,6 +58,13 @@ def test_keystep_small(golden_dir, dt):
 
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_exo_audio_and_pairwise(golden_dir, dt):
+    from tests.exo_cases import run_audio_pairwise_case
+    from tests.tan_cases import load_golden
+    run_audio_pairwise_case(load_golden(golden_dir, "exo_audio"), "cuda", dt)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 def test_vi_mlp_grads(dt):
     from tests.exo_cases import run_vi_mlp_grad_case
     run_vi_mlp_grad_case("cuda", dt)
