@@ -153,11 +153,14 @@ def time_cpu(B, steps, warmup, kind_pref="auto"):
             "ms_per_step": sec * 1e3}
 
 
-def workload_config(n_gpus, xneg=False, batch=0):
+def workload_config(n_gpus, xneg=False, batch=0, overlap=False):
     global PER_GPU_BATCH
     if batch:
         PER_GPU_BATCH = batch
     cfg = _workload_config(n_gpus)
+    if n_gpus > 1:
+        cfg["grad_allreduce"] = ("NCCL, per-block buckets (~25 MB) issued asynchronously during backward, inside the "
+                                 "step's CUDA graph" if overlap else "NCCL, one call after backward")
     if xneg and n_gpus > 1:
         cfg["parallelism"] = f"dp{n_gpus} + cross-GPU negatives (text features all-gathered; NCE over the global batch)"
     return cfg
@@ -169,6 +172,19 @@ def _workload_config(n_gpus):
             "global_batch": PER_GPU_BATCH * n_gpus, "per_gpu_batch": PER_GPU_BATCH, "seq_len": T,
             "parallelism": f"dp{n_gpus}", "loss": "loss_threshold=0.5, use_alignability_head=1",
             "l2": "no flush: per-step working set (2 x 403 MB bf16 logits + saved activations, > 3 GB) exceeds the 126 MB L2"}
+
+
+def nccl_options():
+    """Communicator options (experiments with the overlapped gradient all-reduce): EXG_NCCL_HIPRI=1 runs NCCL's
+    kernels on a high-priority stream, EXG_NCCL_MAX_CTAS=k caps their CTA count.  Default: NCCL's own choices, which
+    measured best (profiles/allreduce_overlap_r01.txt)."""
+    import torch.distributed as dist
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.is_high_priority_stream = os.environ.get("EXG_NCCL_HIPRI", "0") != "0"
+    max_ctas = int(os.environ.get("EXG_NCCL_MAX_CTAS", "0"))
+    if max_ctas > 0:
+        opts.config.max_ctas = max_ctas
+    return opts
 
 
 def run_reference(a):
@@ -205,7 +221,9 @@ def run_ours(a):
     dev = f"cuda:{local}"
     pg = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device(dev))
+        # NCCL writes its version / debug lines to stdout by default; stdout carries the ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        dist.init_process_group("nccl", device_id=torch.device(dev), pg_options=nccl_options())
         pg = dist.group.WORLD
     assert ops.get().name == "cuda"
     B = a.batch or PER_GPU_BATCH
@@ -216,7 +234,7 @@ def run_ours(a):
                             text_embed_dim=D_IN, compute_dtype=torch.bfloat16)
     args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
     tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg,
-                      cross_gpu_negatives=a.xneg)
+                      cross_gpu_negatives=a.xneg, overlap_allreduce=a.overlap)
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
@@ -317,7 +335,7 @@ def run_ours(a):
         gf = train_gflop_per_clip(B)
         line = {"metric": METRIC, "value": round(value, 1), "unit": "clips/s", "n_gpus": world, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world, a.xneg, a.batch),
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world, a.xneg, a.batch, a.overlap),
                 "e2e": {"value": round(gb / (ms_e2e * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_e2e, 4),
                         "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last},
                 "gpu_launches": int(launches_per_step * a.steps),
@@ -345,6 +363,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--overlap", action="store_true",
+                    help="N>1: per-block gradient buckets all-reduced asynchronously during backward instead of one "
+                         "all-reduce after it (measured: no gain, see DESIGN.md §6)")
     ap.add_argument("--xneg", action="store_true",
                     help="N > 1: cross-GPU negatives (text features all-gathered, NCE over the global batch; "
                          "train/xneg.py) instead of the DDP-equivalent local negatives")

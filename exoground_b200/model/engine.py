@@ -104,6 +104,7 @@ class EncoderStackFn(torch.autograd.Function):
         K = ops.get()
         B, S, L, T, shadows = meta[:5]
         ctx.sinks = meta[5] if len(meta) > 5 else None      # per-parameter gradient sinks (ENC_KEYS order) or None
+        ctx.hook = (meta[6], meta[7]) if len(meta) > 7 and meta[6] is not None else None
         M = B * S
         stages = torch.empty((L, M, C), dtype=T, device=x0.device)
         saved = []
@@ -159,6 +160,8 @@ class EncoderStackFn(torch.autograd.Function):
                 grads[12 * i:12 * i + 12] = [dW_in, db_in, dW_out, db_out, dg1, db1, dW_fc, db_fc, dW_pj, db_pj,
                                              dg2, db2]
             ctx.saved[i] = None
+            if ctx.hook is not None:        # block i's weight gradients are final in the trainer's flat buffer
+                ctx.hook[0](f"{ctx.hook[1]}resblocks.{i}.")
         return (dx, None, None, dg_post, db_post, *grads)
 
 

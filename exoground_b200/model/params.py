@@ -42,6 +42,8 @@ class FlatParams:
         self.n_no_decay = 0      # elements [0, n_no_decay) take no weight decay
         self.n_used = 0          # elements [n_no_decay, n_used) take weight decay; [n_used, end) never get a gradient
         self.unused = set()      # parameter names that receive no gradient (torch.optim skips them: grad is None)
+        self.layer_ranges = {}   # "<stack>.resblocks.<i>." -> (lo, hi): that block's weight-decayed matrices, contiguous
+        self.n_bucketed = 0      # elements [n_bucketed, n_used) are covered by layer_ranges (overlapped all-reduce)
         self._ptr_check = []
 
     def set_unused(self, names):
@@ -56,17 +58,30 @@ class FlatParams:
     def _layout(self):
         def cls(n):
             return 2 if n in self.unused else (0 if is_no_decay(n) else 1)
+
+        def order(n):
+            # decayed matrices of transformer blocks go last inside the decay segment, block by block, so a
+            # trainer can all-reduce one block's gradients as one contiguous range while backward continues
+            return (cls(n), 1 if (cls(n) == 1 and ".resblocks." in "." + n) else 0)
         named = own_named_parameters(self.module)
-        named.sort(key=lambda np_: cls(np_[0]))
+        named.sort(key=lambda np_: order(np_[0]))
         off = 0
         index = {}
         ends = [0, 0, 0]
+        ranges = {}
         for n, p in named:
             index[n] = (off, p.numel(), tuple(p.shape))
+            lo = off
             off += (p.numel() + ALIGN - 1) // ALIGN * ALIGN
             ends[cls(n)] = off
+            if order(n) == (1, 1):
+                pre = n[:n.index(".", n.index("resblocks.") + len("resblocks.")) + 1]
+                r = ranges.get(pre)
+                ranges[pre] = (lo, off) if r is None else (r[0], off)
         n_no_decay = ends[0]
         n_used = max(ends[0], ends[1])
+        self._ranges = ranges
+        self._n_bucketed = min((r[0] for r in ranges.values()), default=n_used)
         return named, index, off, n_no_decay, n_used
 
     def ensure(self):
@@ -84,6 +99,7 @@ class FlatParams:
             p.data = view
             self._ptr_check.append((p, p.data_ptr()))
         self.flat, self.index, self.n_no_decay, self.n_used = flat, index, n_no_decay, n_used
+        self.layer_ranges, self.n_bucketed = self._ranges, self._n_bucketed
         self.shadow = None
         self.grad = None
         return True

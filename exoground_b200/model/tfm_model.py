@@ -79,8 +79,10 @@ class TemporalEncoder(nn.Module):
             # a trainer owns (and zeroes) the .grad views: the backward kernels write into them directly
             if all(p.grad is not None and p.grad.dtype == torch.float32 and p.grad.is_contiguous() for p in params):
                 sinks = [p.grad for p in params]
-        return engine.EncoderStackFn.apply(x0, key_pad_u8, (B, S, self.layers, T, shadows, sinks), g_post, b_post,
-                                           *params)
+        # a data-parallel trainer may ask to be told when a block's gradients are final (overlapped all-reduce)
+        hook = getattr(self, "_grad_ready_hook", None) if sinks is not None else None
+        return engine.EncoderStackFn.apply(x0, key_pad_u8, (B, S, self.layers, T, shadows, sinks, hook, prefix),
+                                           g_post, b_post, *params)
 
 
 class TemporalDecoder(nn.Module):

@@ -46,11 +46,19 @@ def _worker(rank, world, port, q):
 
         # distributed run: this rank's batch only
         m, b = _make(rank)
-        st = TanTrainStep(m, args, B, T, N, DIN, DIN, process_group=dist.group.WORLD, **kw)
+        # (overlapped all-reduce: one asynchronous bucket per ~2 transformer blocks + the remainder at the end)
+        st = TanTrainStep(m, args, B, T, N, DIN, DIN, process_group=dist.group.WORLD, overlap_allreduce=True,
+                          bucket_mb=8.0, **kw)
         st.load_batch(b, non_blocking=False)
         st.prepare()
+        calls = []
+        orig_ar = dist.all_reduce
+        dist.all_reduce = lambda t, **k: (calls.append(t.numel()), orig_ar(t, **k))[1]
         loss0 = float(st.run())
+        dist.all_reduce = orig_ar
         fp = m.flat_params()
+        assert st._hooked and len(fp.layer_ranges) == E + D and len(calls) >= 3, (calls, fp.layer_ranges)
+        assert sum(calls) == fp.n_used and calls[-1] == fp.n_bucketed
         summed = fp.grad[:fp.n_used].clone()
 
         # single-process restatement: both ranks' gradients computed locally, mean applied
