@@ -368,6 +368,36 @@ class CudaBackend:
                                      _stream()), "exg_nce_bwd")
         return G
 
+    def tan_loss_tail(self, tgt, valid, sums_d, sums_j, own_max_d, own_max_j, la, abs_c, B, T, N, inv_temp,
+                      loss_threshold, use_head, nce_weight):
+        """Scalar tail of the TAN loss (train/loss.py:251-360) in two launches (csrc/loss_tail.cu).
+        tgt uint8 [B,N,T] (AND-ed with the valid sentences), valid uint8 [B*N]; sums_x = the four exp-sum views
+        returned by nce_fwd (rows [2,S,R] / cols [2,S,Cc] storage); own_max_x fp32 [B*N]; la fp32 [B*N] or None;
+        abs_c fp32 [B*N] or None.  Returns (out fp32 [16], w fp32 [5, L]) with L = padded max(R, Cc): rows of w =
+        wr_dual, wc_dual, wr_joint, wc_joint, d loss / d la."""
+        _cuda(tgt, valid, own_max_d, own_max_j, la, abs_c, *sums_d, *sums_j)
+        E, D = sums_d[0].shape[0], sums_j[0].shape[0]
+        R, Cc = B * T, B * N
+        dev = tgt.device
+        for sm, S in ((sums_d, E), (sums_j, D)):
+            ra, rp, ca, cp = sm
+            assert rp.data_ptr() == ra.data_ptr() + 4 * S * R and cp.data_ptr() == ca.data_ptr() + 4 * S * Cc, \
+                "tan_loss_tail expects the [2,S,R] / [2,S,Cc] buffers of nce_fwd"
+        Lp = (max(R, Cc) + 63) // 64 * 64
+        v = torch.empty((4, Lp), dtype=torch.float32, device=dev)
+        w = torch.zeros((5, Lp), dtype=torch.float32, device=dev)
+        out = torch.zeros(16, dtype=torch.float32, device=dev)
+        L.check(self.lib.exg_nce_logdiff(_p(sums_d[0]), _p(sums_d[2]), E, _p(sums_j[0]), _p(sums_j[2]), D, R, Cc,
+                                         _p(v[0]), _p(v[1]), _p(v[2]), _p(v[3]), _stream()), "exg_nce_logdiff")
+        nws = int(self.lib.exg_tan_loss_tail_workspace(B, T, N))
+        ws = torch.empty(nws, dtype=torch.uint8, device=dev)
+        L.check(self.lib.exg_tan_loss_tail(_p(tgt), _p(valid), _p(v[0]), _p(v[1]), _p(v[2]), _p(v[3]),
+                                           _p(own_max_d), _p(own_max_j), _p(la), _p(abs_c), B, T, N, E, D,
+                                           float(inv_temp), float(loss_threshold), int(bool(use_head)),
+                                           float(nce_weight), _p(w[0]), _p(w[1]), _p(w[2]), _p(w[3]), _p(w[4]),
+                                           _p(out), _p(ws), nws, _stream()), "exg_tan_loss_tail")
+        return out, w
+
     def own_max(self, logits, stage, B, T, N, Bc=None, clip0=0):
         _cuda(logits)
         out = torch.empty((B, N), dtype=torch.float32, device=logits.device)

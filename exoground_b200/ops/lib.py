@@ -78,6 +78,10 @@ _SIGS = {
     "exg_nce_bwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int,
                               C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp]),
     "exg_own_max": (C.c_int, [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
+    "exg_nce_logdiff": (C.c_int, [vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+    "exg_tan_loss_tail_workspace": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "exg_tan_loss_tail": (C.c_int, [vp] * 10 + [C.c_int] * 5 + [C.c_float, C.c_float, C.c_int, C.c_float] +
+                          [vp] * 7 + [C.c_size_t, vp]),
     "exg_adamw": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, C.c_float, C.c_float, C.c_float, C.c_float,
                             C.c_float, C.c_int, C.c_float, vp]),
     "exg_ema": (C.c_int, [vp, vp, C.c_long, C.c_float, vp]),

@@ -90,6 +90,34 @@ def _masked_standardise(x, mask):
     return (x - mean) / var.sqrt()
 
 
+class TanLossTailFn(torch.autograd.Function):
+    """loss = ((dual + joint) / 2) * nce_weight + BCE from the exp-sums of exg_nce_fwd (train/loss.py:251-376):
+    forward = exg_nce_logdiff + exg_tan_loss_tail, backward = one scale of the packed weights + two exg_nce_bwd."""
+
+    @staticmethod
+    def forward(ctx, ld, lj, la, meta):
+        K = ops.get()
+        (tgt3, col_valid, sums_d, sums_j, md, mj, abs_c, dims, th, use_head, nce_weight) = meta
+        B, T, N = dims[:3]
+        out, w = K.tan_loss_tail(tgt3[0], col_valid, sums_d, sums_j, md, mj,
+                                 la.contiguous() if la is not None else None, abs_c, B, T, N, INV_TEMP, th,
+                                 use_head, nce_weight)
+        ctx.saved = (ld, lj, tgt3, col_valid, sums_d, sums_j, w, dims, la is not None)
+        ctx.mark_non_differentiable(out)
+        return out[0].clone(), out
+
+    @staticmethod
+    def backward(ctx, g, _):
+        K = ops.get()
+        ld, lj, (tgt, bits, orm), col_valid, sums_d, sums_j, w, dims, has_la = ctx.saved
+        B, T, N = dims[:3]
+        R, Cc = B * T, B * N
+        wg = w * g
+        Gd = K.nce_bwd(ld, tgt, col_valid, sums_d, wg[0, :R], wg[1, :Cc], B, T, N, INV_TEMP, tgt_bits=bits)
+        Gj = K.nce_bwd(lj, tgt, col_valid, sums_j, wg[2, :R], wg[3, :Cc], B, T, N, INV_TEMP, tgt_bits=bits)
+        return Gd, Gj, (wg[4, :Cc] if has_la else None), None
+
+
 def get_loss(input_data, video_seq, text_embed, video_padding_mask, text_padding_mask, logits, args,
              abs_text_pos=None):
     """Same contract as reference train/loss.py::get_loss for args.model == 'init'
@@ -149,12 +177,6 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video
     tgt = tgt & valid[:, :, None]
     tgt_u8 = tgt.to(torch.uint8).contiguous()
     col_valid = valid_g.reshape(-1).to(torch.uint8).contiguous()
-    rowp = tgt.any(dim=1).reshape(-1)                                               # [B*T]   local rows
-    colp = gather(tgt.any(dim=2)).reshape(-1)                                       # [Bc*N]  global columns
-    # this rank's own columns: the only column terms it counts in its share of the loss value
-    cidx = torch.arange(Bc * N, device=ld.device)
-    own_cols = ((cidx >= clip0 * N) & (cidx < (clip0 + B) * N)).float() if grp is not None else None
-
     tgt_bits = K.nce_pack_targets(tgt_u8)          # per-(clip, second) bit rows, shared by the 4 NCE launches
     sums_d = K.nce_fwd(ld.detach(), tgt_u8, col_valid, B, T, N, INV_TEMP, tgt_bits=tgt_bits,
                        own_row_mask=own_row_mask, **shard)
@@ -164,11 +186,39 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video
         for t in (sums_d[2], sums_d[3], sums_j[2], sums_j[3]):
             grp.sum_(t)
     tgt_u8 = (tgt_u8, tgt_bits, own_row_mask)
-    wr_d, wc_d = _weights(rowp, colp, E, grp)
-    wr_j, wc_j = _weights(rowp, colp, D, grp)
     use_th = args.loss_threshold > 0
     use_head = bool(args.use_alignability_head)
     dims = (B, T, N, Bc, clip0)
+
+    if (use_th or use_head) and grp is None and own_row_mask is None and Bc * N <= 32768:
+        # fused tail: exp-sums -> masked means, quantile threshold, median-split labels, BCE and the backward
+        # weights in two launches (csrc/loss_tail.cu) instead of ~300 elementwise / reduction / sort launches
+        md = K.own_max(ld.detach(), E - 1, B, T, N)                                   # loss.py:283
+        mj = K.own_max(lj.detach(), D - 1, B, T, N)                                   # loss.py:285
+        la_j = abs_c = None
+        if use_head:
+            la_j = logits['joint_logits_alignability'][:, 2, :, 0].reshape(-1).float()   # 3rd stage hard-coded (:344)
+            if abs_text_pos is not None:
+                abs_c = abs_text_pos.reshape(B, N, -1).float().mean(-1).reshape(-1).contiguous()
+        nce_weight = 0 if args.optim_policy == 'bce' else 1
+        meta = (tgt_u8, col_valid, sums_d, sums_j, md, mj, abs_c, dims, float(args.loss_threshold) if use_th else 0.0,
+                use_head, nce_weight)
+        loss, out = TanLossTailFn.apply(ld, lj, la_j, meta)
+        loss_dict['loss-dual'], loss_dict['loss-joint'] = out[1], out[2]
+        if use_th:
+            loss_dict['loss-dual-all'], loss_dict['loss-joint-all'], loss_dict['loss-total'] = out[3], out[4], out[5]
+        if use_head:
+            loss_dict['loss-joint-bce'], loss_dict['alignability_top1'] = out[6], out[7]
+        loss_dict['loss'] = loss
+        return loss_dict
+
+    rowp = tgt.any(dim=1).reshape(-1)                                               # [B*T]   local rows
+    colp = gather(tgt.any(dim=2)).reshape(-1)                                       # [Bc*N]  global columns
+    # this rank's own columns: the only column terms it counts in its share of the loss value
+    cidx = torch.arange(Bc * N, device=ld.device)
+    own_cols = ((cidx >= clip0 * N) & (cidx < (clip0 + B) * N)).float() if grp is not None else None
+    wr_d, wc_d = _weights(rowp, colp, E, grp)
+    wr_j, wc_j = _weights(rowp, colp, D, grp)
 
     def nce(lg, sums, wr, wc):
         return NceLossFn.apply(lg, sums, tgt_u8, col_valid, wr, wc, dims, INV_TEMP, own_cols)

@@ -319,6 +319,66 @@ class TorchBackend:
             G = G - inv_temp * mpos * (lr_[..., None] + lc_[:, None, :])
         return G.to(g_dtype or logits.dtype)
 
+    def tan_loss_tail(self, tgt, valid, sums_d, sums_j, own_max_d, own_max_j, la, abs_c, B, T, N, inv_temp,
+                      loss_threshold, use_head, nce_weight):
+        """Spec of exg_nce_logdiff + exg_tan_loss_tail, written the way the reference computes it
+        (train/loss.py:251-360: boolean compaction, torch.quantile, Tensor.std, F.binary_cross_entropy_with_logits)."""
+        R, Cc = B * T, B * N
+        tg = tgt.bool().view(B, N, T)
+        vflat = valid.bool().view(-1)
+        rowp, colp = tg.any(dim=1).reshape(-1), tg.any(dim=2).reshape(-1)
+
+        def masked_mean_loss(sums, rmask, cmask):
+            ra, rp, ca, cp = sums
+            v = torch.log(ra) - torch.log(rp.clamp(min=1e-38))
+            t = torch.log(ca.clamp(min=1e-38)) - torch.log(cp.clamp(min=1e-38))
+            return (v[:, rmask].mean() + t[:, cmask].mean()) / 2
+
+        E, D = sums_d[0].shape[0], sums_j[0].shape[0]
+        ld_all, lj_all = masked_mean_loss(sums_d, rowp, colp), masked_mean_loss(sums_j, rowp, colp)
+        ld, lj, rmask, cmask = ld_all, lj_all, rowp, colp
+        md, mj = own_max_d.reshape(-1) * inv_temp, own_max_j.reshape(-1) * inv_temp
+        if loss_threshold > 0:
+            zd = (md - md[vflat].mean()) / md[vflat].std()
+            zj = (mj - mj[vflat].mean()) / mj[vflat].std()
+            metric = -(zd + zj)
+            keep = vflat & (metric <= torch.quantile(metric[vflat], loss_threshold))
+            rmask = (tg & keep.view(B, N, 1)).any(dim=1).reshape(-1)
+            cmask = keep
+            ld, lj = masked_mean_loss(sums_d, rmask, cmask), masked_mean_loss(sums_j, rmask, cmask)
+        Lp = (max(R, Cc) + 63) // 64 * 64
+        w = torch.zeros((5, Lp), dtype=torch.float32, device=tgt.device)
+        out = torch.zeros(16, dtype=torch.float32, device=tgt.device)
+        bce = top1 = torch.zeros((), device=tgt.device)
+        if use_head:
+            qd, qj = torch.quantile(md[vflat], 0.5), torch.quantile(mj[vflat], 0.5)
+            lab = torch.full_like(md, 2.0)
+            lab[(md > qd) & (mj > qj)] = 1.0
+            lab[(md < qd) & (mj < qj)] = 0.0
+            if abs_c is not None:
+                lab[(abs_c < 0.2) | (abs_c > 0.8)] = 0.0
+            sel = vflat & (lab != 2)
+            y = lab[sel]
+            x = la.detach().clone().requires_grad_(True)
+            with torch.enable_grad():
+                bce_t = torch.nn.functional.binary_cross_entropy_with_logits(x[sel], y, pos_weight=1 / y.mean() - 1)
+                bce_t.backward()
+            w[4, :Cc] = x.grad
+            bce = bce_t.detach()
+            top1 = ((x.detach()[sel] > 0).float() == y).float().mean()
+        scale = 0.5 * (nce_weight if use_head else 1.0)
+        nr, nc = rmask.float().sum(), cmask.float().sum()
+        w[0, :R] = rmask.float() * scale / (2 * E * nr)
+        w[1, :Cc] = cmask.float() * scale / (2 * E * nc)
+        w[2, :R] = rmask.float() * scale / (2 * D * nr)
+        w[3, :Cc] = cmask.float() * scale / (2 * D * nc)
+        loss = (ld + lj) / 2
+        if use_head:
+            loss = loss * nce_weight + bce
+        for i, val in enumerate((loss, ld, lj, ld_all, lj_all, (ld_all + lj_all) / 2, bce, top1, nr, nc, vflat.float().sum())):
+            out[i] = val
+        return out, w
+
     def own_max(self, logits, stage, B, T, N, Bc=None, clip0=0):
         Bc = B if Bc is None else Bc
         lg = logits[stage].float().view(B, T, Bc, N)

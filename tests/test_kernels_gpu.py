@@ -303,6 +303,41 @@ def test_nce(K, dt, S, B, T, N):
     _check(G, Gr, dt, "nce masked leak G")
 
 
+@pytest.mark.parametrize("th,head,use_abs,nce_w", [(0.5, 1, 0, 1), (0.3, 0, 0, 1), (0.0, 1, 1, 1), (0.5, 1, 1, 0),
+                                                   (0.7, 1, 0, 1)])
+@pytest.mark.parametrize("E,D,B,T,N", [(2, 3, 3, 16, 8), (6, 6, 128, 64, 32), (1, 2, 37, 9, 20), (3, 1, 512, 4, 40)])
+def test_tan_loss_tail(K, E, D, B, T, N, th, head, use_abs, nce_w):
+    """exg_nce_logdiff + exg_tan_loss_tail against the reference-style torch spec (boolean compaction,
+    torch.quantile, Tensor.std, F.binary_cross_entropy_with_logits): every logged scalar, the row / column weights
+    of the backward and d loss / d alignability logits."""
+    it = 1 / 0.07
+    tgt = (torch.rand((B, N, T), generator=_g(2)) < 0.15).to(torch.uint8).to(DEV)
+    cv = (torch.rand((B * N,), generator=_g(3)) < 0.8).to(torch.uint8).to(DEV)
+    tgt = (tgt * cv.view(B, N, 1)).contiguous()
+    sums = []
+    for S, seed in ((E, 11), (D, 12)):
+        Lg = (torch.rand((S, B * T, B * N), generator=_g(seed)) * 2 - 1).to(DEV)
+        sums.append((REF.nce_fwd(Lg, tgt, cv, B, T, N, it), REF.own_max(Lg, S - 1, B, T, N).contiguous()))
+        del Lg
+    def pack(sm):      # the [2,S,R] / [2,S,Cc] storage exg_nce_fwd writes
+        rows, cols = torch.stack((sm[0], sm[1])).contiguous(), torch.stack((sm[2], sm[3])).contiguous()
+        return rows[0], rows[1], cols[0], cols[1]
+    (sd, md), (sj, mj) = sums
+    sd, sj = pack(sd), pack(sj)
+    la = (torch.randn((B * N,), generator=_g(13)) * 2).to(DEV) if head else None
+    abs_c = torch.rand((B * N,), generator=_g(14)).to(DEV) if (use_abs and head) else None
+    out, w = K.tan_loss_tail(tgt, cv, sd, sj, md, mj, la, abs_c, B, T, N, it, th, head, nce_w)
+    ro, rw = REF.tan_loss_tail(tgt, cv, sd, sj, md, mj, la, abs_c, B, T, N, it, th, head, nce_w)
+    names = ("loss", "loss-dual", "loss-joint", "loss-dual-all", "loss-joint-all", "loss-total", "bce", "top1",
+             "n_rows", "n_cols", "n_valid")
+    for i, n in enumerate(names):
+        a, r = float(out[i]), float(ro[i])
+        assert abs(a - r) <= 2e-5 * max(1.0, abs(r)), (n, a, r)
+    for i, n in enumerate(("wr_d", "wc_d", "wr_j", "wc_j", "dla")):
+        assert torch.equal(w[i] != 0, rw[i] != 0) or n == "dla", n       # identical keep / row masks
+        _check(w[i], rw[i], torch.float32, "tail " + n)
+
+
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("S,W,B,T,N", [(2, 2, 3, 16, 8), (3, 4, 16, 64, 32), (2, 3, 5, 7, 12), (1, 8, 16, 64, 32)])
 def test_nce_row_blocks(K, dt, S, W, B, T, N):
