@@ -76,35 +76,54 @@ ln_fwd_kernel(const void* __restrict__ x, int xd, const float* __restrict__ gamm
 
 constexpr int kLnBwdThreads = 256;  // 8 warps
 
-template <int NCH>
+__device__ __forceinline__ float4 bf16x4_to_float4(uint2 u) {
+  float4 r;
+  r.x = __uint_as_float(u.x << 16);
+  r.y = __uint_as_float(u.x & 0xffff0000u);
+  r.z = __uint_as_float(u.y << 16);
+  r.w = __uint_as_float(u.y & 0xffff0000u);
+  return r;
+}
+
+// FAST = the training configuration (x fp32, dy1 / dy2 bf16): the prefetched dy chunks stay RAW bf16 bits in
+// registers and are converted / added when the row is consumed.  Converting inside fetch() (the generic path) makes
+// the warp wait for its own prefetch at issue time, which serialises load latency and reductions (ncu: 80 % of the
+// stall samples were long-scoreboard waits on the bf16 -> fp32 shifts, 19 % of DRAM peak).
+template <int NCH, bool FAST>
 __global__ void __launch_bounds__(kLnBwdThreads, 2)
 ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* __restrict__ dy2, int d2,
               exg_rowmap m2, const void* __restrict__ x, int xd, const float* __restrict__ gamma,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
               const float* __restrict__ dres, float* __restrict__ dx, void* __restrict__ dxT, int dxTd,
-              float* __restrict__ dgamma, float* __restrict__ dbeta, long rows, int C, float eps) {
+              float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dxsum, long rows, int C,
+              float eps) {
   // One warp per row, software-pipelined: the loads of the warp's next row (x, dy, residual gradient) are issued
   // before the reductions of the current one, so every warp keeps two rows of HBM traffic in flight.  The
   // dgamma / dbeta column partials live in this warp's slice of shared memory (conflict-free float4 RMW), which
   // is what leaves the registers for the prefetch.
-  extern __shared__ float red[];  // [warps][2*C]
+  // dxsum (optional): column sums of the OUTPUT rows = the bias gradient of the Linear whose output this
+  // residual stream receives (out_proj / c_proj bias: tfm_model.py:36-37), saving a separate pass over dx.
+  extern __shared__ float red[];  // [warps][NS*C], NS = 2 (+1 with dxsum)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nwarps = blockDim.x / 32;
   const bool want_cols = dgamma || dbeta;
-  float* rg = red + (size_t)warp * 2 * C;
-  if (want_cols) {
+  const int NS = dxsum ? 3 : 2;
+  float* rg = red + (size_t)warp * NS * C;
+  if (want_cols || dxsum) {
 #pragma unroll
     for (int j = 0; j < NCH; ++j) {
       const int col = (j * 32 + lane) * 4;
       if (col < C) {
         *reinterpret_cast<float4*>(rg + col) = make_float4(0.f, 0.f, 0.f, 0.f);
         *reinterpret_cast<float4*>(rg + C + col) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (dxsum) *reinterpret_cast<float4*>(rg + 2 * C + col) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
   }
   const long stride = (long)gridDim.x * nwarps;
   long row = (long)blockIdx.x * nwarps + warp;
   float4 nx[NCH], nd[NCH], nr[NCH];
+  uint2 q1[FAST ? NCH : 1], q2[FAST ? NCH : 1];      // FAST: raw bf16 bits of dy1 / dy2
   auto fetch = [&](long r) {
     const long r1 = exg_map_row(m1, r);
     const long r2 = dy2 ? exg_map_row(m2, r) : 0;
@@ -112,15 +131,23 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
     for (int j = 0; j < NCH; ++j) {
       const int col = (j * 32 + lane) * 4;
       if (col < C) {
-        nx[j] = load4(x, xd, r * C + col);
-        nd[j] = load4(dy1, d1, r1 * C + col);
-        if (dy2) {
-          const float4 t = load4(dy2, d2, r2 * C + col);
-          nd[j].x += t.x; nd[j].y += t.y; nd[j].z += t.z; nd[j].w += t.w;
+        if constexpr (FAST) {
+          nx[j] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(x) + r * C + col);
+          q1[j] = *reinterpret_cast<const uint2*>(reinterpret_cast<const uint16_t*>(dy1) + r1 * C + col);
+          q2[j] = dy2 ? *reinterpret_cast<const uint2*>(reinterpret_cast<const uint16_t*>(dy2) + r2 * C + col)
+                      : make_uint2(0u, 0u);
+        } else {
+          nx[j] = load4(x, xd, r * C + col);
+          nd[j] = load4(dy1, d1, r1 * C + col);
+          if (dy2) {
+            const float4 t = load4(dy2, d2, r2 * C + col);
+            nd[j].x += t.x; nd[j].y += t.y; nd[j].z += t.z; nd[j].w += t.w;
+          }
         }
         nr[j] = dres ? *reinterpret_cast<const float4*>(dres + r * C + col) : make_float4(0.f, 0.f, 0.f, 0.f);
       } else {
         nx[j] = nd[j] = nr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if constexpr (FAST) q1[j] = q2[j] = make_uint2(0u, 0u);
       }
     }
   };
@@ -128,7 +155,15 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
   for (; row < rows; row += stride) {
     float4 xv[NCH], dv[NCH], rv[NCH];
 #pragma unroll
-    for (int j = 0; j < NCH; ++j) { xv[j] = nx[j]; dv[j] = nd[j]; rv[j] = nr[j]; }
+    for (int j = 0; j < NCH; ++j) {
+      xv[j] = nx[j]; rv[j] = nr[j];
+      if constexpr (FAST) {
+        const float4 a = bf16x4_to_float4(q1[j]), b = bf16x4_to_float4(q2[j]);
+        dv[j] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+      } else {
+        dv[j] = nd[j];
+      }
+    }
     if (row + stride < rows) fetch(row + stride);
     float mean, rstd;
     if (mean_in && rstd_in) {
@@ -183,17 +218,23 @@ ln_bwd_kernel(const void* __restrict__ dy1, int d1, exg_rowmap m1, const void* _
         o.w = (dv[j].w - c1 - xv[j].w * c2) * rstd + rv[j].w;
         if (dx) *reinterpret_cast<float4*>(dx + row * C + col) = o;
         if (dxT) store4(dxT, dxTd, row * C + col, o);
+        if (dxsum) {
+          float4 a = *reinterpret_cast<float4*>(rg + 2 * C + col);
+          a.x += o.x; a.y += o.y; a.z += o.z; a.w += o.w;
+          *reinterpret_cast<float4*>(rg + 2 * C + col) = a;
+        }
       }
     }
   }
-  if (!want_cols) return;
+  if (!want_cols && !dxsum) return;
   // cross-warp reduction of the per-warp column partials, then one atomic per column per CTA
   __syncthreads();
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
+  for (int i = threadIdx.x; i < NS * C; i += blockDim.x) {
     float t = 0.f;
-    for (int w = 0; w < nwarps; ++w) t += red[(size_t)w * 2 * C + i];
+    for (int w = 0; w < nwarps; ++w) t += red[(size_t)w * NS * C + i];
     if (i < C) { if (dgamma) atomicAdd(dgamma + i, t); }
-    else       { if (dbeta) atomicAdd(dbeta + (i - C), t); }
+    else if (i < 2 * C) { if (dbeta) atomicAdd(dbeta + (i - C), t); }
+    else atomicAdd(dxsum + (i - 2 * C), t);
   }
 }
 
@@ -473,7 +514,7 @@ extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1
                                  int dy2_dtype, exg_rowmap map2, const void* x, int x_dtype,
                                  const float* gamma, const float* mean, const float* rstd,
                                  const float* dres, float* dx, void* dxT, int dxT_dtype, float* dgamma,
-                                 float* dbeta, long rows, int C, void* stream) {
+                                 float* dbeta, float* dxsum, long rows, int C, void* stream) {
   EXG_CHECK_ARG(dy1 && x && gamma, "layernorm_bwd: null pointer");
   EXG_CHECK_ARG(exg_valid_dtype(dy1_dtype) && exg_valid_dtype(dy2_dtype) && exg_valid_dtype(x_dtype) &&
                     exg_valid_dtype(dxT_dtype), "layernorm_bwd: bad dtype");
@@ -481,20 +522,22 @@ extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1
   EXG_CHECK_ARG(rowmap_ok(map1) && (!dy2 || rowmap_ok(map2)), "layernorm_bwd: bad row map");
   if (rows <= 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
-  const int threads = C > 2048 ? 128 : kLnBwdThreads;   // keeps the [warps][2C] reduction buffer under 227 KB
+  const int threads = C > 1024 ? 128 : kLnBwdThreads;   // keeps the [warps][3C] reduction buffer under 227 KB
+  EXG_CHECK_ARG(!dxsum || C <= 2048, "layernorm_bwd: dxsum needs C <= 2048");
   const int nwarps = threads / 32;
   long want = (rows + nwarps - 1) / nwarps;
   int blocks = (int)(want < 2L * exg_num_sms() ? want : 2L * exg_num_sms());
-  size_t smem = (size_t)nwarps * 2 * C * sizeof(float);
+  size_t smem = (size_t)nwarps * (dxsum ? 3 : 2) * C * sizeof(float);
   const float eps = 1e-5f;
+  const bool fast = x_dtype == EXG_F32 && dy1_dtype == EXG_BF16 && (!dy2 || dy2_dtype == EXG_BF16);
   ExgProfScope prof(EXG_PC_LN_BWD, (double)rows * C * (exg_dtype_size(x_dtype) + exg_dtype_size(dy1_dtype) + (dy2 ? exg_dtype_size(dy2_dtype) : 0) + (dres ? 4 : 0) + (dx ? 4 : 0) + (dxT ? exg_dtype_size(dxT_dtype) : 0)), stream);
 #define LN_BWD_CALL                                                                               \
   do {                                                                                            \
-    auto kfn = ln_bwd_kernel<NCH>;                                                                \
+    auto kfn = fast ? ln_bwd_kernel<NCH, true> : ln_bwd_kernel<NCH, false>;                       \
     if (smem > 48 * 1024) cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     kfn<<<blocks, threads, smem, s>>>(dy1, dy1_dtype, map1, dy2, dy2_dtype, map2, x, x_dtype, \
                                             gamma, mean, rstd, dres, dx, dxT, dxT_dtype, dgamma,  \
-                                            dbeta, rows, C, eps);                                 \
+                                            dbeta, dxsum, rows, C, eps);                          \
   } while (0)
   DISPATCH_NCH(C, LN_BWD_CALL);
 #undef LN_BWD_CALL

@@ -54,12 +54,12 @@ def _sk(sinks, i):
     return sinks[i] if sinks is not None else None
 
 
-def _self_attn_bwd(K, dxT, saved, xn, in_w, out_w, key_pad, B, S, sk=(None, None, None, None)):
+def _self_attn_bwd(K, dxT, saved, xn, in_w, out_w, key_pad, B, S, sk=(None, None, None, None), db_done=False):
     """dxT: grad of the block output of the attention residual branch, in T.  Returns
     (dxn T, dW_in, db_in, dW_out, db_out).  sk = gradient sinks (dW_in, db_in, dW_out, db_out): fp32 views of
     the trainer's flat gradient buffer that the kernels write / accumulate into directly (no autograd add)."""
     qkv, o, lse = saved
-    db_out = K.colsum(dxT, out=sk[3])
+    db_out = sk[3] if db_done else K.colsum(dxT, out=sk[3])     # db_done: the LayerNorm backward that made dxT summed it
     dW_out = K.gemm(dxT, o, transA=True, transB=True, out_dtype=torch.float32, out=sk[2])
     do = K.gemm(dxT, out_w, transB=True)
     dqkv = torch.empty_like(qkv)
@@ -78,10 +78,10 @@ def _ffn_fwd(K, h, fc_w, fc_b, proj_w, proj_b):
     return delta, (u, f)
 
 
-def _ffn_bwd(K, dxT, saved, h, fc_w, proj_w, sk=(None, None, None, None)):
+def _ffn_bwd(K, dxT, saved, h, fc_w, proj_w, sk=(None, None, None, None), db_done=False):
     """sk = gradient sinks (dW_fc, db_fc, dW_proj, db_proj)."""
     u, f = saved
-    db_proj = K.colsum(dxT, out=sk[3])
+    db_proj = sk[3] if db_done else K.colsum(dxT, out=sk[3])
     dW_proj = K.gemm(dxT, f, transA=True, transB=True, out_dtype=torch.float32, out=sk[2])
     du = K.gemm(dxT, proj_w, transB=True, epilogue=ops.EPI_QGELU_BWD, aux=u)
     db_fc = K.colsum(du, out=sk[1])
@@ -142,20 +142,28 @@ class EncoderStackFn(torch.autograd.Function):
         TT = None if T == torch.float32 else T
         grads = [None] * (12 * L)
         sinks = ctx.sinks
-        dx, dxT, dg_post, db_post = K.layernorm_bwd(d_stages[L - 1], ctx.x_last, ctx.post[0], dxT_dtype=TT)
+        # with gradient sinks the LayerNorm backward that PRODUCES a residual-stream gradient also accumulates its
+        # column sums into the bias gradient of the Linear feeding that stream (c_proj / out_proj), so those
+        # colsum passes disappear
+        fused = sinks is not None
+        dx, dxT, dg_post, db_post = K.layernorm_bwd(d_stages[L - 1], ctx.x_last, ctx.post[0], dxT_dtype=TT,
+                                                    dxsum_out=sinks[12 * (L - 1) + 9] if fused else None)
         for i in reversed(range(L)):
             (in_w, in_b, out_w, out_b, g1, b1, fc_w, fc_b, pj_w, pj_b, g2, b2) = params[12 * i:12 * i + 12]
             x_in, xn, att, x_mid, h, ffn, (in_wT, out_wT, fc_wT, pj_wT) = ctx.saved[i]
             sk = sinks[12 * i:12 * i + 12] if sinks is not None else [None] * 12
             dh, dW_fc, db_fc, dW_pj, db_pj = _ffn_bwd(K, dxT if TT else dx, ffn, h, fc_wT, pj_wT,
-                                                      (sk[6], sk[7], sk[8], sk[9]))
+                                                      (sk[6], sk[7], sk[8], sk[9]), db_done=fused)
             dxm, dxmT, dg2, db2 = K.layernorm_bwd(dh, x_mid, g2, dres=dx, dxT_dtype=TT,
-                                                  dg_out=(sk[10], sk[11]) if sk[10] is not None else None)
+                                                  dg_out=(sk[10], sk[11]) if sk[10] is not None else None,
+                                                  dxsum_out=sk[3] if fused else None)
             dxn, dW_in, db_in, dW_out, db_out = _self_attn_bwd(K, dxmT if TT else dxm, att, xn, in_wT, out_wT,
-                                                               key_pad, B, S, (sk[0], sk[1], sk[2], sk[3]))
+                                                               key_pad, B, S, (sk[0], sk[1], sk[2], sk[3]),
+                                                               db_done=fused)
             dx, dxT, dg1, db1 = K.layernorm_bwd(dxn, x_in, g1, dy2=d_stages[i - 1] if i > 0 else None,
                                                 dres=dxm, dxT_dtype=TT if i > 0 else None,
-                                                dg_out=(sk[4], sk[5]) if sk[4] is not None else None)
+                                                dg_out=(sk[4], sk[5]) if sk[4] is not None else None,
+                                                dxsum_out=sinks[12 * (i - 1) + 9] if fused and i > 0 else None)
             if sinks is None:
                 grads[12 * i:12 * i + 12] = [dW_in, db_in, dW_out, db_out, dg1, db1, dW_fc, db_fc, dW_pj, db_pj,
                                              dg2, db2]

@@ -131,10 +131,11 @@ class CudaBackend:
         return out, s
 
     def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
-                      want_dx=True, dg_out=None):
+                      want_dx=True, dg_out=None, dxsum_out=None):
         """Backward of y = LN(x)*gamma+beta with dy = dy1[map1] (+ dy2[map2]).
-        Returns (dx fp32 [rows,C] = dres + LN'(dy), dxT copy or None, dgamma fp32 [C], dbeta fp32 [C])."""
-        _cuda(dy1, x, gamma, dy2, dres)
+        Returns (dx fp32 [rows,C] = dres + LN'(dy), dxT copy or None, dgamma fp32 [C], dbeta fp32 [C]).
+        dxsum_out (fp32 [C], optional): the column sums of dx are ACCUMULATED into it (bias-gradient sink)."""
+        _cuda(dy1, x, gamma, dy2, dres, dxsum_out)
         rows, Cn = x.shape
         dx = torch.empty((rows, Cn), dtype=torch.float32, device=x.device) if want_dx else None
         dxT = torch.empty((rows, Cn), dtype=dxT_dtype, device=x.device) if dxT_dtype is not None else None
@@ -146,7 +147,7 @@ class CudaBackend:
                                            _dt(dy2.dtype) if dy2 is not None else 0, _rm(map2, rows), _p(x),
                                            _dt(x.dtype), _p(gamma), None, None, _p(dres), _p(dx), _p(dxT),
                                            _dt(dxT.dtype) if dxT is not None else 0, _p(dg[0]), _p(dg[1]),
-                                           rows, Cn, _stream()), "exg_layernorm_bwd")
+                                           _p(dxsum_out), rows, Cn, _stream()), "exg_layernorm_bwd")
         return dx, dxT, dg[0], dg[1]
 
     def add_rows(self, x, rows, *, map_x=None, x2=None, map_x2=None, add=None, add_period=0, out=None,

@@ -46,7 +46,7 @@ _SIGS = {
     "exg_add_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, RowMap, C.c_long, C.c_int,
                                         C.c_float, vp]),
     "exg_layernorm_bwd": (C.c_int, [vp, C.c_int, RowMap, vp, C.c_int, RowMap, vp, C.c_int, vp, vp, vp, vp,
-                                    vp, vp, C.c_int, vp, vp, C.c_long, C.c_int, vp]),
+                                    vp, vp, C.c_int, vp, vp, vp, C.c_long, C.c_int, vp]),
     "exg_add_rows": (C.c_int, [vp, RowMap, vp, RowMap, vp, C.c_long, vp, C.c_int, RowMap, vp, C.c_int,
                                C.c_long, C.c_int, vp]),
     "exg_l2norm_fwd": (C.c_int, [vp, C.c_int, RowMap, vp, C.c_int, vp, C.c_long, C.c_int, vp]),

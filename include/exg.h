@@ -109,13 +109,15 @@ int exg_add_layernorm_fwd(const void* x, int x_dtype, const float* resid, float*
                           long rows, int C, float eps, void* stream);
 /* LayerNorm backward.  dy = dy1[map1(r)] (+ dy2[map2(r)] if dy2);
  *   dx[r] = (dres ? dres[r] : 0) + LN'(dy)        written fp32 to dx and (optional) dtype copy dxT
- *   dgamma[C] += sum_r dy*xhat ; dbeta[C] += sum_r dy    (fp32 atomics: caller zero-initialises) */
+ *   dgamma[C] += sum_r dy*xhat ; dbeta[C] += sum_r dy    (fp32 atomics: caller zero-initialises)
+ *   dxsum[C] (optional) += sum_r dx[r]: the bias gradient of the Linear that feeds this residual stream
+ *   (out_proj / c_proj of model/tfm_model.py:36-37), produced without another pass over dx */
 int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1,
                       const void* dy2, int dy2_dtype, exg_rowmap map2,
                       const void* x, int x_dtype, const float* gamma,
                       const float* mean, const float* rstd, const float* dres,
                       float* dx, void* dxT, int dxT_dtype,
-                      float* dgamma, float* dbeta, long rows, int C, void* stream);
+                      float* dgamma, float* dbeta, float* dxsum, long rows, int C, void* stream);
 /* out[map_out(r)] = x[map_x(r)] + (add ? add[r % add_period] : 0) (+ x2[map_x2(r)] if x2); fp32 in,
  * out_dtype out.  Replaces `video_embed + ln_position_init(pos)` (tan_model.py:161,193) and torch.cat. */
 int exg_add_rows(const float* x, exg_rowmap map_x, const float* x2, exg_rowmap map_x2,

@@ -80,7 +80,7 @@ class TorchBackend:
         return y, s
 
     def layernorm_bwd(self, dy1, x, gamma, *, map1=None, dy2=None, map2=None, dres=None, dxT_dtype=None,
-                      want_dx=True, dg_out=None):
+                      want_dx=True, dg_out=None, dxsum_out=None):
         rows, C = x.shape
         dy = dy1.view(-1, C)[_map_idx(map1, rows, x.device)].float()
         if dy2 is not None:
@@ -95,6 +95,8 @@ class TorchBackend:
         if dres is not None:
             dx = dx + dres
         dxT = dx.to(dxT_dtype) if dxT_dtype is not None else None
+        if dxsum_out is not None:
+            dxsum_out.add_(dx.sum(0))
         dgam, dbet = (dy * xhat).sum(0), dy.sum(0)
         if dg_out is not None:
             dg_out[0].add_(dgam); dg_out[1].add_(dbet)

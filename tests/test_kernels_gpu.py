@@ -157,6 +157,32 @@ def test_layernorm_fwd_bwd(K, xd, yd, C):
     _check(got[1], ref[1], torch.bfloat16, "ln dxT")
     _check(got[2], ref[2], torch.float32 if yd == torch.float32 and xd == torch.float32 else torch.bfloat16, "ln dgamma")
     _check(got[3], ref[3], torch.float32 if yd == torch.float32 else torch.bfloat16, "ln dbeta")
+    if C <= 2048:       # fused bias-gradient sink: column sums of dx accumulated into a caller buffer
+        acc = _rand((C,), torch.float32, 8)
+        accr = acc.clone()
+        K.layernorm_bwd(dy1, x, g, dy2=dy2, dres=dres, dxT_dtype=torch.bfloat16, dxsum_out=acc)
+        REF.layernorm_bwd(dy1, x, g, dy2=dy2, dres=dres, dxT_dtype=torch.bfloat16, dxsum_out=accr)
+        _check(acc, accr, torch.float32 if xd == torch.float32 and yd == torch.float32 else torch.bfloat16, "ln dxsum")
+
+
+@pytest.mark.parametrize("rows", [5, 8192, 12288 + 3])
+def test_layernorm_bwd_pipelined_bf16(K, rows):
+    """The training configuration (x fp32, dy1 / dy2 bf16, raw-bits prefetch) over many rows per warp."""
+    C = 512
+    x = _rand((rows, C), torch.float32, 1, 2.0)
+    g = 1 + 0.1 * _rand((C,), torch.float32, 2)
+    dy1, dy2 = _rand((rows, C), torch.bfloat16, 5), _rand((rows, C), torch.bfloat16, 6)
+    dres = _rand((rows, C), torch.float32, 7)
+    for d2 in (dy2, None):
+        acc = torch.zeros(C, device=DEV)
+        accr = torch.zeros(C, device=DEV)
+        got = K.layernorm_bwd(dy1, x, g, dy2=d2, dres=dres, dxT_dtype=torch.bfloat16, dxsum_out=acc)
+        ref = REF.layernorm_bwd(dy1, x, g, dy2=d2, dres=dres, dxT_dtype=torch.bfloat16, dxsum_out=accr)
+        _check(got[0], ref[0], torch.float32, "ln dx")
+        _check(got[1], ref[1], torch.bfloat16, "ln dxT")
+        _check(got[2], ref[2], torch.float32, "ln dgamma")
+        _check(got[3], ref[3], torch.float32, "ln dbeta")
+        _check(acc, accr, torch.float32, "ln dxsum")
 
 
 def test_layernorm_rowmaps(K):
