@@ -9,9 +9,10 @@
 //     and its top-1 accuracy                                                                  (loss.py:309-360)
 // as ~300 tiny elementwise / reduction / sort launches.  Here:
 //   exg_nce_logdiff : grid-wide, vr[r] = sum_s (log row_all - log row_pos), tc[c] = sum_s (log col_all - log col_pos)
-//   exg_tan_loss_tail: ONE CTA (1024 threads): masks, counts, weighted sums, three bitonic-sort quantiles in shared
-//                      memory, BCE value + gradient, and the row / column weights exg_nce_bwd needs.
-// HBM-/latency-bound: (2R + 2Cc) * S * 8 B read by the first, ~(B*N*T + 6 Cc + 2R) * 4 B by the second.
+//   exg_tan_loss_tail: ONE CTA (1024 threads): row / column masks from the packed target bit rows, counts, weighted
+//                      sums, three quantiles by 8-bit radix selection (shared-memory histograms), BCE value +
+//                      gradient, and the row / column weights exg_nce_bwd needs.
+// Latency-bound: (2R + 2Cc) * S * 8 B read by the first, ~(2 R W + 8 Cc + 4 R) * 4 B by the second.
 #include "common.cuh"
 
 namespace {
@@ -59,43 +60,102 @@ __device__ float block_sum(float v, float* red) {
   return red[32];
 }
 
-// ascending bitonic sort of buf[0, P) (P a power of two) in shared memory
-__device__ void bitonic_sort(float* buf, int P) {
-  for (int k = 2; k <= P; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      __syncthreads();
-      for (int i = threadIdx.x; i < P; i += NT) {
-        const int l = i ^ j;
-        if (l > i) {
-          const float a = buf[i], b = buf[l];
-          const bool up = (i & k) == 0;
-          if ((a > b) == up) { buf[i] = b; buf[l] = a; }
+__device__ float block_min(float v, float* red) {
+  v = -warp_max(-v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = threadIdx.x < NT / 32 ? red[threadIdx.x] : INFINITY;
+  if (threadIdx.x < 32) {
+    t = -warp_max(-t);
+    if (threadIdx.x == 0) red[32] = t;
+  }
+  __syncthreads();
+  return red[32];
+}
+
+__device__ __forceinline__ uint32_t sort_key(float x) {      // monotone float -> uint32 (ascending)
+  const uint32_t u = __float_as_uint(x);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_value(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// k-th smallest (0-based) of {x[i] : mask[i]} by 4 passes of 8-bit radix selection: shared-memory histogram of the
+// candidates that still match the selected prefix, warp-parallel scan for the bin holding rank k.
+__device__ float radix_select(const float* x, const uint8_t* mask, int Cc, int k, uint32_t* hist, float* red) {
+  uint32_t prefix = 0, pmask = 0;
+  __shared__ uint32_t sel[2];
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    __syncthreads();
+    if (threadIdx.x < 256) hist[threadIdx.x] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < Cc; i += NT) {
+      if (!mask[i]) continue;
+      const uint32_t key = sort_key(x[i]);
+      if ((key & pmask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      uint32_t h[8], tot = 0;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { h[j] = hist[threadIdx.x * 8 + j]; tot += h[j]; }
+      uint32_t incl = tot;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)threadIdx.x >= o) incl += t;
+      }
+      uint32_t before = incl - tot;                 // candidates in lower bins
+      if ((uint32_t)k >= before && (uint32_t)k < incl) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          if ((uint32_t)k < before + h[j]) { sel[0] = threadIdx.x * 8 + j; sel[1] = before; break; }
+          before += h[j];
         }
       }
     }
+    __syncthreads();
+    prefix |= sel[0] << shift;
+    pmask |= 255u << shift;
+    k -= (int)sel[1];
   }
-  __syncthreads();
+  (void)red;
+  return key_value(prefix);
 }
 
-// torch.quantile(x[mask], q) with linear interpolation, the way train/loss.py::_masked_quantile restates it:
-// sort with +inf in the masked slots, pos = (n-1)*q, lo = floor(pos), hi = min(lo+1, n-1), a + (b-a)*(pos-lo)
-__device__ float masked_quantile(const float* x, const uint8_t* mask, int Cc, int P, float n, float q, float* buf) {
-  __syncthreads();
-  for (int i = threadIdx.x; i < P; i += NT) buf[i] = (i < Cc && mask[i]) ? x[i] : INFINITY;
-  bitonic_sort(buf, P);
+// torch.quantile(x[mask], q) with linear interpolation: pos = (n-1)*q, lo = floor(pos), hi = min(lo+1, n-1),
+// v_lo + (v_hi - v_lo)*(pos - lo) over the sorted valid values (train/loss.py:289, :315-316).  v_lo by radix
+// selection; v_hi = v_lo if it has a duplicate at rank lo+1, else the smallest value above v_lo.
+__device__ float masked_quantile(const float* x, const uint8_t* mask, int Cc, float n, float q, uint32_t* hist,
+                                 float* red) {
   const float pos = (n - 1.f) * q;
   int lo = (int)floorf(pos);
   lo = lo < 0 ? 0 : lo;
   int last = (int)n - 1;
   last = last < 0 ? 0 : last;
+  lo = min(lo, last);
   const int hi = min(lo + 1, last);
   const float w = pos - (float)lo;
-  const float a = buf[min(lo, P - 1)], b = buf[hi];
+  const float a = radix_select(x, mask, Cc, lo, hist, red);
+  float b = a;
+  if (hi > lo) {
+    float cnt = 0.f, mn = INFINITY;
+    for (int i = threadIdx.x; i < Cc; i += NT) {
+      if (!mask[i]) continue;
+      const float v = x[i];
+      if (v <= a) cnt += 1.f; else mn = fminf(mn, v);
+    }
+    cnt = block_sum(cnt, red);
+    mn = block_min(mn, red);
+    b = (cnt >= (float)(lo + 2)) ? a : mn;
+  }
   return a + (b - a) * w;
 }
 
 struct TailArgs {
-  const uint8_t* tgt;      // [B,N,T], already AND-ed with the valid sentences
+  const uint32_t* bits;    // exg_nce_pack_targets([B,N,T] targets AND-ed with the valid sentences): [B*T][W]
   const uint8_t* valid;    // [B*N]
   const float *vr_d, *tc_d, *vr_j, *tc_j;
   const float *md, *mj;    // [B*N] raw per-sentence maxima (scaled by inv_temp here)
@@ -105,33 +165,40 @@ struct TailArgs {
   uint8_t* flags;          // [R + 2*Cc] scratch: rowp / rowp_th, colp, keep
   float *wr_d, *wc_d, *wr_j, *wc_j, *dla;   // outputs consumed by the backward
   float* out;              // [16] scalars
-  int B, T, N, E, D, P;
+  int B, T, N, E, D, W;
   float inv_temp, q;       // q <= 0: no threshold
   int use_head;
   float nce_weight;
 };
 
 __global__ void __launch_bounds__(NT, 1) tan_loss_tail_kernel(TailArgs a) {
-  extern __shared__ float buf[];          // P floats for the sorts
+  extern __shared__ uint32_t cbits[];     // [2][B*W]: per-clip OR of the target bit rows | kept-sentence bits
   __shared__ float red[33];
-  const int B = a.B, T = a.T, N = a.N, R = B * T, Cc = B * N;
+  __shared__ uint32_t hist[256];
+  const int B = a.B, T = a.T, N = a.N, W = a.W, R = B * T, Cc = B * N;
   const int tid = threadIdx.x;
   uint8_t* rowp = a.flags;
   uint8_t* colp = a.flags + R;
   uint8_t* keep = a.flags + R + Cc;
+  uint32_t* kbits = cbits + B * W;
   const bool use_th = a.q > 0.f;
 
-  // ---- rows / columns with at least one positive (loss.py:247-250)
+  // ---- rows / columns with at least one positive (loss.py:247-250), from the packed target rows
+  for (int i = tid; i < 2 * B * W; i += NT) cbits[i] = 0;
+  __syncthreads();
   for (int r = tid; r < R; r += NT) {
-    const int b = r / T, t = r % T;
-    int any = 0;
-    for (int n = 0; n < N; ++n) any |= a.tgt[((size_t)b * N + n) * T + t];
+    uint32_t any = 0;
+    for (int w = 0; w < W; ++w) {
+      const uint32_t v = a.bits[(size_t)r * W + w];
+      any |= v;
+      if (v) atomicOr(&cbits[(r / T) * W + w], v);
+    }
     rowp[r] = any != 0;
   }
+  __syncthreads();
   for (int c = tid; c < Cc; c += NT) {
-    int any = 0;
-    for (int t = 0; t < T; ++t) any |= a.tgt[(size_t)c * T + t];
-    colp[c] = any != 0;
+    const int b = c / N, n = c % N;
+    colp[c] = (cbits[b * W + (n >> 5)] >> (n & 31)) & 1u;
   }
   __syncthreads();
   float nr = 0.f, nc = 0.f, nv = 0.f;
@@ -166,14 +233,18 @@ __global__ void __launch_bounds__(NT, 1) tan_loss_tail_kernel(TailArgs a) {
       if (a.valid[c]) { const float u = md[c] - mean_d, v = mj[c] - mean_j; s1 += u * u; s2 += v * v; }
     const float sd_d = sqrtf(block_sum(s1, red) / (nv - 1.f)), sd_j = sqrtf(block_sum(s2, red) / (nv - 1.f));
     for (int c = tid; c < Cc; c += NT) metric[c] = -((md[c] - mean_d) / sd_d + (mj[c] - mean_j) / sd_j);
-    const float qv = masked_quantile(metric, a.valid, Cc, a.P, nv, a.q, buf);
     __syncthreads();
-    for (int c = tid; c < Cc; c += NT) keep[c] = a.valid[c] && (metric[c] <= qv);
+    const float qv = masked_quantile(metric, a.valid, Cc, nv, a.q, hist, red);
+    __syncthreads();
+    for (int c = tid; c < Cc; c += NT) {
+      const bool k = a.valid[c] && (metric[c] <= qv);
+      keep[c] = k;
+      if (k) atomicOr(&kbits[(c / N) * W + ((c % N) >> 5)], 1u << ((c % N) & 31));
+    }
     __syncthreads();
     for (int r = tid; r < R; r += NT) {
-      const int b = r / T, t = r % T;
-      int any = 0;
-      for (int n = 0; n < N; ++n) any |= (a.tgt[((size_t)b * N + n) * T + t] & keep[b * N + n]);
+      uint32_t any = 0;
+      for (int w = 0; w < W; ++w) any |= a.bits[(size_t)r * W + w] & kbits[(r / T) * W + w];
       rowp[r] = any != 0;                   // rowp now holds the thresholded row mask
     }
     __syncthreads();
@@ -193,8 +264,9 @@ __global__ void __launch_bounds__(NT, 1) tan_loss_tail_kernel(TailArgs a) {
   // ---- alignability labels + BCE (loss.py:309-360)
   float bce = 0.f, top1 = 0.f;
   if (a.use_head) {
-    const float qd = masked_quantile(md, a.valid, Cc, a.P, nv, 0.5f, buf);
-    const float qj = masked_quantile(mj, a.valid, Cc, a.P, nv, 0.5f, buf);
+    __syncthreads();
+    const float qd = masked_quantile(md, a.valid, Cc, nv, 0.5f, hist, red);
+    const float qj = masked_quantile(mj, a.valid, Cc, nv, 0.5f, hist, red);
     __syncthreads();
     float nsel = 0.f, ysum = 0.f;
     for (int c = tid; c < Cc; c += NT) {
@@ -265,38 +337,31 @@ extern "C" size_t exg_tan_loss_tail_workspace(int B, int T, int N) {
   return 3 * Cc * sizeof(float) + (R + 2 * Cc + 15) / 16 * 16;
 }
 
-extern "C" int exg_tan_loss_tail(const uint8_t* tgt, const uint8_t* valid, const float* vr_d, const float* tc_d,
+extern "C" int exg_tan_loss_tail(const uint32_t* tgt_bits, const uint8_t* valid, const float* vr_d, const float* tc_d,
                                  const float* vr_j, const float* tc_j, const float* own_max_d, const float* own_max_j,
                                  const float* la, const float* abs_c, int B, int T, int N, int E, int D,
                                  float inv_temp, float loss_threshold, int use_head, float nce_weight, float* wr_d,
                                  float* wc_d, float* wr_j, float* wc_j, float* dla, float* out, void* ws,
                                  size_t ws_bytes, void* stream) {
-  EXG_CHECK_ARG(tgt && valid && vr_d && tc_d && vr_j && tc_j && own_max_d && own_max_j && wr_d && wc_d && wr_j &&
+  EXG_CHECK_ARG(tgt_bits && valid && vr_d && tc_d && vr_j && tc_j && own_max_d && own_max_j && wr_d && wc_d && wr_j &&
                 wc_j && out && ws, "tan_loss_tail: null pointer");
   EXG_CHECK_ARG(B > 0 && T > 0 && N > 0 && E > 0 && D > 0, "tan_loss_tail: bad sizes");
   EXG_CHECK_ARG(!use_head || (la && dla), "tan_loss_tail: the alignability head needs la and dla");
   EXG_CHECK_ARG(ws_bytes >= exg_tan_loss_tail_workspace(B, T, N), "tan_loss_tail: workspace too small");
   const long Cc = (long)B * N;
-  int P = 1;
-  while (P < Cc) P <<= 1;
-  if (P > 32768) {
-    exg_set_error("tan_loss_tail: %ld sentences exceed the 32768-entry shared-memory sort", Cc);
-    return EXG_EUNSUPPORTED;
-  }
+  const int W = (N + 31) / 32;
+  const size_t smem = (size_t)2 * B * W * sizeof(uint32_t);
+  EXG_CHECK_ARG(smem <= 160 * 1024, "tan_loss_tail: B*ceil(N/32) = %d too large for the per-clip bit rows", B * W);
   TailArgs a = {};
-  a.tgt = tgt; a.valid = valid; a.vr_d = vr_d; a.tc_d = tc_d; a.vr_j = vr_j; a.tc_j = tc_j;
+  a.bits = tgt_bits; a.valid = valid; a.vr_d = vr_d; a.tc_d = tc_d; a.vr_j = vr_j; a.tc_j = tc_j;
   a.md = own_max_d; a.mj = own_max_j; a.la = la; a.abs_c = abs_c;
   a.ws = (float*)ws; a.flags = (uint8_t*)ws + 3 * Cc * sizeof(float);
   a.wr_d = wr_d; a.wc_d = wc_d; a.wr_j = wr_j; a.wc_j = wc_j; a.dla = dla; a.out = out;
-  a.B = B; a.T = T; a.N = N; a.E = E; a.D = D; a.P = P;
+  a.B = B; a.T = T; a.N = N; a.E = E; a.D = D; a.W = W;
   a.inv_temp = inv_temp; a.q = loss_threshold; a.use_head = use_head; a.nce_weight = nce_weight;
-  const size_t smem = (size_t)P * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set) {
-    EXG_CUDA(cudaFuncSetAttribute(tan_loss_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4));
-    attr_set = true;
-  }
-  ExgProfScope prof(EXG_PC_ROWWISE, (double)B * N * T * 2.0 + (double)(B * T + Cc) * 8.0 * 4.0, stream);
+  if (smem > 40 * 1024)
+    EXG_CUDA(cudaFuncSetAttribute(tan_loss_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ExgProfScope prof(EXG_PC_ROWWISE, (double)B * T * W * 8.0 + (double)(B * T + Cc) * 8.0 * 4.0, stream);
   tan_loss_tail_kernel<<<1, NT, smem, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("tan_loss_tail");
   return 0;

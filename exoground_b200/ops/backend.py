@@ -370,13 +370,15 @@ class CudaBackend:
         return G
 
     def tan_loss_tail(self, tgt, valid, sums_d, sums_j, own_max_d, own_max_j, la, abs_c, B, T, N, inv_temp,
-                      loss_threshold, use_head, nce_weight):
+                      loss_threshold, use_head, nce_weight, tgt_bits=None):
         """Scalar tail of the TAN loss (train/loss.py:251-360) in two launches (csrc/loss_tail.cu).
         tgt uint8 [B,N,T] (AND-ed with the valid sentences), valid uint8 [B*N]; sums_x = the four exp-sum views
         returned by nce_fwd (rows [2,S,R] / cols [2,S,Cc] storage); own_max_x fp32 [B*N]; la fp32 [B*N] or None;
         abs_c fp32 [B*N] or None.  Returns (out fp32 [16], w fp32 [5, L]) with L = padded max(R, Cc): rows of w =
         wr_dual, wc_dual, wr_joint, wc_joint, d loss / d la."""
-        _cuda(tgt, valid, own_max_d, own_max_j, la, abs_c, *sums_d, *sums_j)
+        _cuda(tgt, valid, own_max_d, own_max_j, la, abs_c, tgt_bits, *sums_d, *sums_j)
+        if tgt_bits is None:
+            tgt_bits = self.nce_pack_targets(tgt)
         E, D = sums_d[0].shape[0], sums_j[0].shape[0]
         R, Cc = B * T, B * N
         dev = tgt.device
@@ -392,7 +394,7 @@ class CudaBackend:
                                          _p(v[0]), _p(v[1]), _p(v[2]), _p(v[3]), _stream()), "exg_nce_logdiff")
         nws = int(self.lib.exg_tan_loss_tail_workspace(B, T, N))
         ws = torch.empty(nws, dtype=torch.uint8, device=dev)
-        L.check(self.lib.exg_tan_loss_tail(_p(tgt), _p(valid), _p(v[0]), _p(v[1]), _p(v[2]), _p(v[3]),
+        L.check(self.lib.exg_tan_loss_tail(_p(tgt_bits), _p(valid), _p(v[0]), _p(v[1]), _p(v[2]), _p(v[3]),
                                            _p(own_max_d), _p(own_max_j), _p(la), _p(abs_c), B, T, N, E, D,
                                            float(inv_temp), float(loss_threshold), int(bool(use_head)),
                                            float(nce_weight), _p(w[0]), _p(w[1]), _p(w[2]), _p(w[3]), _p(w[4]),

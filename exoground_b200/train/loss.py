@@ -101,7 +101,7 @@ class TanLossTailFn(torch.autograd.Function):
         B, T, N = dims[:3]
         out, w = K.tan_loss_tail(tgt3[0], col_valid, sums_d, sums_j, md, mj,
                                  la.contiguous() if la is not None else None, abs_c, B, T, N, INV_TEMP, th,
-                                 use_head, nce_weight)
+                                 use_head, nce_weight, tgt_bits=tgt3[1])
         ctx.saved = (ld, lj, tgt3, col_valid, sums_d, sums_j, w, dims, la is not None)
         ctx.mark_non_differentiable(out)
         return out[0].clone(), out
@@ -190,7 +190,7 @@ def loss_core(tgt, text_padding_mask, logits, args, abs_text_pos, B, T, N, video
     use_head = bool(args.use_alignability_head)
     dims = (B, T, N, Bc, clip0)
 
-    if (use_th or use_head) and grp is None and own_row_mask is None and Bc * N <= 32768:
+    if (use_th or use_head) and grp is None and own_row_mask is None:
         # fused tail: exp-sums -> masked means, quantile threshold, median-split labels, BCE and the backward
         # weights in two launches (csrc/loss_tail.cu) instead of ~300 elementwise / reduction / sort launches
         md = K.own_max(ld.detach(), E - 1, B, T, N)                                   # loss.py:283

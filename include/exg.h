@@ -208,7 +208,8 @@ int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B,
  * elementwise / reduction / sort launches.
  *   exg_nce_logdiff: rows_x = [2,S,R] (row_all | row_pos), cols_x = [2,S,Cc] as written by exg_nce_fwd;
  *     vr_x[r] = sum_s log(row_all) - log(max(row_pos, 1e-38)),  tc_x[c] = sum_s log(max(col_all, 1e-38)) - log(max(col_pos, 1e-38))
- *   exg_tan_loss_tail (one CTA): tgt [B,N,T] (already AND-ed with the valid sentences), valid [B*N],
+ *   exg_tan_loss_tail (one CTA): tgt_bits = exg_nce_pack_targets of the [B,N,T] targets (already AND-ed with the
+ *     valid sentences), valid [B*N],
  *     own_max_x [B*N] = exg_own_max of the last stage, la = alignability logits [B*N] (null without the head),
  *     abs_c = mean absolute text position [B*N] or null.  loss_threshold <= 0 disables the quantile re-weighting
  *     (loss.py:280-307); use_head enables the median-split BCE (loss.py:309-360).
@@ -218,7 +219,7 @@ int exg_own_max(const void* logits, int dtype, float* own_max, int stage, int B,
 int exg_nce_logdiff(const float* rows_d, const float* cols_d, int E, const float* rows_j, const float* cols_j, int D,
                     int R, int Cc, float* vr_d, float* tc_d, float* vr_j, float* tc_j, void* stream);
 size_t exg_tan_loss_tail_workspace(int B, int T, int N);
-int exg_tan_loss_tail(const uint8_t* tgt, const uint8_t* valid, const float* vr_d, const float* tc_d,
+int exg_tan_loss_tail(const uint32_t* tgt_bits, const uint8_t* valid, const float* vr_d, const float* tc_d,
                       const float* vr_j, const float* tc_j, const float* own_max_d, const float* own_max_j,
                       const float* la, const float* abs_c, int B, int T, int N, int E, int D, float inv_temp,
                       float loss_threshold, int use_head, float nce_weight, float* wr_d, float* wc_d, float* wr_j,

@@ -322,7 +322,7 @@ class TorchBackend:
         return G.to(g_dtype or logits.dtype)
 
     def tan_loss_tail(self, tgt, valid, sums_d, sums_j, own_max_d, own_max_j, la, abs_c, B, T, N, inv_temp,
-                      loss_threshold, use_head, nce_weight):
+                      loss_threshold, use_head, nce_weight, tgt_bits=None):
         """Spec of exg_nce_logdiff + exg_tan_loss_tail, written the way the reference computes it
         (train/loss.py:251-360: boolean compaction, torch.quantile, Tensor.std, F.binary_cross_entropy_with_logits)."""
         R, Cc = B * T, B * N
