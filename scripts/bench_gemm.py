@@ -29,6 +29,9 @@ SHAPES += [
     (1536, 512, 12288, 1, 1, L.EPI_NONE, 0, 1, "dW_in splitK"),
     (12288, 512, 512, 0, 0, L.EPI_NONE, 1, 0, "out_proj 12288"),
 ]
+if os.environ.get("ONLY"):
+    SHAPES = [x for x in SHAPES if any(k in x[8] for k in os.environ["ONLY"].split(","))]
+PRE = bool(os.environ.get("PRE"))      # c_fc also writes the pre-activation (training forward)
 NOCUBLAS = bool(__import__("os").environ.get("NOCUBLAS"))
 for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
     A = torch.randn((Kd, M) if tA else (M, Kd), device="cuda").bfloat16()
@@ -37,16 +40,35 @@ for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
     out = torch.empty(M, N, device="cuda", dtype=torch.float32 if f32 else torch.bfloat16)
     aux = torch.randn(M, N, device="cuda").bfloat16() if epi == L.EPI_QGELU_BWD else None
     line = f"{tag:16s} M{M} N{N} K{Kd}: "
+    ROT = int(os.environ.get("ROTATE", "0"))
+    if ROT:      # cycle through ROT sets of activations / outputs so every call sees L2-cold tensors (as in the step)
+        As = [A.clone() for _ in range(ROT)]
+        outs = [torch.empty_like(out) for _ in range(ROT)]
+        auxs = [aux.clone() if aux is not None else None for _ in range(ROT)]
+        for _ in range(3):
+            K.gemm(As[0], B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=outs[0], aux=auxs[0],
+                   want_preact=PRE and epi == L.EPI_QGELU)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        reps = 24
+        for i in range(reps):
+            K.gemm(As[i % ROT], B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=outs[i % ROT],
+                   aux=auxs[i % ROT], want_preact=PRE and epi == L.EPI_QGELU)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        print(line + f"rotating x{ROT}: {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s", flush=True)
+        continue
     for name, impl in impls:
         try:
             for _ in range(3):
                 K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl,
-                       aux=aux)
+                       aux=aux, want_preact=PRE and epi == L.EPI_QGELU)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             reps = 20
             for _ in range(reps):
-                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl, aux=aux)
+                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl, aux=aux,
+                       want_preact=PRE and epi == L.EPI_QGELU)
             e1.record(); torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
             line += f"{name} {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s | "
