@@ -234,7 +234,8 @@ def run_ours(a):
                             text_embed_dim=D_IN, compute_dtype=torch.bfloat16)
     args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
     tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg,
-                      cross_gpu_negatives=a.xneg, overlap_allreduce=a.overlap)
+                      cross_gpu_negatives=a.xneg, overlap_allreduce=a.overlap,
+                      comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")))
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)

@@ -14,6 +14,18 @@ void exg_set_error(const char* fmt, ...) {
 }
 void exg_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+// SMs set aside for kernels of other streams (NCCL during an overlapped gradient all-reduce): persistent kernels
+// size their grid to the remaining SMs, so none of their CTAs queues behind a communication CTA.
+static std::atomic<int> g_reserved_sms{0};
+int exg_persistent_sms() {
+  const int n = exg_num_sms() - g_reserved_sms.load(std::memory_order_relaxed);
+  return n < 2 ? 2 : n;
+}
+extern "C" int exg_reserve_sms(int n) {
+  if (n < 0) n = 0;
+  return g_reserved_sms.exchange(n, std::memory_order_relaxed);
+}
+
 extern "C" int exg_version(void) { return 100; }
 extern "C" const char* exg_last_error(void) { return g_err; }
 extern "C" long long exg_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

@@ -146,6 +146,8 @@ __device__ __forceinline__ float quick_gelu_grad_fast(float u) {
   return fmaf(1.702f * u * s, 1.0f - s, s);
 }
 
+int exg_persistent_sms();      // exg_num_sms() minus the SMs reserved through exg_reserve_sms (abi.cu)
+
 static inline int exg_num_sms() {
   static int n = 0;
   if (n == 0) {

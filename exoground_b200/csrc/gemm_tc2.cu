@@ -418,7 +418,7 @@ int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
     attr_set = true;
   }
   const long total = (long)a.tiles_m * a.tiles_n * a.splits * a.batch;
-  const long units = exg_num_sms() / NCTA;
+  const long units = exg_persistent_sms() / NCTA;
   const int grid = (int)(total < units ? total : units) * NCTA;
   if (NCTA == 1) {
     kfn<<<grid, kThreads, smem, s>>>(ta, tb, tc, tx, ti, a);

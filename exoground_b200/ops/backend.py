@@ -182,6 +182,10 @@ class CudaBackend:
                                         _rm(map_dx, rows), int(accumulate), rows, Cn, _stream()), "exg_l2norm_bwd")
         return dx
 
+    def reserve_sms(self, n):
+        """Persistent kernels launched from now on leave n SMs to other streams (NCCL); returns the previous value."""
+        return int(self.lib.exg_reserve_sms(int(n)))
+
     def colsum(self, x, out=None):
         """fp32 [N] = sum over rows of x [M,N]; with `out` the sums are ACCUMULATED into it (gradient sinks)."""
         _cuda(x, out)

@@ -35,6 +35,7 @@ _SIGS = {
     "exg_version": (C.c_int, []),
     "exg_last_error": (C.c_char_p, []),
     "exg_launch_count": (C.c_longlong, []),
+    "exg_reserve_sms": (C.c_int, [C.c_int]),
     "exg_profile_classes": (C.c_int, []),
     "exg_profile_class_name": (C.c_char_p, [C.c_int]),
     "exg_profile_begin": (C.c_int, []),

@@ -28,7 +28,7 @@ from . import loss as exg_loss
 class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
                  device="cuda", use_graph=True, process_group=None, cross_gpu_negatives=False,
-                 overlap_allreduce=False, bucket_mb=25.0):
+                 overlap_allreduce=False, bucket_mb=25.0, comm_sms=0):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
@@ -54,6 +54,9 @@ class TanTrainStep:
         # (profiles/allreduce_overlap_r01.txt); it needs a work-stealing tile scheduler in gemm_tc2 to pay off
         self.overlap = bool(overlap_allreduce) and self.world > 1
         self.bucket_elems = int(bucket_mb * (1 << 20) / 4)
+        # SMs left to NCCL's CTAs while buckets are in flight: the persistent GEMMs launched in that window use
+        # (SM count - comm_sms) CTAs instead of queueing a second wave behind the SMs NCCL holds
+        self.comm_sms = int(comm_sms)
         self._pending, self._works = [], []
         self.step_count = 0
         self.graph = None
@@ -199,6 +202,8 @@ class TanTrainStep:
                 merged[-1][1] = hi
             else:
                 merged.append([lo, hi])
+        if merged and self.comm_sms > 0 and not self._works:
+            ops.get().reserve_sms(self.comm_sms)
         for lo, hi in merged:
             self._works.append(torch.distributed.all_reduce(g[lo:hi], group=self.pg, async_op=True))
             self._reduced += hi - lo
@@ -213,6 +218,8 @@ class TanTrainStep:
             self._works.append(torch.distributed.all_reduce(fp.grad[:fp.n_bucketed], group=self.pg, async_op=True))
         for w in self._works:
             w.wait()
+        if self.comm_sms > 0:
+            ops.get().reserve_sms(0)
         self._works, self._reduced = [], 0
 
     def _optimizer(self):

@@ -34,6 +34,11 @@ int exg_version(void);
 const char* exg_last_error(void);
 /* number of kernels this library has launched since load (process-wide; for bench gpu_launches) */
 long long exg_launch_count(void);
+/* Reserve n SMs for kernels of other streams (NCCL while a gradient all-reduce overlaps backward): the persistent
+ * kernels launched from now on use (SM count - n) CTAs, so none of them waits behind a communication CTA.  Returns
+ * the previous reservation; 0 restores full-width grids.  Replaces nothing in the reference (DDP's bucket overlap,
+ * train/main_egoexo4d_distributed.py:611-614, relies on non-persistent cuBLAS kernels). */
+int exg_reserve_sms(int n);
 
 /* Per-kernel-class timing for bench.py's roofline: between exg_profile_begin() and exg_profile_end() every
  * launch is bracketed by a CUDA-event pair on its stream.  exg_profile_end synchronises those events and
