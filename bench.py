@@ -198,7 +198,7 @@ def run_reference(a):
             "config": workload_config(a.gpus),
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -235,7 +235,7 @@ def run_ours(a):
     args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
     tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg,
                       cross_gpu_negatives=a.xneg, overlap_allreduce=a.overlap,
-                      comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")))
+                      comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")), branch_streams=not a.single_stream)
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
@@ -348,7 +348,7 @@ def run_ours(a):
         if world == 1 and not a.no_cpu:
             r = time_cpu(CPU_SAMPLE_BATCH, 3, 1, "port")
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         del graph
@@ -356,7 +356,30 @@ def run_ours(a):
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) are sent to stderr
+    for the life of the process, and the line is written to the original descriptor at the end."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -364,6 +387,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--single-stream", action="store_true",
+                    help="keep the joint-encoder branch on the main stream (default: its own stream, concurrent with "
+                         "the video-encoder branch)")
     ap.add_argument("--overlap", action="store_true",
                     help="N>1: per-block gradient buckets all-reduced asynchronously during backward instead of one "
                          "all-reduce after it (measured: no gain, see DESIGN.md §6)")

@@ -166,18 +166,44 @@ class TemporalAligner(ExgModule):
 
         xv = self._video_proj(video_embed, wT)                                     # fp32 [B*T, C]
         xt = self._text_proj(lang_embed, wT)                                       # fp32 [B*N, C]
+        xg = self.xneg if self.xneg is not None and self.xneg.world > 1 else None
+        Bg = B * (xg.world if xg is not None else 1)
+        xt_time = self._text_with_time(xt, B, N, pt, interpolate_from) if self.use_text_pos_enc else xt
+
+        # The joint branch only needs the shared projections (tan_model.py:176-203), not the video encoder's output,
+        # so a trainer may give it a stream of its own (`_branch_stream`): its latency-bound kernels (attention at
+        # S <= 128, LayerNorm, N = 512 GEMMs) then fill the SMs the other branch leaves idle, in forward and - since
+        # autograd replays each node on its forward stream - in backward.
+        side = getattr(self, "_branch_stream", None) if xv.is_cuda and xg is None else None
+        main = torch.cuda.current_stream() if side is not None else None
+
+        def joint_branch():
+            st_j = self._joint_stages(xv, xt_time, B, T, N, vmask, tmask, pj, interpolate_from, wT)
+            jvn, jtn = Fn.SplitL2NormFn.apply(st_j, B, T, N)                       # [D,B*T,C], [D,B*N,C]
+            lj = Fn.SimLogitsFn.apply(jvn, gather_rows(jtn, xg))                   # [D, B*T, Bg*N]
+            ja = None
+            if self.use_alignability_head:
+                jt = Fn.GatherRowsFn.apply(st_j, D * B * N, (N, T + N, T), Tc)       # joint_text_out rows
+                ja = self._head(jt, wT).view(D, B, N, 1).permute(1, 0, 2, 3)
+            return lj, ja
+
+        if side is not None:
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                logits_joint, joint_align = joint_branch()
         st_v = self._video_stages(xv, B, T, vmask, pv, interpolate_from, wT)       # [E, B*T, C]
         vn = Fn.L2NormFn.apply(st_v, Tc)                                           # [E, B*T, C]
         tn = Fn.L2NormFn.apply(xt, Tc)                                             # [B*N, C]
         # cross-GPU negatives (train/xneg.py): columns = the text features of ALL ranks, rows stay local
-        xg = self.xneg if self.xneg is not None and self.xneg.world > 1 else None
-        Bg = B * (xg.world if xg is not None else 1)
         logits_dual = Fn.SimLogitsFn.apply(vn, gather_rows(tn, xg))                # [E, B*T, Bg*N]
-
-        xt_time = self._text_with_time(xt, B, N, pt, interpolate_from) if self.use_text_pos_enc else xt
-        st_j = self._joint_stages(xv, xt_time, B, T, N, vmask, tmask, pj, interpolate_from, wT)
-        jvn, jtn = Fn.SplitL2NormFn.apply(st_j, B, T, N)                           # [D,B*T,C], [D,B*N,C]
-        logits_joint = Fn.SimLogitsFn.apply(jvn, gather_rows(jtn, xg))             # [D, B*T, Bg*N]
+        if side is not None:
+            main.wait_stream(side)
+            if not torch.cuda.is_current_stream_capturing():
+                for t in (logits_joint, joint_align):
+                    if t is not None:
+                        t.record_stream(main)
+        else:
+            logits_joint, joint_align = joint_branch()
 
         out = {'logits_dual': logits_dual.view(E, B, T, Bg, N).permute(1, 0, 2, 3, 4),
                'logits_joint': logits_joint.view(D, B, T, Bg, N).permute(1, 0, 2, 3, 4)}
@@ -186,8 +212,7 @@ class TemporalAligner(ExgModule):
             out['dual_feature_text'] = tn.view(B, N, C)
         if self.use_alignability_head:
             out['dual_logits_alignability'] = self._head(xt, wT).view(B, N, 1)
-            jt = Fn.GatherRowsFn.apply(st_j, D * B * N, (N, T + N, T), Tc)           # joint_text_out rows
-            out['joint_logits_alignability'] = self._head(jt, wT).view(D, B, N, 1).permute(1, 0, 2, 3)
+            out['joint_logits_alignability'] = joint_align
         return out
 
     # ------------------------------------------------------------------ reference helper API

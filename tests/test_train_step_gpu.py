@@ -107,3 +107,32 @@ def test_prefetch_pipeline_matches_plain_steps():
     # without prefetch: scripts/check_determinism.py); a wrong / stale batch would be off by > 1e-2
     assert np.allclose(runs[0], runs[1], rtol=2e-3), runs
     assert min(abs(a - b) for i, a in enumerate(runs[0]) for b in runs[0][i + 1:]) > 1e-2   # the batches really differ
+
+
+@pytest.mark.parametrize("dtype,use_graph", [(torch.float32, False), (torch.float32, True), (torch.bfloat16, True)])
+def test_branch_streams_match_single_stream(dtype, use_graph):
+    """The joint-encoder branch on its own CUDA stream (forward and, through autograd's stream replay, backward) must
+    give the single-stream step: same losses, same flat gradient after one step, same parameters after three."""
+    args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
+    b = _batch()
+    res = []
+    for branch in (False, True):
+        np.random.seed(11)
+        m = _model(dtype)
+        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, wd=1e-2, eps=1e-4, use_graph=use_graph,
+                          branch_streams=branch)
+        assert (tr.branch_stream is not None) == branch
+        tr.load_batch(b)
+        tr.prepare()
+        np.random.seed(12)
+        losses = [tr.step(b)]
+        fp = m.flat_params()
+        g1 = fp.grad[:fp.n_used].clone()
+        losses += [tr.step(b) for _ in range(2)]
+        torch.cuda.synchronize()
+        res.append((losses, g1, fp.flat.clone()))
+    fp32 = dtype == torch.float32
+    assert np.allclose(res[0][0], res[1][0], rtol=1e-5 if fp32 else 2e-3), (res[0][0], res[1][0])
+    gn = res[0][1].norm().item()
+    assert (res[0][1] - res[1][1]).norm().item() <= (1e-5 if fp32 else 2e-2) * gn
+    assert (res[0][2] - res[1][2]).abs().max().item() <= (1e-5 if fp32 else 2e-3)
