@@ -149,6 +149,24 @@ class ExoGroundingTransformer(ExgModule):
             raise AttributeError("'ExoGroundingTransformer' object has no attribute 'audio_pre_proj'")
         return self._proj_ln(audio_embed, self.audio_pre_proj, self.ln_audio_init, wT, "audio_pre_proj")
 
+    def _unimodal_pair(self, video_embed, vmask_u8, xt, tmask_u8, B, N, wT):
+        """The two unimodal encoders are independent (exo_ground_model.py:153-154): with a trainer-provided
+        `_branch_stream` the (short, latency-bound) text encoder runs beside the video encoder, forward and - through
+        autograd's stream replay - backward.  np.random draw order is the reference's (video first)."""
+        side = getattr(self, "_branch_stream", None) if xt.is_cuda else None
+        if side is None:
+            v_enc = self._video_unimodal_mean(video_embed, vmask_u8, wT)     # reference passes no interpolate_from here
+            return v_enc, self._text_unimodal_mean(xt, tmask_u8, B, N, wT)
+        main = torch.cuda.current_stream()
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            t_enc = self._text_unimodal_mean(xt, tmask_u8, B, N, wT)
+        v_enc = self._video_unimodal_mean(video_embed, vmask_u8, wT)
+        main.wait_stream(side)
+        if not torch.cuda.is_current_stream_capturing():
+            t_enc.record_stream(main)
+        return v_enc, t_enc
+
     def _grounding(self, v_enc, t_enc, vmask_u8, tmask_u8, B, T, N, wT, a_feat=None, amask_u8=None,
                    interpolate_from=None):
         """multi-modal encoder -> decoder -> grounding head (exo_ground_model.py:161-177, 323-362).  With audio the
@@ -208,8 +226,7 @@ class ExoGroundingTransformer(ExgModule):
         if self.use_text_pos_enc:
             p0 = 0 if interpolate_from else self._draw(N)
             xt = Fn.AddPosFn.apply(xt, self._pos_ln(self.text_temporal_pos_embed, p0, N, interpolate_from), B, N)
-        v_enc = self._video_unimodal_mean(video_embed, vmask, wT)     # reference passes no interpolate_from here
-        t_enc = self._text_unimodal_mean(xt, tmask, B, N, wT)
+        v_enc, t_enc = self._unimodal_pair(video_embed, vmask, xt, tmask, B, N, wT)
         proj = None
         if (self.use_distill_nce_loss and egocentric_video_embed is not None) or \
                 (self.multi_view and self.use_pairwise_distill_nce_loss):

@@ -44,8 +44,7 @@ class GroundingModel(ExoGroundingTransformer):
                                            interpolate_from=interpolate_from)['high_dim_features']
         else:
             vi_video = video_embed
-        v_enc = self._video_unimodal_mean(vi_video, vmask, wT)
-        t_enc = self._text_unimodal_mean(xt, tmask, B, N, wT)
+        v_enc, t_enc = self._unimodal_pair(vi_video, vmask, xt, tmask, B, N, wT)
         distill = None
         if self.use_distill_nce_loss and egocentric_video_embed is not None:
             distill = info_nce_bmm(self._exo_proj(v_enc, B, T, wT), egocentric_video_embed, self.compute_dtype)

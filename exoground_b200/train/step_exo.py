@@ -19,13 +19,21 @@ _DEVICE_KEYS = ("video_features", "narration_features", "video_padding_mask", "n
 
 class ExoTrainStep:
     def __init__(self, model, args, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8, clip_grad=0.0, device="cuda",
-                 process_group=None):
+                 process_group=None, branch_streams=True):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device)
         self.model, self.args, self.clip_grad = model.to(device), args, clip_grad
         self.opt = FlatAdamW(self.model, lr, wd, betas, eps, process_group)
         self.h2d_bytes = 0
+        # text unimodal encoder beside the video unimodal encoder (model/exo_ground_model.py::_unimodal_pair)
+        self.branch_stream = None
+        if branch_streams and self.device.type == "cuda" and ops.get().name == "cuda":
+            self.branch_stream = torch.cuda.Stream(device=self.device)
+            self.model._branch_stream = self.branch_stream
+            quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+            if quiet is not None:
+                quiet(False)
 
     def to_device(self, batch):
         out, n = dict(batch), 0
@@ -47,6 +55,8 @@ class ExoTrainStep:
                 b["narration_padding_mask"].bool(), **kw)
         L, iou = exo_loss.get_loss(b, out, b["narration_padding_mask"], args)
         L["loss"].backward()
+        if self.branch_stream is not None:
+            torch.cuda.current_stream().wait_stream(self.branch_stream)
         return L, iou
 
     def step(self, batch):

@@ -136,3 +136,31 @@ def test_branch_streams_match_single_stream(dtype, use_graph):
     gn = res[0][1].norm().item()
     assert (res[0][1] - res[1][1]).norm().item() <= (1e-5 if fp32 else 2e-2) * gn
     assert (res[0][2] - res[1][2]).abs().max().item() <= (1e-5 if fp32 else 2e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_exo_step_branch_streams_match_single_stream(dtype):
+    """ExoTrainStep with the text unimodal encoder on its own stream == the single-stream step (loss dict, flat
+    gradient after one step, parameters after three)."""
+    from exoground_b200.model import ExoGroundingTransformer
+    from exoground_b200.train.step_exo import ExoTrainStep
+    from tests.shapes import exo_shapes
+    Dv, Dt, Bx, Tx, Nx = 48, 64, 3, 32, 8
+    args = synth.exo_args(use_distill_nce_loss=True, same_view_negative=True)
+    batch = synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=9)
+    res = []
+    for branch in (False, True):
+        m = ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt, use_distill_nce_loss=True,
+                                    random_pos_start=0, compute_dtype=dtype)
+        m.load_state_dict(synth.fill_state_dict(exo_shapes(2, 2, Dv, Dt, distill=True)))
+        st = ExoTrainStep(m, args, lr=1e-3, wd=1e-2, eps=1e-4, clip_grad=3.0, branch_streams=branch)
+        assert (st.branch_stream is not None) == branch
+        L = st.step(batch)
+        g1 = st.opt.flat_grad().clone()
+        losses = [float(L["loss"])] + [float(st.step(batch)["loss"]) for _ in range(2)]
+        torch.cuda.synchronize()
+        res.append((losses, g1, m.flat_params().flat.clone()))
+    fp32 = dtype == torch.float32
+    assert np.allclose(res[0][0], res[1][0], rtol=1e-5 if fp32 else 5e-3), (res[0][0], res[1][0])
+    assert (res[0][1] - res[1][1]).norm().item() <= (1e-5 if fp32 else 3e-2) * res[0][1].norm().item()
+    assert (res[0][2] - res[1][2]).abs().max().item() <= (1e-5 if fp32 else 3e-3)
