@@ -379,6 +379,7 @@ def emit(line):
 
 
 def main():
+    global T, D_IN
     claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -397,7 +398,13 @@ def main():
                     help="N > 1: cross-GPU negatives (text features all-gathered, NCE over the global batch; "
                          "train/xneg.py) instead of the DDP-equivalent local negatives")
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: BASELINE configs[1], 128)")
+    ap.add_argument("--seq", type=int, default=0, help="T override (BASELINE configs[3]: 256); default 64")
+    ap.add_argument("--din", type=int, default=0, help="feature width override (BASELINE configs[3]: 768); default 4096")
     a = ap.parse_args()
+    if a.seq:
+        T = a.seq
+    if a.din:
+        D_IN = a.din
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
     if a.impl == "reference":
         run_reference(a)

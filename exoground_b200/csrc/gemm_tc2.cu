@@ -29,7 +29,8 @@ constexpr int kEpiWarps = 8;
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
 constexpr int kOutBufs = 2;                        // output staging ring per epilogue warp (plain epilogues)
-constexpr int kAuxBufs = 3;                        // aux-in epilogues: 1 output buffer + 2 aux-in buffers per warp
+constexpr int kAuxBufs = 2;                        // aux-in epilogues: 2 buffers per warp, each first receives an aux-in
+                                                   // chunk and then stages the output chunk computed from it
 constexpr uint32_t kStageBufBytes = 32 * 128;      // 32 rows x 128 B
 
 struct Tc2Args {
@@ -200,8 +201,9 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint32_t sbuf = 0;                            // next staging buffer (ring)
     uint32_t ti = 0;
     const int cols_per_chunk = p.out_f32 ? 32 : 64;
-    // aux-in mode: staging buffer 0 holds the output chunk, 1,2 receive the aux chunks (double-buffered prefetch)
-    const uint32_t n_out_bufs = p.has_aux_in ? 1 : kOutBufs;
+    // aux-in mode: buffer (chunk & 1) receives the aux chunk by TMA, is read into registers, then stages the output
+    // chunk; the prefetch of the next aux chunk waits for the store that last used the other buffer
+    const uint32_t n_out_bufs = kOutBufs;
     const int c_first = half * cols_per_chunk, c_step = 2 * cols_per_chunk;
     uint64_t* my_aux_bar = aux_bar + 2 * ew;
     uint32_t ci = 0;                              // running chunk index of this warp (aux ring position)
@@ -210,7 +212,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (p.has_aux_in && lane == 0 && unit < total_tiles) {
       const TileCoord t0 = tile_coord(p, unit, BN, BM * NCTA, cta_rank);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
-      tma_load_3d(stage + 1 * kStageBufBytes, &tmAuxIn, &my_aux_bar[0], t0.n0 + c_first, t0.m0 + lg * 32, t0.z);
+      tma_load_3d(stage, &tmAuxIn, &my_aux_bar[0], t0.n0 + c_first, t0.m0 + lg * 32, t0.z);
     }
     for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
       const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
@@ -234,15 +236,16 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (nt < total_tiles) {
               const TileCoord tn = tile_coord(p, nt, BN, BM * NCTA, cta_rank);
               const uint32_t nb = (ci + 1) & 1;
+              bulk_wait_read<0>();       // the store of the previous chunk has finished reading buffer nb
               mbar_arrive_expect_tx(&my_aux_bar[nb], kStageBufBytes);
-              tma_load_3d(stage + (1 + nb) * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
+              tma_load_3d(stage + nb * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
                           tn.m0 + lg * 32, tn.z);
             }
           }
           // ... and take this chunk's aux rows (thread = row, 128B-swizzled) into registers
           const uint32_t cb = ci & 1;
           mbar_wait(&my_aux_bar[cb], (ci >> 1) & 1);
-          const uint8_t* abuf = stage + (1 + cb) * kStageBufBytes;
+          const uint8_t* abuf = stage + cb * kStageBufBytes;
 #pragma unroll
           for (int u = 0; u < 8; ++u)
             ax[u] = *reinterpret_cast<const uint4*>(abuf + lane * 128 + ((u ^ (lane & 7)) << 4));
@@ -318,8 +321,10 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
         }
         // ---- stage (128B-swizzled rows) and TMA-store the chunk
-        uint8_t* buf = stage + (size_t)(sbuf % n_out_bufs) * kStageBufBytes;
-        if (lane == 0) { if (p.has_aux_in) bulk_wait_read<0>(); else bulk_wait_read<kOutBufs - 1>(); }
+        // aux-in: reuse the buffer this chunk's aux rows came in (already in registers; its previous store was
+        // waited for before that aux load was issued)
+        uint8_t* buf = stage + (size_t)(p.has_aux_in ? ((ci - 1) & 1) : (sbuf % n_out_bufs)) * kStageBufBytes;
+        if (lane == 0 && !p.has_aux_in) bulk_wait_read<kOutBufs - 1>();
         __syncwarp();
         if (p.out_f32) {
 #pragma unroll
@@ -498,13 +503,11 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
     const bool will_split = splittable && t1 * 2 <= sms;
     if (!will_split && r2 * 2.0 <= r1 * 3.0 + 1e-9) ncta = 2;
   }
-  if (a.has_aux_in && ncta == 1) bn = 128;   // 3 staging buffers per epilogue warp leave a 128-wide ring 4 stages
   {  // tuning overrides (scripts/bench_gemm.py)
     static const int f_bn = getenv("EXG_GEMM_BN") ? atoi(getenv("EXG_GEMM_BN")) : 0;
     static const int f_ncta = getenv("EXG_GEMM_NCTA") ? atoi(getenv("EXG_GEMM_NCTA")) : 0;
     if (f_ncta == 1 || (f_ncta == 2 && q->M > BM)) ncta = f_ncta;
     if ((f_bn == 128 || f_bn == 256) && q->N > 128) bn = f_bn;
-    if (a.has_aux_in && ncta == 1) bn = 128;
   }
   const long tm = (q->M + BM * ncta - 1) / (BM * ncta);
   a.tiles_m = (int)tm; a.tiles_n = (q->N + bn - 1) / bn;
