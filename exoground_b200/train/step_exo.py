@@ -26,6 +26,7 @@ class ExoTrainStep:
         self.model, self.args, self.clip_grad = model.to(device), args, clip_grad
         self.opt = FlatAdamW(self.model, lr, wd, betas, eps, process_group)
         self.h2d_bytes = 0
+        self._copy_stream, self._staged = None, None
         # text unimodal encoder beside the video unimodal encoder (model/exo_ground_model.py::_unimodal_pair)
         self.branch_stream = None
         if branch_streams and self.device.type == "cuda" and ops.get().name == "cuda":
@@ -45,6 +46,34 @@ class ExoTrainStep:
         self.h2d_bytes = n
         return out
 
+    def prefetch(self, batch):
+        """Starts the H2D copies of a FUTURE batch on a copy stream (pinned host tensors make them asynchronous), so
+        they overlap the step that is running; step(batch) of the same dict object picks the staged copy up.  The
+        collate dict carries [B,V,T,D] ego features (251 MB at B=16, T=1024): un-overlapped that copy is a third of
+        the step."""
+        if self.device.type != "cuda":
+            return
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        cs = self._copy_stream
+        with torch.cuda.stream(cs):
+            staged = self.to_device(batch)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._staged = (id(batch), staged, ev)
+
+    def _take(self, batch):
+        if self._staged is not None and self._staged[0] == id(batch):
+            _, staged, ev = self._staged
+            self._staged = None
+            main = torch.cuda.current_stream()
+            main.wait_event(ev)
+            for v in staged.values():
+                if torch.is_tensor(v) and v.is_cuda:
+                    v.record_stream(main)
+            return staged
+        return self.to_device(batch)
+
     def _fwd_bwd(self, b):
         m, args = self.model, self.args
         ego = b.get("ego_video_features") if getattr(args, "use_distill_nce_loss", False) else None
@@ -59,16 +88,19 @@ class ExoTrainStep:
             torch.cuda.current_stream().wait_stream(self.branch_stream)
         return L, iou
 
-    def step(self, batch):
-        """Host batch (the collate dict of data/loader_egoexo4d.py:567-598) in, loss dict out."""
+    def step(self, batch, next_batch=None):
+        """Host batch (the collate dict of data/loader_egoexo4d.py:567-598) in, loss dict out.  `next_batch`
+        (optional) is copied to the device on the copy stream while this step computes."""
         self.model.train()
-        b = self.to_device(batch)
+        b = self._take(batch)
         if not self.opt.attached:
             for p in self.model.parameters():
                 p.grad = None
             self._fwd_bwd(b)                    # discovery pass: which parameters receive gradients
             self.opt.attach()
         self.opt.zero_grad()
+        if next_batch is not None:
+            self.prefetch(next_batch)
         L, _ = self._fwd_bwd(b)
         self.opt.allreduce()
         if self.clip_grad > 0:

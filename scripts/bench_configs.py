@@ -72,7 +72,7 @@ def run_exo(a):
     st = ExoTrainStep(m, args, device=f"cuda:{local}", process_group=pg)
 
     def step():
-        st.step(b)
+        st.step(b, next_batch=b)      # double-buffered input: every step contains one full H2D copy (copy stream)
 
     ms = timed(step, a.warmup, a.steps)
     t = torch.tensor([ms], device="cuda", dtype=torch.float64)

@@ -164,3 +164,27 @@ def test_exo_step_branch_streams_match_single_stream(dtype):
     assert np.allclose(res[0][0], res[1][0], rtol=1e-5 if fp32 else 5e-3), (res[0][0], res[1][0])
     assert (res[0][1] - res[1][1]).norm().item() <= (1e-5 if fp32 else 3e-2) * res[0][1].norm().item()
     assert (res[0][2] - res[1][2]).abs().max().item() <= (1e-5 if fp32 else 3e-3)
+
+
+def test_exo_step_prefetch_matches_plain_steps():
+    """step(b, next_batch=nb) (H2D of nb on the copy stream while b computes) == the same steps without prefetch."""
+    from exoground_b200.model import ExoGroundingTransformer
+    from exoground_b200.train.step_exo import ExoTrainStep
+    from tests.shapes import exo_shapes
+    Dv, Dt, Bx, Tx, Nx = 48, 64, 3, 32, 8
+    args = synth.exo_args(use_distill_nce_loss=True, same_view_negative=True)
+    batches = [synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=20 + i) for i in range(4)]
+    batches = [{k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in b.items()} for b in batches]
+    runs = []
+    for prefetch in (False, True):
+        m = ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt, use_distill_nce_loss=True,
+                                    random_pos_start=0, compute_dtype=torch.float32)
+        m.load_state_dict(synth.fill_state_dict(exo_shapes(2, 2, Dv, Dt, distill=True)))
+        st = ExoTrainStep(m, args, lr=1e-3, wd=1e-2, eps=1e-4)
+        out = []
+        for i, b in enumerate(batches):
+            nb = batches[i + 1] if (prefetch and i + 1 < len(batches)) else None
+            out.append(float(st.step(b, next_batch=nb)["loss"]))
+        runs.append(out)
+    assert np.allclose(runs[0], runs[1], rtol=1e-4), runs
+    assert len({round(x, 3) for x in runs[0]}) == len(runs[0])       # the batches really differ
