@@ -235,7 +235,8 @@ def run_ours(a):
     args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
     tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg,
                       cross_gpu_negatives=a.xneg, overlap_allreduce=a.overlap,
-                      comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")), branch_streams=not a.single_stream)
+                      comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")), branch_streams=not a.single_stream,
+                      early_adamw=a.early_adamw)
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
@@ -391,6 +392,9 @@ def main():
     ap.add_argument("--single-stream", action="store_true",
                     help="keep the joint-encoder branch on the main stream (default: its own stream, concurrent with "
                          "the video-encoder branch)")
+    ap.add_argument("--early-adamw", action="store_true",
+                    help="N=1: launch each transformer stack's AdamW from inside backward as soon as the stack is "
+                         "differentiated (default: the whole AdamW after backward; measured: no gain)")
     ap.add_argument("--overlap", action="store_true",
                     help="N>1: per-block gradient buckets all-reduced asynchronously during backward instead of one "
                          "all-reduce after it (measured: no gain, see DESIGN.md §6)")

@@ -6,9 +6,13 @@
 
 namespace {
 
+// hyper (optional, device): {lr, 1 - beta1^step, sqrt(1 - beta2^step)} read at run time, so a launch captured into a
+// CUDA graph follows the learning-rate schedule and the bias corrections of the step it is replayed for.
 __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                              float* __restrict__ v, uint16_t* __restrict__ shadow, long n, float lr, float b1,
-                             float b2, float eps, float wd, float bc1, float bc2_sqrt, float gscale) {
+                             float b2, float eps, float wd, float bc1, float bc2_sqrt, float gscale,
+                             const float* __restrict__ hyper) {
+  if (hyper) { lr = hyper[0]; bc1 = hyper[1]; bc2_sqrt = hyper[2]; }
   const long n4 = n / 4;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long)gridDim.x * blockDim.x) {
     float4 pp = reinterpret_cast<float4*>(p)[i];
@@ -71,8 +75,24 @@ extern "C" int exg_adamw(float* param, const float* grad, float* exp_avg, float*
   ExgProfScope prof(EXG_PC_OPTIM, (double)n * (28.0 + (shadow_bf16 ? 2.0 : 0.0)), stream);
   adamw_kernel<<<blocks_for(n / 4 + 1), 256, 0, (cudaStream_t)stream>>>(
       param, grad, exp_avg, exp_avg_sq, reinterpret_cast<uint16_t*>(shadow_bf16), n, lr, beta1, beta2, eps,
-      weight_decay, bc1, sqrtf(bc2), grad_scale);
+      weight_decay, bc1, sqrtf(bc2), grad_scale, nullptr);
   EXG_LAUNCH_CHECK("adamw");
+  return 0;
+}
+
+extern "C" int exg_adamw_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+                             long n, const float* hyper, float beta1, float beta2, float eps, float weight_decay,
+                             float grad_scale, void* stream) {
+  EXG_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && hyper, "adamw_dev: bad argument");
+  EXG_CHECK_ARG(((uintptr_t)param & 15) == 0 && ((uintptr_t)grad & 15) == 0 && ((uintptr_t)exp_avg & 15) == 0 &&
+                    ((uintptr_t)exp_avg_sq & 15) == 0 && ((uintptr_t)shadow_bf16 & 7) == 0,
+                "adamw_dev: segments must be 16-byte aligned");
+  if (n <= 0) return 0;
+  ExgProfScope prof(EXG_PC_OPTIM, (double)n * (28.0 + (shadow_bf16 ? 2.0 : 0.0)), stream);
+  adamw_kernel<<<blocks_for(n / 4 + 1), 256, 0, (cudaStream_t)stream>>>(
+      param, grad, exp_avg, exp_avg_sq, reinterpret_cast<uint16_t*>(shadow_bf16), n, 0.f, beta1, beta2, eps,
+      weight_decay, 1.f, 1.f, grad_scale, hyper);
+  EXG_LAUNCH_CHECK("adamw_dev");
   return 0;
 }
 

@@ -419,6 +419,12 @@ class CudaBackend:
         L.check(self.lib.exg_adamw(_p(param), _p(grad), _p(m), _p(v), _p(shadow), param.numel(), lr, beta1, beta2,
                                    eps, wd, int(step), float(grad_scale), _stream()), "exg_adamw")
 
+    def adamw_dev(self, param, grad, m, v, shadow, hyper, beta1, beta2, eps, wd, grad_scale=1.0):
+        """adamw with hyper = device fp32 [3] {lr, 1 - beta1^step, sqrt(1 - beta2^step)} (CUDA-graph capturable)."""
+        _cuda(param, grad, m, v, shadow, hyper)
+        L.check(self.lib.exg_adamw_dev(_p(param), _p(grad), _p(m), _p(v), _p(shadow), param.numel(), _p(hyper),
+                                       beta1, beta2, eps, wd, float(grad_scale), _stream()), "exg_adamw_dev")
+
     def ema(self, target, online, m):
         _cuda(target, online)
         L.check(self.lib.exg_ema(_p(target), _p(online), target.numel(), float(m), _stream()), "exg_ema")

@@ -85,6 +85,8 @@ _SIGS = {
                           [vp] * 7 + [C.c_size_t, vp]),
     "exg_adamw": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, C.c_float, C.c_float, C.c_float, C.c_float,
                             C.c_float, C.c_int, C.c_float, vp]),
+    "exg_adamw_dev": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, vp, C.c_float, C.c_float, C.c_float, C.c_float,
+                                C.c_float, vp]),
     "exg_ema": (C.c_int, [vp, vp, C.c_long, C.c_float, vp]),
 }
 

@@ -267,6 +267,12 @@ int exg_ground_loss(const float* preds, const float* gt_a, const float* gt_b, co
 int exg_adamw(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
               long n, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
               float grad_scale, void* stream);
+/* Same update with {lr, 1 - beta1^step, sqrt(1 - beta2^step)} read from device memory (hyper[3]) at run time: a launch
+ * captured into a CUDA graph then follows the schedule of the step it is replayed for (train/step.py launches the
+ * AdamW of a finished transformer stack from inside the captured backward). */
+int exg_adamw_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16, long n,
+                  const float* hyper, float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                  void* stream);
 /* target = m*target + (1-m)*online   (TwinTemporalAligner._momentum_update, tan_model.py:334-338) */
 int exg_ema(float* target, const float* online, long n, float m, void* stream);
 

@@ -399,5 +399,15 @@ class TorchBackend:
         if shadow is not None:
             shadow.copy_(param.to(shadow.dtype))
 
+    def adamw_dev(self, param, grad, m, v, shadow, hyper, beta1, beta2, eps, wd, grad_scale=1.0):
+        lr, bc1, bc2s = (float(x) for x in hyper)
+        g = grad * grad_scale
+        param.mul_(1 - lr * wd)
+        m.mul_(beta1).add_(g, alpha=1 - beta1)
+        v.mul_(beta2).addcmul_(g, g, value=1 - beta2)
+        param.addcdiv_(m, v.sqrt() / bc2s + eps, value=-lr / bc1)
+        if shadow is not None:
+            shadow.copy_(param)
+
     def ema(self, target, online, m):
         target.mul_(m).add_(online, alpha=1 - m)

@@ -188,3 +188,26 @@ def test_exo_step_prefetch_matches_plain_steps():
         runs.append(out)
     assert np.allclose(runs[0], runs[1], rtol=1e-4), runs
     assert len({round(x, 3) for x in runs[0]}) == len(runs[0])       # the batches really differ
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_early_adamw_matches_late(use_graph):
+    """AdamW launched from inside backward per finished stack (exg_adamw_dev, device-side lr / bias corrections)
+    == the whole AdamW after backward: same parameters after four steps."""
+    args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
+    b = _batch()
+    res = []
+    for early in (False, True):
+        np.random.seed(11)
+        m = _model(torch.float32)
+        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, wd=1e-2, eps=1e-4, use_graph=use_graph,
+                          early_adamw=early)
+        tr.load_batch(b)
+        tr.prepare()
+        assert bool(tr._early_ranges) == early
+        np.random.seed(12)
+        losses = [tr.step(b) for _ in range(4)]
+        torch.cuda.synchronize()
+        res.append((losses, m.flat_params().flat.clone()))
+    assert np.allclose(res[0][0], res[1][0], rtol=1e-5), (res[0][0], res[1][0])
+    assert (res[0][1] - res[1][1]).abs().max().item() <= 2e-6
