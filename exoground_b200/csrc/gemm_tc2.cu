@@ -502,6 +502,9 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
     const double r1 = (double)((t1 + sms - 1) / sms), r2 = (double)((t2 + pairs - 1) / pairs);
     const bool will_split = splittable && t1 * 2 <= sms;
     if (!will_split && r2 * 2.0 <= r1 * 3.0 + 1e-9) ncta = 2;
+    // split-K weight gradients with a long K per split (the [*, 12288] x [12288, *] GEMMs of the FFN / qkv): the main
+    // loop dominates and pairs win 5-7 % (36.0 -> 33.6, 33.2 -> 31.6, 28.6 -> 26.8 us); the 512 x 512 outputs do not
+    if (will_split && t2 >= 8 && kblocks >= 64) ncta = 2;
   }
   {  // tuning overrides (scripts/bench_gemm.py)
     static const int f_bn = getenv("EXG_GEMM_BN") ? atoi(getenv("EXG_GEMM_BN")) : 0;
