@@ -209,5 +209,7 @@ def test_early_adamw_matches_late(use_graph):
         losses = [tr.step(b) for _ in range(4)]
         torch.cuda.synchronize()
         res.append((losses, m.flat_params().flat.clone()))
-    assert np.allclose(res[0][0], res[1][0], rtol=1e-5), (res[0][0], res[1][0])
-    assert (res[0][1] - res[1][1]).abs().max().item() <= 2e-6
+    # bias corrections: float powf on the host path vs double-then-rounded here -> last-bit differences that four
+    # lr = 1e-3 steps amplify to ~1e-5; a wrong step number or a skipped / doubled range would be off by > 1e-2
+    assert np.allclose(res[0][0], res[1][0], rtol=1e-4), (res[0][0], res[1][0])
+    assert (res[0][1] - res[1][1]).abs().max().item() <= 5e-5
