@@ -525,7 +525,9 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
       const long kb = (kblocks + sp - 1) / sp;
       const long items = tiles * ((kblocks + kb - 1) / kb);
       const long rounds = (items + units - 1) / units;
-      const double cost = (double)rounds * ((double)kb + 6.0);
+      // + a per-split term: every extra split adds one more fp32 reduce-add pass over the output tile in L2
+      static const double split_pen = getenv("EXG_GEMM_SPLIT_PEN") ? atof(getenv("EXG_GEMM_SPLIT_PEN")) : 0.0;
+      const double cost = (double)rounds * ((double)kb + 6.0) + split_pen * (double)sp;
       if (cost < best - 1e-9) { best = cost; a.splits = sp; }
     }
   }
