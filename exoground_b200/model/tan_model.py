@@ -338,7 +338,13 @@ class TwinTemporalAligner(nn.Module):
 
     @torch.no_grad()
     def _momentum_update(self):
-        fo, ft = self.online.flat_params(), self.target.flat_params()
+        fo = self.online.flat_params()
+        # a trainer moves the online model's never-used parameters to the tail of its flat buffer
+        # (FlatParams.set_unused): give the target the same layout before updating buffer against buffer
+        self.target._flat.set_unused(fo.unused)
+        ft = self.target.flat_params()
+        if ft.index != fo.index:
+            raise RuntimeError("TwinTemporalAligner: online / target flat layouts differ")
         ops.get().ema(ft.flat, fo.flat, self.m)
         self.target._shadow_stale = True
 

@@ -124,3 +124,29 @@ def test_sliding_window_alignment_host_logic(golden_dir):
     exoground_b200.eval.align: per-sentence scores, Recall, AUC; batched windows == window loop."""
     from tests.align_cases import run_align_case
     run_align_case(_load(golden_dir, "tan_align"), "cpu", torch.float32, 2e-4)
+
+
+def test_twin_momentum_update_after_training_layout_change():
+    """TwinTemporalAligner._momentum_update (tan_model.py:334-338) is one kernel over the flat parameter buffers: it
+    must stay a per-parameter EMA after a trainer has re-laid-out the ONLINE model (never-used parameters moved to
+    the tail of its flat buffer), and the frozen target must keep answering forward_from_ema."""
+    from exoground_b200.model.tan_model import TwinTemporalAligner
+    from exoground_b200.train.step import TanTrainStep
+    tw = TwinTemporalAligner(0.9, 1, 1, video_embed_dim=16, text_embed_dim=16, compute_dtype=torch.float32)
+    B, T, N = 2, 8, 4
+    st = TanTrainStep(tw.online, synth.tan_args(), B, T, N, 16, 16, device="cpu", use_graph=False, lr=1e-2)
+    b = synth.tan_batch(B=B, T=T, N=N, d_video=16, d_text=16, zero_pad_text=False)
+    st.step(b)
+    assert tw.online.flat_params().unused and not tw.target.flat_params().unused
+    before = {n: p.detach().clone() for n, p in tw.target.named_parameters()}
+    tw._momentum_update()
+    on = dict(tw.online.named_parameters())
+    moved = 0
+    for n, p in tw.target.named_parameters():
+        want = before[n] * 0.9 + on[n].detach() * 0.1
+        assert torch.allclose(p, want, atol=1e-6), n
+        assert not p.requires_grad
+        moved += int((p - before[n]).abs().max() > 0)
+    assert moved > 10
+    out = tw.forward_from_ema(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
+    assert torch.isfinite(out["logits_joint"]).all()
