@@ -150,3 +150,26 @@ def test_twin_momentum_update_after_training_layout_change():
     assert moved > 10
     out = tw.forward_from_ema(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
     assert torch.isfinite(out["logits_joint"]).all()
+
+
+def test_symmetric_infonce_matches_reference_formula():
+    """train/loss_nce.py::get_loss == end2end/main_nce.py:30-48 (restated: two F.cross_entropy calls), values and
+    gradients."""
+    import torch.nn.functional as F
+    from exoground_b200.train import loss_nce
+    g = torch.Generator().manual_seed(3)
+    v = F.normalize(torch.randn(37, 64, generator=g), dim=-1).requires_grad_(True)
+    t = F.normalize(torch.randn(37, 64, generator=g), dim=-1).requires_grad_(True)
+    sim = v.matmul(t.t()).div(0.07)
+    target = torch.arange(37)
+    ref = F.cross_entropy(sim, target) + F.cross_entropy(sim.transpose(0, 1), target)
+    gv, gt = torch.autograd.grad(ref, (v, t))
+    v2, t2 = v.detach().clone().requires_grad_(True), t.detach().clone().requires_grad_(True)
+    L = loss_nce.get_loss(v2, t2, None, synth.tan_args())
+    _close(L["loss"].detach(), ref.detach(), what="loss")
+    _close(L["loss-per-text"], F.cross_entropy(sim, target).detach(), what="loss-per-text")
+    _close(L["top1-per-text"], (sim.argmax(-1) == target).float().mean(), what="top1")
+    _close(L["top1-per-video"], (sim.argmax(0) == target).float().mean(), what="top1v")
+    L["loss"].backward()
+    _close(v2.grad, gv, atol=1e-5, what="dv")
+    _close(t2.grad, gt, atol=1e-5, what="dt")
