@@ -86,8 +86,8 @@ class TemporalAligner(ExgModule):
         """Random positional offset (reference tan_model.py:157,189,218: np.random.randint(0, n/2)).  When a
         trainer has installed device-side offsets (`_pos_offsets`, a list of 0-d int64 CUDA tensors it refreshes
         before every step) they are consumed in draw order instead, so a captured CUDA graph sees new offsets."""
-        offs = getattr(self, "_pos_offsets", None)
-        if offs is not None:
+        offs = getattr(self, "_pos_offsets", None) if getattr(self, "_in_forward", False) else None
+        if offs is not None:       # only forward() consumes them: the helper API below always draws on the host
             i = self._pos_cursor
             self._pos_cursor = i + 1
             return offs[i]
@@ -152,6 +152,13 @@ class TemporalAligner(ExgModule):
                 interpolate_from=None, abs_text_pos=None):
         self._check(video_embed, lang_embed)
         self._pos_cursor = 0
+        self._in_forward = True
+        try:
+            return self._forward(video_embed, lang_embed, video_padding_mask, lang_padding_mask, interpolate_from)
+        finally:
+            self._in_forward = False
+
+    def _forward(self, video_embed, lang_embed, video_padding_mask, lang_padding_mask, interpolate_from):
         wT = self._weights()
         Tc = self.compute_dtype
         B, T, _ = video_embed.shape
