@@ -10,11 +10,15 @@ weights): forward -> MIL-NCE + alignability loss -> backward -> gradient all-red
   e2e   : the same K steps through TanTrainStep.step(batch) with pinned-host inputs (H2D copies, host-built
           target masks and the loss read-back inside the timed region).
   roofline / breakdown : per-kernel-class CUDA-event timings of one profiled step (exg_profile_*).
-  cpu_baseline : the CPU oracle port (oracle/, fp32 torch restatement of the reference) fwd+loss+bwd on a
-          bounded sample of the same workload, all host threads (rank 0, N=1 only).
-Reference arm (--impl reference): the reference's own CPU path for this step.  /root/reference does not travel
-to the GPU box, so it times the oracle port (kind "port") with every host thread; when the reference tree is
-present (build container) it times the unmodified reference modules instead (kind "reference").
+  sustained : the same device-resident step repeated for >= 3 s with its own clock record (burst vs sustained).
+  cpu_baseline : the reference's own modules (oracle/_ref archive; kind "reference") - else the CPU oracle port
+          (kind "port") - fwd+loss+bwd+AdamW on a bounded sample of the same workload, all host threads (rank 0, N=1).
+  gpu_eager_baseline : the UNMODIFIED reference modules + torch.optim.AdamW in PyTorch eager (cuBLASLt + SDPA) on the
+          same B200 at the same batch, fp32 / bf16 autocast / the trainer's own fp16 autocast + GradScaler recipe
+          (train/main.py:75-112); outside the timed region, N=1 only.  This is the bar SURVEY.md names.
+Reference arm (--impl reference): the reference's own CPU path for this step: the unmodified reference modules from
+/root/reference or, on the GPU box, from the oracle/_ref archive packed from it (kind "reference"); the oracle port
+(kind "port") only if neither exists.  Every host thread; each step is a batch-8 sample of the 128-clip step.
 """
 import argparse
 import json
@@ -110,31 +114,108 @@ def cpu_step_fn(B, kind_pref="auto"):
             m = r.tan_model.TemporalAligner(E_LAYERS, D_LAYERS, use_alignability_head=1)
         m.load_state_dict(sd)
         inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
+        opt = reference_adamw(m)
 
         def step():
-            m.zero_grad()
+            opt.zero_grad()
             np.random.seed(0)
             out = m(b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"], None)
             with ref_import.quiet():
                 L = r.loss.get_loss(inp, b["video"], b["text"], b["video_padding_mask"], b["text_padding_mask"],
                                     out, args, None)
             L["loss"].backward()
+            opt.step()
             return float(L["loss"])
         return "reference", cores, step
     from oracle import tan_oracle, loss_oracle
     sd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    opt = torch.optim.AdamW(list(sd.values()), lr=1e-4, weight_decay=1e-5)
 
     def step():
-        for v in sd.values():
-            v.grad = None
+        opt.zero_grad()
         np.random.seed(0)
         ps = tan_oracle.draw_pos_starts(T, N)
         out = tan_oracle.tan_forward(sd, E_LAYERS, D_LAYERS, b["video"], b["text"], b["video_padding_mask"],
                                      b["text_padding_mask"], ps, use_alignability_head=1)
         L = loss_oracle.tan_loss(out, b["start"], b["end"], b["text_padding_mask"], T, N, 0.5, 1)
         L["loss"].backward()
+        opt.step()
         return float(L["loss"])
     return "port", cores, step
+
+
+def reference_adamw(model, lr=1e-4, wd=1e-5):
+    """train/main.py:350-376,418: AdamW, no weight decay for `.ln_` / `.bias` parameters."""
+    import torch
+    nd, dc = [], []
+    for n, p in model.named_parameters():
+        (nd if any(k in n for k in (".ln_", ".bias", ".logit_scale", ".entropy_scale")) else dc).append(p)
+    return torch.optim.AdamW([{"params": nd, "lr": lr, "weight_decay": 0.0},
+                              {"params": dc, "lr": lr, "weight_decay": wd}], lr=lr, weight_decay=wd)
+
+
+def gpu_eager_baseline(B, dev, steps=5, warmup=2):
+    """The bar SURVEY.md §0/§8(d) names: the reference's own modules (model/tan_model.py, train/loss.py) with
+    torch.optim.AdamW in PyTorch eager on THIS GPU, same batch / shapes / loss configuration as the timed step.
+    Modes: fp32; bf16 autocast; fp16 autocast + GradScaler (what train/main.py:75-112 actually runs)."""
+    import numpy as np
+    import torch
+    from exoground_b200.utils import synth
+    from oracle import ref_import
+    if not ref_import.available():
+        return {"unavailable": "oracle/_ref archive missing (python -m oracle.build_ref)"}
+    r = ref_import.load()
+    b = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, zero_pad_text=False)
+    bd = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in b.items()}
+    inp = {"start": b["start"], "end": b["end"], "text": b["text_str"]}
+    args = synth.tan_args(loss_threshold=0.5, use_alignability_head=1)
+    out = {"what": f"UNMODIFIED reference TemporalAligner E{E_LAYERS}D{D_LAYERS} + train/loss.py get_loss + backward + "
+                   f"torch.optim.AdamW, PyTorch eager {torch.__version__}, batch {B}, T={T}, N={N}, D_in={D_IN}, "
+                   f"{steps} timed + {warmup} warm-up steps, CUDA events", "unit": "clips/s",
+           "source": ref_import.kind()}
+    for mode in ("fp32", "bf16_autocast", "fp16_autocast_gradscaler"):
+        try:
+            torch.manual_seed(888)
+            with ref_import.quiet():
+                m = r.tan_model.TemporalAligner(E_LAYERS, D_LAYERS, use_alignability_head=1)
+            if D_IN != 4096:
+                m.video_pre_proj = torch.nn.Linear(D_IN, 512, bias=False)
+                m.text_pre_proj = torch.nn.Linear(D_IN, 512, bias=False)
+            m = m.to(dev).train()
+            opt = reference_adamw(m)
+            scaler = torch.amp.GradScaler("cuda", enabled=(mode == "fp16_autocast_gradscaler"))
+            ac = {"fp32": None, "bf16_autocast": torch.bfloat16, "fp16_autocast_gradscaler": torch.float16}[mode]
+
+            def step():
+                np.random.seed(0)
+                with torch.autocast("cuda", dtype=ac, enabled=ac is not None), ref_import.quiet():
+                    o = m(bd["video"], bd["text"], bd["video_padding_mask"], bd["text_padding_mask"], None)
+                    L = r.loss.get_loss(inp, bd["video"], bd["text"], bd["video_padding_mask"],
+                                        bd["text_padding_mask"], o, args, None)
+                scaler.scale(L["loss"]).backward()
+                scaler.step(opt)
+                scaler.update()
+                opt.zero_grad()
+                return L["loss"]
+            for _ in range(warmup):
+                step()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                last = step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out[mode] = {"value": round(B / (ms * 1e-3), 1), "ms_per_step": round(ms, 3),
+                         "last_loss": float(last), "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2)}
+            del m, opt
+            torch.cuda.empty_cache()
+            torch.cuda.reset_peak_memory_stats()
+        except Exception as ex:          # keep the bench line: a failing mode is reported, not fatal
+            out[mode] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
+            torch.cuda.empty_cache()
+    return out
 
 
 def time_cpu(B, steps, warmup, kind_pref="auto"):
@@ -148,8 +229,9 @@ def time_cpu(B, steps, warmup, kind_pref="auto"):
         ts.append(time.perf_counter() - t0)
     sec = sum(ts) / len(ts)
     return {"value": B / sec, "unit": "clips/s", "cores": cores, "kind": kind,
-            "sample": f"TAN E6D6 fwd+loss+bwd fp32, batch {B} of the {PER_GPU_BATCH}-clip step (T={T}, N={N}, "
-                      f"D_in={D_IN}), {steps} timed + {warmup} warm-up steps, torch CPU {cores} threads",
+            "sample": f"TAN E6D6 fwd + loss + bwd + AdamW, fp32, batch {B} of the {PER_GPU_BATCH}-clip step (T={T}, N={N}, "
+                      f"D_in={D_IN}; negatives from the {B} sampled clips), {steps} timed + {warmup} warm-up steps, "
+                      f"torch CPU {cores} threads",
             "ms_per_step": sec * 1e3}
 
 
@@ -168,7 +250,9 @@ def workload_config(n_gpus, xneg=False, batch=0, overlap=False):
 
 def _workload_config(n_gpus):
     return {"workload": f"TAN E6D6 full train step (fwd + MIL-NCE/alignability loss + bwd + AdamW), T={T}, "
-                        f"N={N} sentences, D_in={D_IN}, batch {PER_GPU_BATCH}/GPU (BASELINE.json configs[1])",
+                        f"N={N} sentences, D_in={D_IN}, batch {PER_GPU_BATCH}/GPU (BASELINE.json configs[1]); the CPU "
+                        f"reference arm (--impl reference) times a batch-{CPU_SAMPLE_BATCH} sample of this step per "
+                        f"step, fp32",
             "global_batch": PER_GPU_BATCH * n_gpus, "per_gpu_batch": PER_GPU_BATCH, "seq_len": T,
             "parallelism": f"dp{n_gpus}", "loss": "loss_threshold=0.5, use_alignability_head=1",
             "l2": "no flush: per-step working set (2 x 403 MB bf16 logits + saved activations, > 3 GB) exceeds the 126 MB L2"}
@@ -283,6 +367,27 @@ def run_ours(a):
     sync_all()
     ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps
     clocks = sampler.stop() if rank == 0 else None
+    # ---- sustained leg: the same device-resident step back to back for >= 3 s (is the short timed region a burst?)
+    sustained = None
+    if a.sustain_s > 0:
+        n_sus = max(a.steps, int(a.sustain_s * 1e3 / ms) + 1)
+        sync_all()
+        s2 = ClockSampler(local)
+        if rank == 0:
+            s2.start()
+        e0.record()
+        for _ in range(n_sus):
+            tr.run()
+        e1.record()
+        sync_all()
+        ms_sus = e0.elapsed_time(e1) / n_sus
+        ts = torch.tensor([ms_sus], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        ms_sus = float(ts[0])
+        sustained = {"value": round(B * world / (ms_sus * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_sus, 4),
+                     "steps": n_sus, "seconds": round(ms_sus * n_sus * 1e-3, 2),
+                     "clocks": s2.stop() if rank == 0 else None}
     t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -304,9 +409,13 @@ def run_ours(a):
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        tf_peak = peaks.get("bf16_tflops_sustained", 1400.0)
+        # the profiled step below is ONE eager step (~10 ms): its kernels run at burst clocks, so the denominator is the
+        # burst cuBLAS figure; the sustained figure is reported beside it (and is the one for model_tflops of the
+        # `sustained` leg)
+        tf_peak = peaks.get("bf16_tflops", 1590.0)
+        tf_peak_sus = peaks.get("bf16_tflops_sustained", 1400.0)
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        src = "measured (MEASURED_PEAKS.json, sustained)" if peaks else "fallback (B200_PROFILING.md)"
+        src = "measured (MEASURED_PEAKS.json, burst)" if peaks else "fallback (B200_PROFILING.md)"
         breakdown = {}
         tot = sum(v["ms"] for v in prof.values())
         for k, v in prof.items():
@@ -327,7 +436,9 @@ def run_ours(a):
             pass
         roof = {"kernel": top, "bound": "tensor" if tensor else "hbm", "achieved": round(ach, 2),
                 "peak": tf_peak if tensor else hbm_peak, "unit": "TFLOP/s" if tensor else "GB/s",
-                "frac": round(ach / (tf_peak if tensor else hbm_peak), 4), "traffic": traffic,
+                "frac": round(ach / (tf_peak if tensor else hbm_peak), 4),
+                "frac_of_sustained_peak": round(ach / tf_peak_sus, 4) if tensor else None,
+                "peak_sustained": tf_peak_sus if tensor else None, "traffic": traffic,
                 "traffic_source": traffic_src, "peak_source": src,
                 "launches": tv["launches"], "avg_launch_ms": round(tv["ms"] / tv["launches"], 5),
                 "how": "sum of algorithmic work / sum of CUDA-event durations of every launch of this kernel "
@@ -344,15 +455,24 @@ def run_ours(a):
                 "launches_per_step": int(launches_per_step), "cuda_graph": not a.no_graph,
                 "model_tflops": round(value / world * gf / 1e3, 1),
                 "model_tflops_frac_of_peak": round(value / world * gf / 1e3 / tf_peak, 4),
+                "model_tflops_frac_of_sustained_peak": round(value / world * gf / 1e3 / tf_peak_sus, 4),
                 "train_gflop_per_clip": round(gf, 2),
                 "roofline": roof, "breakdown": breakdown, "clocks": clocks}
+        if sustained is not None:
+            sustained["model_tflops"] = round(sustained["value"] / world * gf / 1e3, 1)
+            sustained["model_tflops_frac_of_sustained_peak"] = round(sustained["model_tflops"] / tf_peak_sus, 4)
+            line["sustained"] = sustained
+        if world == 1 and not a.no_eager:
+            del tr, graph
+            torch.cuda.empty_cache()
+            line["gpu_eager_baseline"] = gpu_eager_baseline(B, dev)
         if world == 1 and not a.no_cpu:
-            r = time_cpu(CPU_SAMPLE_BATCH, 3, 1, "port")
+            r = time_cpu(CPU_SAMPLE_BATCH, 3, 1)
             line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
         emit(line)
     if world > 1:
         dist.barrier()
-        del graph
+        graph = None
         tr.close()              # graphs that captured NCCL kernels must go before their communicator
         dist.destroy_process_group()
 
@@ -389,6 +509,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-graph", action="store_true", help="run the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-eager", action="store_true", help="skip the gpu_eager_baseline leg (reference in PyTorch eager)")
+    ap.add_argument("--sustain-s", type=float, default=3.0,
+                    help="length of the extra `sustained` leg in seconds (0 = skip)")
     ap.add_argument("--single-stream", action="store_true",
                     help="keep the joint-encoder branch on the main stream (default: its own stream, concurrent with "
                          "the video-encoder branch)")

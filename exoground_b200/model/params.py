@@ -167,4 +167,11 @@ class ExgModule(torch.nn.Module):
         if state_dict and all(k.startswith("module.") for k in state_dict):
             state_dict = {k[len("module."):]: v for k, v in state_dict.items()}
         self._shadow_stale = True
-        return super().load_state_dict(state_dict, strict=strict, **kw)
+        res = super().load_state_dict(state_dict, strict=strict, **kw)
+        # a trainer-managed shadow is only refreshed by the AdamW kernel, and a CUDA-graph replay never goes through
+        # _weights(): refresh it now, or the next step would differentiate the OLD bf16 weights
+        if self._flat.flat is not None and self._flat.shadow is not None:
+            self._flat.ensure()
+            self._flat.refresh_shadow()
+            self._shadow_stale = False
+        return res

@@ -425,6 +425,31 @@ class CudaBackend:
         L.check(self.lib.exg_adamw_dev(_p(param), _p(grad), _p(m), _p(v), _p(shadow), param.numel(), _p(hyper),
                                        beta1, beta2, eps, wd, float(grad_scale), _stream()), "exg_adamw_dev")
 
+    def grad_sumsq(self, grad, blk2seg, n_seg, out=None):
+        """fp32 [n_seg]: squared gradient norm of every parameter of the flat buffer `grad` (fp32, numel % 64 == 0);
+        blk2seg int32 [numel / 64] = parameter index of each 64-element block."""
+        _cuda(grad, blk2seg, out)
+        if out is None:
+            out = torch.empty(n_seg, dtype=torch.float32, device=grad.device)
+        L.check(self.lib.exg_grad_sumsq(_p(grad), _p(blk2seg), grad.numel(), _p(out), int(n_seg), _stream()),
+                "exg_grad_sumsq")
+        return out
+
+    def grad_clip_scale(self, grad, blk2seg, sumsq, clip, grad_scale=1.0):
+        """In place: every parameter's gradient *= clip / (||g|| * grad_scale + 1e-6) where that is < 1."""
+        _cuda(grad, blk2seg, sumsq)
+        L.check(self.lib.exg_grad_clip_scale(_p(grad), _p(blk2seg), grad.numel(), _p(sumsq), float(clip),
+                                             float(grad_scale), _stream()), "exg_grad_clip_scale")
+
+    def adamw_clip(self, param, grad, m, v, shadow, lr, beta1, beta2, eps, wd, step, blk2seg, sumsq, clip,
+                   grad_scale=1.0, hyper=None):
+        """adamw with the per-parameter clip factor folded into the gradient read (blk2seg indexed from this
+        segment's first 64-element block)."""
+        _cuda(param, grad, m, v, shadow, blk2seg, sumsq, hyper)
+        L.check(self.lib.exg_adamw_clip(_p(param), _p(grad), _p(m), _p(v), _p(shadow), param.numel(), _p(hyper),
+                                        float(lr), beta1, beta2, eps, wd, int(step), float(grad_scale), _p(blk2seg),
+                                        _p(sumsq), float(clip), _stream()), "exg_adamw_clip")
+
     def ema(self, target, online, m):
         _cuda(target, online)
         L.check(self.lib.exg_ema(_p(target), _p(online), target.numel(), float(m), _stream()), "exg_ema")

@@ -87,6 +87,10 @@ _SIGS = {
                             C.c_float, C.c_int, C.c_float, vp]),
     "exg_adamw_dev": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, vp, C.c_float, C.c_float, C.c_float, C.c_float,
                                 C.c_float, vp]),
+    "exg_grad_sumsq": (C.c_int, [vp, vp, C.c_long, vp, C.c_int, vp]),
+    "exg_grad_clip_scale": (C.c_int, [vp, vp, C.c_long, vp, C.c_float, C.c_float, vp]),
+    "exg_adamw_clip": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, vp, C.c_float, C.c_float, C.c_float, C.c_float,
+                                 C.c_float, C.c_int, C.c_float, vp, vp, C.c_float, vp]),
     "exg_ema": (C.c_int, [vp, vp, C.c_long, C.c_float, vp]),
 }
 

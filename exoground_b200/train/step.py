@@ -32,10 +32,20 @@ from . import loss as exg_loss
 class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
                  device="cuda", use_graph=True, process_group=None, cross_gpu_negatives=False,
-                 overlap_allreduce=False, bucket_mb=25.0, comm_sms=0, branch_streams=True, early_adamw=False):
+                 overlap_allreduce=False, bucket_mb=25.0, comm_sms=0, branch_streams=True, early_adamw=False,
+                 clip_grad=0.0):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
+        # 'cotrain' (train/main.py:82-89,116-117): an online / EMA-target pair.  The target's no-grad forward supplies
+        # the `ema-` logits the self-labelling branch reads, and exg_ema follows the optimizer every step.
+        self.twin = None
+        if hasattr(model, "online") and hasattr(model, "target"):
+            self.twin = model.to(device)
+            model = model.online
+        if getattr(args, "model", "init") == "cotrain" and self.twin is None:
+            raise ValueError("args.model == 'cotrain' needs a TwinTemporalAligner (online + EMA target)")
+        self.clip_grad = float(clip_grad)              # utils/train_utils.py:3-13 per-parameter clipping (0 = off)
         self.model, self.args = model.to(device), args
         self.B, self.T, self.N = B, T, N
         self.lr, self.wd, self.betas, self.eps = lr, wd, betas, eps
@@ -77,7 +87,7 @@ class TanTrainStep:
         # a 3-float device buffer refreshed before every step, which keeps those launches CUDA-graph capturable
         # (exg_adamw_dev).  Off by default: measured 7.31 vs 7.34 ms per step, within run-to-run noise - only the
         # shorter (video) branch's update really overlaps, the joint branch's update sits on the critical path.
-        self.early_adamw = bool(early_adamw) and self.world == 1
+        self.early_adamw = bool(early_adamw) and self.world == 1 and self.clip_grad == 0
         self._early_on = False                 # armed only for real steps (not for prepare()'s warm-up passes)
         self._early_ranges = {}                # stack prefix -> (lo, hi, blocks) in the flat buffers
         self._early_seen, self._early_done = {}, []
@@ -125,12 +135,21 @@ class TanTrainStep:
         for dst, key in ((self.video_s, "video"), (self.text_s, "text"), (self.vmask_s, "video_padding_mask"),
                          (self.tmask_s, "text_padding_mask")):
             src = batch[key]
+            if tuple(src.shape) != tuple(dst.shape):
+                # the captured step has static shapes; a silent broadcast (B' = 1) or a copy_ error deep inside is
+                # worse than saying so.  Ragged batches: pad to the configured (B, T, N) with masked rows.
+                raise ValueError(f"TanTrainStep: batch[{key!r}] has shape {tuple(src.shape)}, the step was built for "
+                                 f"{tuple(dst.shape)} (B={self.B}, T={self.T}, N={self.N}); pad the batch or build "
+                                 f"another step")
             dst.copy_(src, non_blocking=non_blocking)
             n += src.numel() * src.element_size()
         if "tgt" in batch:
             tgt = batch["tgt"]
         else:
             tgt = exg_loss.get_mask_from_time(batch["start"], batch["end"], self.T, self.N, device="cpu")[0]
+        if tuple(tgt.shape) != tuple(self.tgt_s.shape):
+            raise ValueError(f"TanTrainStep: target mask has shape {tuple(tgt.shape)}, expected "
+                             f"{tuple(self.tgt_s.shape)}")
         self.tgt_s.copy_(tgt, non_blocking=non_blocking)
         n += tgt.numel()
         if batch.get("abs_text_pos") is not None:
@@ -206,9 +225,13 @@ class TanTrainStep:
     def _fwd_bwd(self):
         m = self.model
         out = m(self.video, self.text, self.vmask, self.tmask, None)
+        if self.twin is not None and getattr(self.args, "model", "init") == "cotrain":
+            with torch.no_grad():          # train/main.py:82-89 (the target never draws a random offset, tan_model.py:326)
+                ema = self.twin.target(self.video, self.text, self.vmask, self.tmask, None)
+            out = {**out, **{f"ema-{k}": v for k, v in ema.items()}}
         L = exg_loss.loss_core(self.tgt, self.tmask, out, self.args,
                                self.abs_pos if getattr(self.args, "use_abs_text_pos", False) else None,
-                               self.B, self.T, self.N, xneg=self.xneg)
+                               self.B, self.T, self.N, video_padding_mask=self.vmask, xneg=self.xneg)
         L["loss"].backward()
         if self.branch_stream is not None:     # every gradient written on the branch stream is final past this point
             torch.cuda.current_stream().wait_stream(self.branch_stream)
@@ -296,11 +319,41 @@ class TanTrainStep:
             cur = max(cur, hi)
         if fp.n_used > cur:
             segs.append((cur, fp.n_used, self.wd))
+        gscale = 1.0 if self.xneg is not None else 1.0 / self.world
+        if self.clip_grad > 0:                         # train/main.py:108-110, fused: norms in one launch, factor in AdamW
+            K.grad_sumsq(fp.grad[:fp.n_used], self.blk2seg, len(self.seg_names), out=self.seg_sumsq)
         for lo, hi, wd in segs:
             if hi > lo:
-                K.adamw(fp.flat[lo:hi], fp.grad[lo:hi], self.m1[lo:hi], self.m2[lo:hi],
-                        shadow[lo:hi] if shadow is not None else None, self.lr, b1, b2, self.eps, wd,
-                        self.step_count, grad_scale=1.0 if self.xneg is not None else 1.0 / self.world)
+                sh = shadow[lo:hi] if shadow is not None else None
+                if self.clip_grad > 0:
+                    K.adamw_clip(fp.flat[lo:hi], fp.grad[lo:hi], self.m1[lo:hi], self.m2[lo:hi], sh, self.lr, b1, b2,
+                                 self.eps, wd, self.step_count, self.blk2seg[lo // 64:], self.seg_sumsq,
+                                 self.clip_grad, grad_scale=gscale)
+                else:
+                    K.adamw(fp.flat[lo:hi], fp.grad[lo:hi], self.m1[lo:hi], self.m2[lo:hi], sh, self.lr, b1, b2,
+                            self.eps, wd, self.step_count, grad_scale=gscale)
+        if self.twin is not None:                      # train/main.py:116-117
+            self.twin._momentum_update()
+
+    # ------------------------------------------------------------------ checkpointing (train/main.py:136-146,469)
+    def state_dict(self):
+        """Optimizer state in torch.optim.AdamW's layout over the reference's two parameter groups: what the
+        reference stores under 'optimizer' in its runtime / epoch checkpoints, so training on the fused path can be
+        checkpointed and resumed like (and interchangeably with) the reference loop."""
+        from .flat import optim_state_dict
+        if not self._prepared:
+            self.prepare()
+        return optim_state_dict(self.model, self.m1, self.m2, self.step_count, self.lr, self.wd, self.betas, self.eps)
+
+    def load_state_dict(self, sd):
+        """Restores AdamW moments / step count (and lr, weight decay) from state_dict() or from a checkpointed
+        torch.optim.AdamW over the reference's parameter groups.  Load the MODEL's state_dict first."""
+        from .flat import load_optim_state_dict
+        if not self._prepared:
+            self.prepare()
+        self.step_count, self.lr, self.wd = load_optim_state_dict(self.model, self.m1, self.m2, sd)
+        if self.model.compute_dtype == torch.bfloat16:
+            self.model.flat_params().refresh_shadow()      # the graph replays read the shadow, not the fp32 weights
 
     def _allreduce(self):
         if self.world > 1 and not self._hooked:
@@ -321,6 +374,12 @@ class TanTrainStep:
         fp.set_unused(unused)
         fp = m.flat_params()
         m._shadow_stale = True
+        if self.twin is not None:
+            # the EMA target follows the online model's flat layout (exg_ema runs buffer against buffer); settle it
+            # BEFORE the capture below, so no replay ever reads a re-laid-out (freed) target buffer
+            self.twin.target._flat.set_unused(fp.unused)
+            self.twin.target.flat_params()
+            self.twin.target._shadow_stale = True
         g = fp.grad_buffer()
         for n, p in m.named_parameters():
             off, numel, shape = fp.index[n]
@@ -349,6 +408,9 @@ class TanTrainStep:
             self._early_static = sorted((lo, hi) for lo, hi, _ in self._early_ranges.values())
         self.m1 = torch.zeros_like(fp.flat)
         self.m2 = torch.zeros_like(fp.flat)
+        from .flat import build_blk2seg
+        self.blk2seg, self.seg_names = build_blk2seg(fp)
+        self.seg_sumsq = torch.zeros(len(self.seg_names), dtype=torch.float32, device=fp.flat.device)
         if m.compute_dtype == torch.bfloat16:
             fp.refresh_shadow()
             m._shadow_stale = False

@@ -103,7 +103,5 @@ class ExoTrainStep:
             self.prefetch(next_batch)
         L, _ = self._fwd_bwd(b)
         self.opt.allreduce()
-        if self.clip_grad > 0:
-            self.opt.clip_per_param(self.clip_grad)
-        self.opt.step()
+        self.opt.step(clip_grad=self.clip_grad)       # per-parameter clip folded into the AdamW kernel's gradient read
         return L

@@ -273,6 +273,20 @@ int exg_adamw(float* param, const float* grad, float* exp_avg, float* exp_avg_sq
 int exg_adamw_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16, long n,
                   const float* hyper, float beta1, float beta2, float eps, float weight_decay, float grad_scale,
                   void* stream);
+/* Per-parameter gradient clipping (utils/train_utils.py:3-13 clip_gradients, called at train/main.py:108-110 and
+ * train/main_egoexo4d_distributed.py:176-181) on the flat gradient buffer, no host round trip.  Parameters start on
+ * 64-element boundaries; blk2seg[b] (int32, device) = parameter index of 64-element block b; n % 64 == 0.
+ *   exg_grad_sumsq      : seg_sumsq[s] = sum of squares of parameter s's gradient (zeroes seg_sumsq first);
+ *   exg_grad_clip_scale : grad *= clip / (||grad|| * grad_scale + 1e-6) where that factor is < 1 (in place: the
+ *                         reference's semantics, for callers that read .grad afterwards);
+ *   exg_adamw_clip      : AdamW that applies the same factor to the gradient as it reads it (no extra write pass).
+ *                         hyper (device, optional) as in exg_adamw_dev; otherwise lr / step are host values. */
+int exg_grad_sumsq(const float* grad, const int* blk2seg, long n, float* seg_sumsq, int n_seg, void* stream);
+int exg_grad_clip_scale(float* grad, const int* blk2seg, long n, const float* seg_sumsq, float clip, float grad_scale,
+                        void* stream);
+int exg_adamw_clip(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16, long n,
+                   const float* hyper, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                   float grad_scale, const int* blk2seg, const float* seg_sumsq, float clip, void* stream);
 /* target = m*target + (1-m)*online   (TwinTemporalAligner._momentum_update, tan_model.py:334-338) */
 int exg_ema(float* target, const float* online, long n, float m, void* stream);
 

@@ -409,5 +409,29 @@ class TorchBackend:
         if shadow is not None:
             shadow.copy_(param)
 
+    def grad_sumsq(self, grad, blk2seg, n_seg, out=None):
+        sq = grad.double().pow(2).view(-1, 64).sum(1)
+        res = torch.zeros(n_seg, dtype=torch.float64, device=grad.device).index_add_(0, blk2seg.long(), sq).float()
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+
+    @staticmethod
+    def _clip_coef(blk2seg, sumsq, clip, grad_scale):
+        c = clip / (sumsq.sqrt() * grad_scale + 1e-6)
+        return c.clamp(max=1.0)[blk2seg.long()].repeat_interleave(64)
+
+    def grad_clip_scale(self, grad, blk2seg, sumsq, clip, grad_scale=1.0):
+        grad.mul_(self._clip_coef(blk2seg, sumsq, clip, grad_scale))
+
+    def adamw_clip(self, param, grad, m, v, shadow, lr, beta1, beta2, eps, wd, step, blk2seg, sumsq, clip,
+                   grad_scale=1.0, hyper=None):
+        g = grad * self._clip_coef(blk2seg, sumsq, clip, grad_scale)[:grad.numel()]
+        if hyper is not None:
+            self.adamw_dev(param, g, m, v, shadow, hyper, beta1, beta2, eps, wd, grad_scale)
+        else:
+            self.adamw(param, g, m, v, shadow, lr, beta1, beta2, eps, wd, step, grad_scale)
+
     def ema(self, target, online, m):
         target.mul_(m).add_(online, alpha=1 - m)

@@ -433,6 +433,62 @@ def test_adamw_and_ema(K):
     _check(t, tr, torch.float32, "ema")
 
 
+def test_per_parameter_clip(K):
+    """exg_grad_sumsq / exg_grad_clip_scale / exg_adamw_clip vs utils/train_utils.py:3-13 + torch.optim.AdamW."""
+    sizes = [512, 1536 * 512, 70, 2048 * 512 + 3, 64, 4096 * 512, 1]
+    offs, off = [], 0
+    for n in sizes:
+        offs.append(off)
+        off += (n + 63) // 64 * 64
+    total = off
+    tab = torch.zeros(total // 64, dtype=torch.int32)
+    for i, (o, n) in enumerate(zip(offs, sizes)):
+        tab[o // 64:(o + n + 63) // 64] = i
+    tab = tab.to(DEV)
+    g = torch.zeros(total, device=DEV)
+    gen = torch.Generator(device="cpu").manual_seed(5)
+    for i, (o, n) in enumerate(zip(offs, sizes)):
+        g[o:o + n] = (torch.randn(n, generator=gen) * (10.0 ** (i % 3 - 2))).to(DEV)
+    clip, gscale = 0.7, 0.5
+    ss = K.grad_sumsq(g, tab, len(sizes))
+    want = torch.stack([g[o:o + n].double().pow(2).sum() for o, n in zip(offs, sizes)]).float()
+    _check(ss, want, torch.float32, "grad_sumsq")
+    _check(ss, REF.grad_sumsq(g, tab, len(sizes)), torch.float32, "grad_sumsq vs spec")
+    # reference semantics: clip the (mean) gradient in place, then AdamW
+    ps = [torch.nn.Parameter(torch.randn(n, generator=gen).to(DEV)) for n in sizes]
+    p_flat = torch.zeros(total, device=DEV)
+    for o, n, p in zip(offs, sizes, ps):
+        p_flat[o:o + n] = p.detach()
+    opt = torch.optim.AdamW(ps, lr=1e-3, weight_decay=1e-2)
+    m, v = torch.zeros(total, device=DEV), torch.zeros(total, device=DEV)
+    sh = torch.zeros(total, dtype=torch.bfloat16, device=DEV)
+    g2 = g.clone()
+    for step in (1, 2):
+        for o, n, p in zip(offs, sizes, ps):
+            p.grad = g[o:o + n] * gscale
+            c = clip / (p.grad.norm(2) + 1e-6)
+            if c < 1:
+                p.grad.mul_(c)
+        opt.step()
+        K.grad_sumsq(g, tab, len(sizes), out=ss)
+        K.adamw_clip(p_flat, g, m, v, sh, 1e-3, 0.9, 0.999, 1e-8, 1e-2, step, tab, ss, clip, grad_scale=gscale)
+    for o, n, p in zip(offs, sizes, ps):
+        _check(p_flat[o:o + n], p.detach(), torch.float32, f"adamw_clip segment {n}")
+    _check(sh, p_flat.bfloat16(), torch.bfloat16, "adamw_clip shadow")
+    assert torch.equal(g, g2)                          # the fused form leaves .grad unscaled
+    K.grad_clip_scale(g2, tab, ss, clip, gscale)       # the in-place form
+    for o, n in zip(offs, sizes):
+        c = min(1.0, clip / (float(g[o:o + n].norm()) * gscale + 1e-6))
+        _check(g2[o:o + n], g[o:o + n] * c, torch.float32, f"clip_scale segment {n}")
+    # a segment view that starts past the first parameter (the decay segment of a flat buffer)
+    lo = offs[3]
+    p3, m3, v3 = p_flat[lo:].clone(), torch.zeros(total - lo, device=DEV), torch.zeros(total - lo, device=DEV)
+    pr3, mr3, vr3 = p3.clone(), m3.clone(), v3.clone()
+    K.adamw_clip(p3, g[lo:], m3, v3, None, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, tab[lo // 64:], ss, clip, grad_scale=gscale)
+    REF.adamw_clip(pr3, g[lo:], mr3, vr3, None, 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, tab[lo // 64:], ss, clip, grad_scale=gscale)
+    _check(p3, pr3, torch.float32, "adamw_clip offset segment")
+
+
 # ------------------------------------------------------------------------------------------- persistent GEMM
 @pytest.mark.parametrize("tA,tB", [(False, False), (False, True), (True, True), (True, False)])
 @pytest.mark.parametrize("shape", [(128, 128, 64), (256, 256, 512), (384, 512, 2048), (8192, 1536, 512),

@@ -1,0 +1,31 @@
+"""Trainer contract on the op-spec backend (CPU, host logic): see tests/train_contract.py; the same bodies run on the
+CUDA kernels (eager and CUDA-graph, fp32 and bf16) in tests/test_train_step_gpu.py."""
+import pytest
+import torch
+
+from exoground_b200 import ops
+from tests import train_contract as tc
+from tests.fake_backend import TorchBackend
+
+
+@pytest.fixture(autouse=True)
+def fake_backend():
+    prev = ops.set_backend(TorchBackend())
+    yield
+    ops.set_backend(prev)
+
+
+def test_helper_api_after_fused_step():
+    tc.check_helpers_after_step("cpu", torch.float32, False)
+
+
+def test_clip_and_optimizer_state_roundtrip():
+    tc.check_clip_and_state_roundtrip("cpu", torch.float32, False)
+
+
+def test_cotrain_and_learn_agreement_step():
+    tc.check_cotrain_step("cpu", torch.float32, False)
+
+
+def test_shape_validation():
+    tc.check_shape_validation_and_shadow_reload("cpu", torch.float32)

@@ -213,3 +213,34 @@ def test_early_adamw_matches_late(use_graph):
     # lr = 1e-3 steps amplify to ~1e-5; a wrong step number or a skipped / doubled range would be off by > 1e-2
     assert np.allclose(res[0][0], res[1][0], rtol=1e-4), (res[0][0], res[1][0])
     assert (res[0][1] - res[1][1]).abs().max().item() <= 5e-5
+
+
+# ---------------------------------------------------------------------- trainer contract (tests/train_contract.py)
+from tests import train_contract as tc      # noqa: E402
+
+GRAPH = [False, True]
+
+
+@pytest.mark.parametrize("use_graph", GRAPH)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_helper_api_after_fused_step(dtype, use_graph):
+    tc.check_helpers_after_step("cuda", dtype, use_graph)
+
+
+@pytest.mark.parametrize("use_graph", GRAPH)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_clip_and_optimizer_state_roundtrip(dtype, use_graph):
+    """train/main.py:108-110 (clip_gradients) and :136-146,469 (optimizer state in checkpoints) on the fused step."""
+    tc.check_clip_and_state_roundtrip("cuda", dtype, use_graph)
+
+
+@pytest.mark.parametrize("use_graph", GRAPH)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_cotrain_and_learn_agreement_step(dtype, use_graph):
+    """train/main.py:82-89,116-117: online / EMA-target recipe with self-labelling, eager and captured."""
+    tc.check_cotrain_step("cuda", dtype, use_graph)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_shape_validation_and_shadow_reload(dtype):
+    tc.check_shape_validation_and_shadow_reload("cuda", dtype)
