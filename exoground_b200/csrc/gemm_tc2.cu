@@ -28,10 +28,13 @@ constexpr int BM = 128, BK = 64, UK = 16;
 constexpr int kEpiWarps = 8;
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 constexpr uint32_t kABytes = BM * BK * 2;          // 16 KB
-constexpr int kOutBufs = 2;                        // output staging ring per epilogue warp (plain epilogues)
-constexpr int kAuxBufs = 2;                        // aux-in epilogues: 2 buffers per warp, each first receives an aux-in
-                                                   // chunk and then stages the output chunk computed from it
+constexpr int kOutBufs = 2;                        // output staging buffers per epilogue warp (plain epilogues): chunks are
+                                                   // staged into them and stored by ONE fence + TMA-store group
+constexpr int kAuxBufs = 3;                        // aux-in epilogues: ring of 3 buffers per warp; a buffer first receives an
+                                                   // aux-in chunk (TMA, issued a whole chunk ahead), then stages the output
+                                                   // chunk computed from it
 constexpr uint32_t kStageBufBytes = 32 * 128;      // 32 rows x 128 B
+constexpr uint32_t kBiasStripBytes = 128 * 4;      // per epilogue warp: the bias values of the columns it owns in a tile
 
 struct Tc2Args {
   int M, N, K;
@@ -44,6 +47,21 @@ struct Tc2Args {
   int stages;        // depth of the operand ring (what fits beside the epilogue staging buffers)
   int has_aux_out;
   int has_aux_in;    // QGELU_BWD / RELU_BWD: bf16 aux tile streamed in by TMA, chunk by chunk, by the epilogue warps
+  unsigned long long* trace;   // optional per-role event log of ONE CTA (exg_gemm_trace; scripts/gemm_trace.py)
+  int trace_cap, trace_cta;
+};
+
+// Event log for pipeline analysis without a profiler: role r (0 producer, 1 MMA issuer, 2..9 epilogue warps, 10 CTA)
+// appends clock64() * 256 + tag to its own row of the buffer.  Costs one uniform predicate per event when off.
+struct Tracer {
+  unsigned long long* row; int cap, n;
+  __device__ __forceinline__ Tracer(const Tc2Args& p, int role) {
+    row = (p.trace && (int)blockIdx.x == p.trace_cta) ? p.trace + (size_t)role * p.trace_cap : nullptr;
+    cap = p.trace_cap; n = 0;
+  }
+  __device__ __forceinline__ void ev(int tag) {
+    if (row && n < cap) row[n++] = ((unsigned long long)clock64() << 8) | (unsigned)tag;
+  }
 };
 
 constexpr int kMaxStages = 6;
@@ -52,7 +70,9 @@ constexpr uint32_t kMaxSmem = 232448;
 template <int BN, int NCTA> struct Cfg2 {
   static constexpr uint32_t kBBytes = (BN / NCTA) * BK * 2;       // a CTA of a pair stages half of the B tile
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
-  __host__ __device__ static constexpr uint32_t epi_bytes(int aux_in) { return kEpiWarps * (aux_in ? kAuxBufs : kOutBufs) * kStageBufBytes; }
+  __host__ __device__ static constexpr uint32_t epi_bytes(int aux_in) {
+    return kEpiWarps * ((aux_in ? kAuxBufs : kOutBufs) * kStageBufBytes + kBiasStripBytes);
+  }
   __host__ __device__ static constexpr int stages(int aux_in) {
     const int n = (int)((kMaxSmem - 1024 - 512 - epi_bytes(aux_in)) / kStageBytes);
     return n > kMaxStages ? kMaxStages : n;
@@ -64,15 +84,26 @@ template <int BN, int NCTA> struct Cfg2 {
 
 struct TileCoord { int m0, n0, z, kb0, nkb; };
 
+// n / d and n % d for 0 <= n < 2^24, 0 < d < 2^24 without the ~40-instruction integer division: every role of the CTA
+// decodes a tile index once per tile, and on the single MMA-issuing thread that was a ~600-cycle bubble between tiles
+__device__ __forceinline__ int fast_divmod(int n, int d, int& rem) {
+  int q = __float2int_rz(__int2float_rz(n) * __frcp_rz(__int2float_rz(d)));
+  int r = n - q * d;
+  if (r >= d) { ++q; r -= d; }
+  if (r < 0) { --q; r += d; }
+  rem = r;
+  return q;
+}
+
 __device__ __forceinline__ TileCoord tile_coord(const Tc2Args& p, int tile, int BN, int bm_tile, int cta_rank) {
   // order: n fastest, then m, then split, then batch -> CTAs running concurrently share A row blocks in L2
   TileCoord t;
-  const int tn = tile % p.tiles_n; tile /= p.tiles_n;
-  const int tm = tile % p.tiles_m; tile /= p.tiles_m;
-  const int sp = tile % p.splits;
-  t.z = tile / p.splits;
+  int tn, tm, sp;
+  tile = fast_divmod(tile, p.tiles_n, tn);
+  tile = fast_divmod(tile, p.tiles_m, tm);
+  if (p.splits == 1) { sp = 0; t.z = tile; } else { t.z = fast_divmod(tile, p.splits, sp); }
   t.m0 = tm * bm_tile + cta_rank * BM; t.n0 = tn * BN;
-  const int kbt = (p.K + BK - 1) / BK;
+  const int kbt = (p.K + BK - 1) >> 6;
   t.kb0 = sp * p.kblocks_per_split;
   const int kb1 = min(kbt, t.kb0 + p.kblocks_per_split);
   t.nkb = kb1 - t.kb0;
@@ -95,16 +126,18 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* empty = full + kMaxStages;
   uint64_t* tmem_full = empty + kMaxStages;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
-  uint64_t* aux_bar = tmem_empty + 2;            // [kEpiWarps][2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + 2 * kEpiWarps);
+  uint64_t* aux_bar = tmem_empty + 2;            // [kEpiWarps][kAuxBufs]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux_bar + kAuxBufs * kEpiWarps);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits * p.batch;
+  Tracer tr_cta(p, 10);
+  if (threadIdx.x == 64) tr_cta.ev(11);
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < n_stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&tmem_full[s], 1); mbar_init(&tmem_empty[s], kEpiWarps * NCTA); }
-    for (int s = 0; s < 2 * kEpiWarps; ++s) mbar_init(&aux_bar[s], 1);
+    for (int s = 0; s < kAuxBufs * kEpiWarps; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 0 && lane == 0) {
@@ -118,10 +151,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (NCTA == 2) cluster_sync_all();      // the peer's barriers are initialised before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 64) tr_cta.ev(12);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
+      Tracer tr(p, 0);
       int s = 0; uint32_t ph = 0;
       // a pair's loads all signal the LEADER's full barrier, which expects both CTAs' bytes
       uint32_t full_addr[kMaxStages];
@@ -135,6 +170,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int nb0 = t.n0 + cta_rank * BNL;
         for (int i = 0; i < t.nkb; ++i) {
           mbar_wait(&empty[s], ph ^ 1);
+          tr.ev(1);
           uint8_t* sa = smem + (size_t)s * C_::kStageBytes;
           uint8_t* sb = sa + kABytes;
           const int k0 = (t.kb0 + i) * BK;
@@ -167,14 +203,17 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const uint32_t a_kstep = p.a_mn ? (UK * 128u) : (UK * 2u);
       const uint32_t b_kstep = p.b_mn ? (UK * 128u) : (UK * 2u);
       int s = 0; uint32_t ph = 0, ti = 0;
+      Tracer tr(p, 1);
       for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
         const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
         const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
         mbar_wait(&tmem_empty[as], aph ^ 1);          // every epilogue warp (of both CTAs) has drained this stage
+        tr.ev(2);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
         for (int i = 0; i < t.nkb; ++i) {
           mbar_wait(&full[s], ph);
+          tr.ev(3);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + (size_t)s * C_::kStageBytes);
           const uint32_t sb = sa + kABytes;
@@ -189,26 +228,65 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (++s == n_stages) { s = 0; ph ^= 1; }
         }
         if (NCTA == 2) umma_commit_2sm(&tmem_full[as], 3); else umma_commit(&tmem_full[as]);
+        tr.ev(4);
       }
     }
   } else {
     // ===================== epilogue =====================
     const int ew = warp - 2;                      // staging slot
+    Tracer tr(p, 2 + ew);
+    if (lane != 0) tr.row = nullptr;
     const int lg = warp & 3;                      // TMEM lane group this warp may access
     const int half = ew >> 2;                     // which of the two interleaved chunk sequences this warp takes
     const uint32_t n_bufs = p.has_aux_in ? kAuxBufs : kOutBufs;
     uint8_t* stage = epi_smem + (size_t)ew * n_bufs * kStageBufBytes;
-    uint32_t sbuf = 0;                            // next staging buffer (ring)
+    float* bias_s = reinterpret_cast<float*>(epi_smem + (size_t)kEpiWarps * n_bufs * kStageBufBytes) + ew * 128;
     uint32_t ti = 0;
     const int cols_per_chunk = p.out_f32 ? 32 : 64;
-    // aux-in mode: buffer (chunk & 1) receives the aux chunk by TMA, is read into registers, then stages the output
-    // chunk; the prefetch of the next aux chunk waits for the store that last used the other buffer
-    const uint32_t n_out_bufs = kOutBufs;
     const int c_first = half * cols_per_chunk, c_step = 2 * cols_per_chunk;
-    uint64_t* my_aux_bar = aux_bar + 2 * ew;
+    uint64_t* my_aux_bar = aux_bar + kAuxBufs * ew;
     uint32_t ci = 0;                              // running chunk index of this warp (aux ring position)
     const uint32_t tmem_empty_addr[2] = {NCTA == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u,
                                          NCTA == 2 ? mapa_u32(smem_u32(&tmem_empty[1]), 0) : 0u};
+    const bool use_alpha = p.alpha != 1.0f;
+    // this lane's float4 of the warp's bias strip: strip element e = 4 * lane covers chunk e / cols_per_chunk
+    const int b_chunk = (lane * 4) / cols_per_chunk, b_within = (lane * 4) % cols_per_chunk;
+    const int b_col = c_first + b_chunk * c_step + b_within;
+    // plain epilogues: chunks are staged into the warp's buffers and leave as ONE fence + store group per
+    // kOutBufs buffers (one per tile for bf16 outputs), instead of a proxy fence per chunk
+    uint32_t pend = 0;
+    static_assert(kOutBufs == 2, "the pending-store bookkeeping below is written for two buffers");
+    int pend_x0 = 0, pend_x1 = 0, pend_k0 = 0, pend_k1 = 0;    // kind: 0 store C, 1 reduce-add C, 2 store aux-out
+    auto issue = [&](const uint8_t* b, int kind, int x, int row0, int z) {
+      if (kind == 2) tma_store_3d(&tmAux, b, x, row0, z);
+      else if (kind == 1) tma_reduce_add_3d(&tmC, b, x, row0, z);
+      else tma_store_3d(&tmC, b, x, row0, z);
+    };
+    auto flush = [&](int row0, int z) {
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        issue(stage, pend_k0, pend_x0, row0, z);
+        if (pend > 1) issue(stage + kStageBufBytes, pend_k1, pend_x1, row0, z);
+        bulk_commit();
+      }
+      pend = 0;
+    };
+    auto note = [&](int x, int kind) {
+      if (pend == 0) { pend_x0 = x; pend_k0 = kind; } else { pend_x1 = x; pend_k1 = kind; }
+      ++pend;
+    };
+    auto stage_bf16 = [&](uint8_t* buf, const uint32_t (&r)[64]) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        uint4 q;
+        q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
+        q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
+        q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
+        q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
+        *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
+      }
+    };
     if (p.has_aux_in && lane == 0 && unit < total_tiles) {
       const TileCoord t0 = tile_coord(p, unit, BN, BM * NCTA, cta_rank);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
@@ -217,40 +295,51 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
       const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
       const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
+      // the tile's bias values are requested BEFORE the wait for the accumulator (their L2 latency hides behind it) and
+      // parked in shared memory; the math below reads them as warp-wide broadcasts
+      float4 bpre = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p.bias && b_col < BN && t.n0 + b_col < p.N) bpre = __ldg(reinterpret_cast<const float4*>(p.bias + t.n0 + b_col));
       mbar_wait(&tmem_full[as], aph);
+      tr.ev(5);
       tc_fence_after();
+      if (p.bias) {
+        __syncwarp();                                     // the previous tile's reads of the strip are done
+        *reinterpret_cast<float4*>(bias_s + lane * 4) = bpre;
+        __syncwarp();
+      }
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(lg * 32) << 16);
       const int row0 = t.m0 + lg * 32;
       const bool rows_live = row0 < p.M;
       const int n_live = min(BN, p.N - t.n0);
+      int chunk_k = 0;                                    // index of the chunk within this warp's strip
 #pragma unroll 1
-      for (int c0 = c_first; c0 < BN; c0 += c_step) {
+      for (int c0 = c_first; c0 < BN; c0 += c_step, ++chunk_k) {
         const bool live = rows_live && c0 < n_live;      // warp-uniform
+        const bool last_chunk = c0 + c_step >= BN;
         uint32_t r[64];
         uint4 ax[8];
         if (p.has_aux_in) {
-          // prefetch the aux chunk after this one (same tile, or first chunk of this CTA's next tile) ...
+          // prefetch the aux chunk after this one (same tile, or first chunk of this CTA's next tile) into the ring
+          // buffer after this one: its last user is the store issued two chunks ago
           if (lane == 0) {
             int nt = tile, nc = c0 + c_step;
             if (nc >= BN) { nt = tile + n_units; nc = c_first; }
             if (nt < total_tiles) {
               const TileCoord tn = tile_coord(p, nt, BN, BM * NCTA, cta_rank);
-              const uint32_t nb = (ci + 1) & 1;
-              bulk_wait_read<0>();       // the store of the previous chunk has finished reading buffer nb
+              const uint32_t nb = (ci + 1) % kAuxBufs;
+              bulk_wait_read<1>();       // only the previous chunk's store may still be reading (another buffer)
               mbar_arrive_expect_tx(&my_aux_bar[nb], kStageBufBytes);
               tma_load_3d(stage + nb * kStageBufBytes, &tmAuxIn, &my_aux_bar[nb], tn.n0 + nc,
                           tn.m0 + lg * 32, tn.z);
             }
           }
           // ... and take this chunk's aux rows (thread = row, 128B-swizzled) into registers
-          const uint32_t cb = ci & 1;
-          mbar_wait(&my_aux_bar[cb], (ci >> 1) & 1);
+          const uint32_t cb = ci % kAuxBufs;
+          mbar_wait(&my_aux_bar[cb], (ci / kAuxBufs) & 1);
           const uint8_t* abuf = stage + cb * kStageBufBytes;
 #pragma unroll
           for (int u = 0; u < 8; ++u)
             ax[u] = *reinterpret_cast<const uint4*>(abuf + lane * 128 + ((u ^ (lane & 7)) << 4));
-          fence_proxy_async();       // order these generic-proxy reads before the next TMA write into this buffer
-          __syncwarp();
           ++ci;
         }
         if (live) {
@@ -258,46 +347,42 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
           tmem_ld_wait();
         }
-        if (c0 + c_step >= BN) {
+        tr.ev(6);
+        if (last_chunk) {
           // all TMEM reads of this tile are done: hand the accumulator stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) { if (NCTA == 2) mbar_arrive_cluster(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
+          if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
         }
-        if (!live) continue;
+        if (!live) {
+          if (last_chunk && pend) flush(row0, t.z);
+          continue;
+        }
         // ---- math in the thread = row layout
         const int ncols = cols_per_chunk;
         const int nbase = t.n0 + c0;
+        if (use_alpha) {
 #pragma unroll
-        for (int j = 0; j < 64; j += 4) {
-          if (j >= ncols) break;
-          float4 v = make_float4(__uint_as_float(r[j]) * p.alpha, __uint_as_float(r[j + 1]) * p.alpha,
-                                 __uint_as_float(r[j + 2]) * p.alpha, __uint_as_float(r[j + 3]) * p.alpha);
-          if (p.bias && nbase + j < p.N) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + nbase + j));
-            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-          }
-          r[j] = __float_as_uint(v.x); r[j + 1] = __float_as_uint(v.y);
-          r[j + 2] = __float_as_uint(v.z); r[j + 3] = __float_as_uint(v.w);
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
         }
-        // ---- optional second output: the pre-activation (bf16), staged and stored first
-        if (p.has_aux_out) {
-          uint8_t* buf = stage + (size_t)(sbuf % n_out_bufs) * kStageBufBytes;
-          if (lane == 0) bulk_wait_read<kOutBufs - 1>();
-          __syncwarp();
+        if (p.bias) {
+          const float* bs = bias_s + chunk_k * cols_per_chunk;
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            uint4 q;
-            q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
-            q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
-            q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
-            q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
-            *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
+          for (int j = 0; j < 64; j += 4) {
+            if (j >= ncols) break;
+            const float4 b = *reinterpret_cast<const float4*>(bs + j);         // same address in every lane: broadcast
+            r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
+            r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
+            r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b.z);
+            r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
           }
-          fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) { tma_store_3d(&tmAux, buf, nbase, row0, t.z); bulk_commit(); }
-          ++sbuf;
+        }
+        // ---- optional second output: the pre-activation (bf16), staged first
+        if (p.has_aux_out) {
+          if (pend == 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+          stage_bf16(stage + (size_t)pend * kStageBufBytes, r);
+          note(nbase, 2);
+          if (pend == kOutBufs) flush(row0, t.z);
         }
         if (p.epilogue == EXG_EPI_QGELU) {
 #pragma unroll
@@ -320,12 +405,23 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
           }
         }
-        // ---- stage (128B-swizzled rows) and TMA-store the chunk
-        // aux-in: reuse the buffer this chunk's aux rows came in (already in registers; its previous store was
-        // waited for before that aux load was issued)
-        uint8_t* buf = stage + (size_t)(p.has_aux_in ? ((ci - 1) & 1) : (sbuf % n_out_bufs)) * kStageBufBytes;
-        if (lane == 0 && !p.has_aux_in) bulk_wait_read<kOutBufs - 1>();
-        __syncwarp();
+        tr.ev(7);
+        if (p.has_aux_in) {
+          // stage into the buffer this chunk's aux rows came in (they are in registers) and store it right away
+          uint8_t* buf = stage + (size_t)((ci - 1) % kAuxBufs) * kStageBufBytes;
+          __syncwarp();                   // every lane has taken its aux row out of the buffer
+          tr.ev(8);
+          stage_bf16(buf, r);
+          fence_proxy_async();            // also orders the generic reads of the aux rows before later TMA writes
+          __syncwarp();
+          if (lane == 0) { tma_store_3d(&tmC, buf, nbase, row0, t.z); bulk_commit(); }
+          tr.ev(9);
+          continue;
+        }
+        // ---- stage (128B-swizzled rows); the stores leave together once the buffers are full / the tile is done
+        if (pend == 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+        tr.ev(8);
+        uint8_t* buf = stage + (size_t)pend * kStageBufBytes;
         if (p.out_f32) {
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
@@ -333,28 +429,18 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
           }
         } else {
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            uint4 q;
-            q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
-            q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
-            q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
-            q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
-            *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
-          }
+          stage_bf16(buf, r);
         }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-          if (p.splits > 1) tma_reduce_add_3d(&tmC, buf, nbase, row0, t.z);
-          else tma_store_3d(&tmC, buf, nbase, row0, t.z);
-          bulk_commit();
-        }
-        ++sbuf;
+        note(nbase, p.splits > 1 ? 1 : 0);
+        if (pend == kOutBufs || last_chunk) flush(row0, t.z);
+        tr.ev(9);
       }
+      tr.ev(10);
     }
     if (lane == 0) bulk_wait_all();
+    tr.ev(15);
   }
+  if (threadIdx.x == 64) tr_cta.ev(13);
   tc_fence_before();
   __syncthreads();
   if (NCTA == 2) cluster_sync_all();      // the peer may still be reading this CTA's smem / signalling its barriers
@@ -362,6 +448,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     tc_fence_after();
     if (NCTA == 2) tmem_dealloc_2sm(tmem_base, 2 * BN); else tmem_dealloc(tmem_base, 2 * BN);
   }
+  if (threadIdx.x == 64) tr_cta.ev(14);
 }
 
 // ---------------------------------------------------------------- host side
@@ -443,6 +530,9 @@ int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
 
 bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
+unsigned long long* g_trace = nullptr;
+int g_trace_cap = 0, g_trace_cta = 0;
+
 double wave_eff(long tiles) {
   const long sms = exg_num_sms();
   const long waves = (tiles + sms - 1) / sms;
@@ -450,6 +540,17 @@ double wave_eff(long tiles) {
 }
 
 }  // namespace
+
+// Pipeline event log of the persistent GEMM (development aid, scripts/gemm_trace.py): while `buf` (device, 11 rows of
+// `cap` uint64) is installed, CTA `cta` of every gemm_tc2 launch appends clock64() * 256 + tag per role.  buf = null
+// switches it off.  Tags: 1 producer slot free, 2 MMA accumulator free, 3 MMA operands landed, 4 tile committed,
+// 5 epilogue accumulator ready, 6 TMEM read done, 7 math done, 8 staging buffer free, 9 store issued, 10 tile done,
+// 11 kernel entry, 12 setup done, 13 roles done, 14 teardown done, 15 stores drained.
+extern "C" int exg_gemm_trace(void* buf, int cap, int cta) {
+  g_trace = reinterpret_cast<unsigned long long*>(buf);
+  g_trace_cap = cap; g_trace_cta = cta;
+  return 0;
+}
 
 // 1 if the persistent TMA-epilogue kernel takes these parameters.
 int exg_gemm_tc2_supported(const exg_gemm_params* p) {
@@ -482,6 +583,7 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.bias = q->bias; a.alpha = q->alpha; a.batch = q->batch;
   a.has_aux_out = q->aux_out ? 1 : 0;
   a.has_aux_in = (q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD) ? 1 : 0;
+  a.trace = g_trace; a.trace_cap = g_trace_cap; a.trace_cta = g_trace_cta;
 
   const int kblocks = (q->K + BK - 1) / BK;
   const long tm1 = (q->M + BM - 1) / BM;

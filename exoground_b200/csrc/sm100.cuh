@@ -182,6 +182,13 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t rank)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Arrive on a peer CTA's mbarrier with the default (release, CTA-scope) semantics.  The TMEM hand-off is ordered by
+// tcgen05.fence::before_thread_sync on this side and ::after_thread_sync on the waiter's; a cluster-scope release
+// (mbar_arrive_cluster) makes every epilogue warp drain all of its outstanding memory traffic first - measured
+// ~2000 cycles per tile per warp (profiles/gemm_trace_r02a.txt).
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // TMA load of one CTA of a pair: data lands in THIS CTA's smem, the transaction bytes are signalled on the mbarrier at
 // `bar_cluster_addr` (the leader CTA's barrier, a shared::cluster address).
 __device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr,

@@ -73,7 +73,7 @@ def self_label_targets(own_joint, own_dual, tgt_raw, video_pad, text_pad, mode):
     iou = inter.sum(-1).float() / union.sum(-1).float().clamp(min=1e-5)               # [B, N]
     valid = ~tp
     conf_text = (d_conf >= _quantile(d_conf, valid, 0.3)) & (j_conf >= _quantile(j_conf, valid, 0.3))
-    iou_th = torch.tensor(0.5, device=dev)
+    iou_th = torch.full((), 0.5, device=dev)         # (torch.tensor(..) is a host copy: not graph-capturable)
     conf_iou = iou >= iou_th
     conf = conf_text & conf_iou
     if mode == 'i':

@@ -261,6 +261,10 @@ int exg_ground_loss(const float* preds, const float* gt_a, const float* gt_b, co
                     int use_center_duration, float eps, const float* thresholds, int n_thresh, float* stats,
                     float* iou, float* dpreds, void* stream);
 
+/* Development aid: per-role pipeline event log of the persistent tcgen05 GEMM (csrc/gemm_tc2.cu; read by
+ * scripts/gemm_trace.py).  buf: device uint64 [11][cap] or NULL (off); cta: which CTA of each launch records. */
+int exg_gemm_trace(void* buf, int cap, int cta);
+
 /* ---------------------------------------------------------------- optimizer -------------------
  * AdamW (torch.optim.AdamW semantics, train/main.py:418) on a flat fp32 segment; optional bf16
  * shadow copy of the updated weights.  grad_scale multiplies the gradient first (1/world_size). */

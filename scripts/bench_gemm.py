@@ -1,4 +1,7 @@
-"""GPU helper: TFLOP/s of the tcgen05 GEMM variants on the shapes of the TAN train step (CUDA events)."""
+"""GPU helper: TFLOP/s of the tcgen05 GEMM variants on the shapes of the TAN train step against cuBLAS (torch.matmul)
+on the same shapes.  Both sides are timed as a CUDA-graph replay of REPS launches (CUDA events around the replay), so
+the host cost of a launch (ctypes + five cuTensorMapEncodeTiled calls here, the dispatcher there) is not in the number:
+the train step replays a graph too.  GRAPH=0 times eager launches instead."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -58,33 +61,49 @@ for (M, N, Kd, tA, tB, epi, bias, f32, tag) in SHAPES:
         ms = e0.elapsed_time(e1) / reps
         print(line + f"rotating x{ROT}: {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s", flush=True)
         continue
-    for name, impl in impls:
-        try:
-            for _ in range(3):
-                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl,
-                       aux=aux, want_preact=PRE and epi == L.EPI_QGELU)
+    def timed(fn, reps=20):
+        """us per call of fn(): REPS calls captured into one CUDA graph, 3 replays, best."""
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        if os.environ.get("GRAPH", "1") == "0":
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            reps = 20
             for _ in range(reps):
-                K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl, aux=aux,
-                       want_preact=PRE and epi == L.EPI_QGELU)
+                fn()
             e1.record(); torch.cuda.synchronize()
-            ms = e0.elapsed_time(e1) / reps
-            line += f"{name} {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s | "
+            return e0.elapsed_time(e1) / reps * 1e3
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                for _ in range(reps):
+                    fn()
+        torch.cuda.synchronize()
+        best = 1e9
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1) / reps * 1e3)
+        return best
+
+    t_own = None
+    for name, impl in impls:
+        try:
+            us = timed(lambda: K.gemm(A, B, transA=bool(tA), transB=bool(tB), bias=bs, epilogue=epi, out=out, impl=impl,
+                                      aux=aux, want_preact=PRE and epi == L.EPI_QGELU))
+            t_own = us
+            line += f"{name} {us:8.1f} us {2*M*N*Kd/us/1e6:7.1f} TF/s | "
         except Exception as ex:
             line += f"{name} ERR {str(ex)[:60]} | "
     if NOCUBLAS:
         print(line, flush=True)
         continue
-    a = A.float().t() if tA else A.float()
-    torch.matmul(a[:8].bfloat16(), a[:8].bfloat16().t())
     Ab = (A.t() if tA else A).contiguous(); Bb = (B if tB else B.t()).contiguous()
-    for _ in range(3): torch.matmul(Ab, Bb)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(20): torch.matmul(Ab, Bb)
-    e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 20
-    line += f"cublas {ms*1e3:8.1f} us {2*M*N*Kd/ms/1e9:7.1f} TF/s"
+    outc = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    us = timed(lambda: torch.matmul(Ab, Bb, out=outc))
+    line += f"cublas {us:8.1f} us {2*M*N*Kd/us/1e6:7.1f} TF/s"
+    if t_own is not None:
+        line += f" | own/cublas time {t_own/us:5.2f}" + ("  WIN" if t_own <= us else "")
     print(line, flush=True)

@@ -178,11 +178,11 @@ def exo_pair(E, D, Dv, Dt, device, dtype, seed=41, **kw):
 
 
 def run_exo_live(device, dtype, E, D, B, T, N, Dv, Dt, *, distill, cd=True, svn=False, only=False, dec=True, tpos=0,
-                 seed=1, min_text=4, np_seed=5, what="exo", grad_tol_mult=1.0):
+                 seed=1, min_text=4, np_seed=5, what="exo", grad_tol_mult=1.0, random_pos_start=1):
     """ExoGroundingTransformer + loss_egoexo4d.get_loss + backward against the live reference on `device`."""
     fp32 = dtype == torch.float32
     r, ref, own = exo_pair(E, D, Dv, Dt, device, dtype, use_decoder=dec, use_distill_nce_loss=distill,
-                           use_text_pos_enc=tpos)
+                           use_text_pos_enc=tpos, random_pos_start=random_pos_start)
     b = synth.exo_batch(B=B, T=T, N=N, d_video=Dv, d_text=Dt, d_ego=Dv if distill else None, seed=seed,
                         min_text=min_text)
     bd = _to(b, device)

@@ -60,8 +60,10 @@ def test_cfg4_t256_d768_vs_live_reference(dt):
 def test_cfg3_exoground_e6d6_t1024_vs_live_reference(dt):
     """BASELINE configs[2]: ExoGround E6D6 with decoder at T=1024, N=64 - the long-sequence attention kernels
     (attention_flash.cu in bf16, the SIMT flash path in fp32) reached through the model."""
+    # random_pos_start=0 (SURVEY cfg-3): the table has 1024 rows, so at T=1024 any non-zero random offset makes the
+    # REFERENCE itself fail (exo_ground_model.py:310 adds a shorter slice)
     rep = live_ref.run_exo_live("cuda", dt, 6, 6, 2, 1024, 64, 768, 4096, distill=False, what=f"cfg3/{dt}",
-                                grad_tol_mult=2.0)
+                                grad_tol_mult=2.0, random_pos_start=0)
     print("cfg-3", dt, rep)
 
 
