@@ -49,7 +49,29 @@ struct Tc2Args {
   int has_aux_in;    // QGELU_BWD / RELU_BWD: bf16 aux tile streamed in by TMA, chunk by chunk, by the epilogue warps
   unsigned long long* trace;   // optional per-role event log of ONE CTA (exg_gemm_trace; scripts/gemm_trace.py)
   int trace_cap, trace_cta;
+  // direct epilogue: outputs leave the registers as 16-byte global stores (thread = row, 128 contiguous bytes per thread
+  // and chunk) and the aux-in tile arrives by 16-byte global loads issued a chunk ahead, so the SM's TMA unit - which
+  // the operand ring already saturates (profiles/gemm_trace_r02b.txt) - carries operands only, and the shared memory
+  // of the staging buffers goes to a deeper operand ring
+  int direct;
+  int epi_bytes;               // shared memory of the epilogue region (staging buffers + bias strips)
+  void* c_ptr; void* auxo_ptr; const void* auxi_ptr;
+  long ldc, strideC, ldaux, strideAux;
 };
+
+__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg_v4(void* p, uint4 v) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void red_add_v4_f32(void* p, uint4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
+}
 
 // Event log for pipeline analysis without a profiler: role r (0 producer, 1 MMA issuer, 2..9 epilogue warps, 10 CTA)
 // appends clock64() * 256 + tag to its own row of the buffer.  Costs one uniform predicate per event when off.
@@ -64,7 +86,7 @@ struct Tracer {
   }
 };
 
-constexpr int kMaxStages = 6;
+constexpr int kMaxStages = 8;
 constexpr uint32_t kMaxSmem = 232448;
 
 template <int BN, int NCTA> struct Cfg2 {
@@ -73,12 +95,13 @@ template <int BN, int NCTA> struct Cfg2 {
   __host__ __device__ static constexpr uint32_t epi_bytes(int aux_in) {
     return kEpiWarps * ((aux_in ? kAuxBufs : kOutBufs) * kStageBufBytes + kBiasStripBytes);
   }
-  __host__ __device__ static constexpr int stages(int aux_in) {
-    const int n = (int)((kMaxSmem - 1024 - 512 - epi_bytes(aux_in)) / kStageBytes);
+  static constexpr uint32_t kDirectEpiBytes = kEpiWarps * kBiasStripBytes;
+  __host__ __device__ static constexpr int stages_for(uint32_t epi) {
+    const int n = (int)((kMaxSmem - 1024 - 512 - epi) / kStageBytes);
     return n > kMaxStages ? kMaxStages : n;
   }
-  __host__ __device__ static constexpr uint32_t smem_bytes(int aux_in) {
-    return stages(aux_in) * kStageBytes + epi_bytes(aux_in) + 1024 /*align*/ + 512 /*barriers*/;
+  __host__ __device__ static constexpr uint32_t smem_for(uint32_t epi) {
+    return stages_for(epi) * kStageBytes + epi + 1024 /*align*/ + 512 /*barriers*/;
   }
 };
 
@@ -122,7 +145,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* epi_smem = smem + (size_t)n_stages * C_::kStageBytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + C_::epi_bytes(p.has_aux_in));
+  uint64_t* full = reinterpret_cast<uint64_t*>(epi_smem + p.epi_bytes);
   uint64_t* empty = full + kMaxStages;
   uint64_t* tmem_full = empty + kMaxStages;      // [2]
   uint64_t* tmem_empty = tmem_full + 2;          // [2]
@@ -240,7 +263,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int half = ew >> 2;                     // which of the two interleaved chunk sequences this warp takes
     const uint32_t n_bufs = p.has_aux_in ? kAuxBufs : kOutBufs;
     uint8_t* stage = epi_smem + (size_t)ew * n_bufs * kStageBufBytes;
-    float* bias_s = reinterpret_cast<float*>(epi_smem + (size_t)kEpiWarps * n_bufs * kStageBufBytes) + ew * 128;
+    float* bias_s = reinterpret_cast<float*>(epi_smem + p.epi_bytes - kEpiWarps * kBiasStripBytes) + ew * 128;
     uint32_t ti = 0;
     const int cols_per_chunk = p.out_f32 ? 32 : 64;
     const int c_first = half * cols_per_chunk, c_step = 2 * cols_per_chunk;
@@ -287,6 +310,140 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
       }
     };
+    if (p.direct) {
+      // ================= direct epilogue (no staging buffers, no TMA stores) =================
+      uint4 axn[8];                                 // aux rows of the NEXT chunk (bf16, thread = row), loaded a chunk ahead
+      auto aux_ld = [&](const TileCoord& tc_, int c0) {
+        const long row = (long)tc_.m0 + lg * 32 + lane;
+        const uint16_t* src = reinterpret_cast<const uint16_t*>(p.auxi_ptr) + (long)tc_.z * p.strideAux +
+                              row * p.ldaux + tc_.n0 + c0;
+        const bool ok = row < p.M;
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          axn[u] = (ok && tc_.n0 + c0 + 8 * u < p.N) ? ldg_nc_v4(src + 8 * u) : make_uint4(0u, 0u, 0u, 0u);
+      };
+      if (p.has_aux_in && unit < total_tiles) aux_ld(tile_coord(p, unit, BN, BM * NCTA, cta_rank), c_first);
+      for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
+        const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
+        const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
+        float4 bpre = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.bias && b_col < BN && t.n0 + b_col < p.N) bpre = __ldg(reinterpret_cast<const float4*>(p.bias + t.n0 + b_col));
+        mbar_wait(&tmem_full[as], aph);
+        tr.ev(5);
+        tc_fence_after();
+        if (p.bias) {
+          __syncwarp();
+          *reinterpret_cast<float4*>(bias_s + lane * 4) = bpre;
+          __syncwarp();
+        }
+        const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(lg * 32) << 16);
+        const int row0 = t.m0 + lg * 32;
+        const bool rows_live = row0 < p.M;
+        const long row = (long)row0 + lane;
+        const bool row_ok = row < p.M;
+        const int n_live = min(BN, p.N - t.n0);
+        int chunk_k = 0;
+#pragma unroll 1
+        for (int c0 = c_first; c0 < BN; c0 += c_step, ++chunk_k) {
+          const bool live = rows_live && c0 < n_live;      // warp-uniform
+          const bool last_chunk = c0 + c_step >= BN;
+          uint32_t r[64];
+          uint4 ax[8];
+          if (p.has_aux_in) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) ax[u] = axn[u];
+            int nt = tile, nc = c0 + c_step;
+            if (nc >= BN) { nt = tile + n_units; nc = c_first; }
+            if (nt < total_tiles) aux_ld(nt == tile ? t : tile_coord(p, nt, BN, BM * NCTA, cta_rank), nc);
+          }
+          if (live) {
+            tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+            if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+            tmem_ld_wait();
+          }
+          tr.ev(6);
+          if (last_chunk) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
+          }
+          if (!live) continue;
+          const int ncols = cols_per_chunk;
+          const int nbase = t.n0 + c0;
+          if (use_alpha) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
+          }
+          if (p.bias) {
+            const float* bs = bias_s + chunk_k * cols_per_chunk;
+#pragma unroll
+            for (int j = 0; j < 64; j += 4) {
+              if (j >= ncols) break;
+              const float4 b = *reinterpret_cast<const float4*>(bs + j);
+              r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
+              r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
+              r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b.z);
+              r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
+            }
+          }
+          auto store_bf16 = [&](void* base) {
+            if (!row_ok) return;
+            uint16_t* dst = reinterpret_cast<uint16_t*>(base) + (long)t.z * p.strideC + row * p.ldc + nbase;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              if (nbase + 8 * u < p.N) {
+                uint4 q;
+                q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
+                q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
+                q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
+                q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
+                stg_v4(dst + 8 * u, q);
+              }
+            }
+          };
+          if (p.has_aux_out) store_bf16(p.auxo_ptr);        // the pre-activation (same leading dimension as C)
+          if (p.epilogue == EXG_EPI_QGELU) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(quick_gelu_fast(__uint_as_float(r[j])));
+          } else if (p.epilogue == EXG_EPI_RELU) {
+#pragma unroll
+            for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
+          } else if (p.epilogue == EXG_EPI_QGELU_BWD || p.epilogue == EXG_EPI_RELU_BWD) {
+            const bool gelu = p.epilogue == EXG_EPI_QGELU_BWD;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const uint32_t w[4] = {ax[u].x, ax[u].y, ax[u].z, ax[u].w};
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                const float a0 = __uint_as_float(w[h] << 16), a1 = __uint_as_float(w[h] & 0xffff0000u);
+                const int j = u * 8 + h * 2;
+                const float v0 = __uint_as_float(r[j]), v1 = __uint_as_float(r[j + 1]);
+                r[j] = __float_as_uint(gelu ? v0 * quick_gelu_grad_fast(a0) : (a0 > 0.f ? v0 : 0.f));
+                r[j + 1] = __float_as_uint(gelu ? v1 * quick_gelu_grad_fast(a1) : (a1 > 0.f ? v1 : 0.f));
+              }
+            }
+          }
+          tr.ev(7);
+          if (p.out_f32) {
+            if (row_ok) {
+              float* dst = reinterpret_cast<float*>(p.c_ptr) + (long)t.z * p.strideC + row * p.ldc + nbase;
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                if (nbase + 4 * u < p.N) {
+                  const uint4 q = make_uint4(r[u * 4], r[u * 4 + 1], r[u * 4 + 2], r[u * 4 + 3]);
+                  if (p.splits > 1) red_add_v4_f32(dst + 4 * u, q); else stg_v4(dst + 4 * u, q);
+                }
+              }
+            }
+          } else {
+            store_bf16(p.c_ptr);
+          }
+          tr.ev(9);
+        }
+        tr.ev(10);
+      }
+      tr.ev(15);
+    } else {
     if (p.has_aux_in && lane == 0 && unit < total_tiles) {
       const TileCoord t0 = tile_coord(p, unit, BN, BM * NCTA, cta_rank);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
@@ -439,6 +596,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     if (lane == 0) bulk_wait_all();
     tr.ev(15);
+    }
   }
   if (threadIdx.x == 64) tr_cta.ev(13);
   tc_fence_before();
@@ -497,15 +655,15 @@ int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
   using C_ = Cfg2<BN, NCTA>;
   static bool attr_set = false;
   auto kfn = gemm_tc2_kernel<BN, NCTA>;
-  a.stages = C_::stages(a.has_aux_in);
-  const uint32_t smem = C_::smem_bytes(a.has_aux_in);
+  a.epi_bytes = a.direct ? (int)C_::kDirectEpiBytes : (int)C_::epi_bytes(a.has_aux_in);
+  a.stages = C_::stages_for((uint32_t)a.epi_bytes);
+  const uint32_t smem = C_::smem_for((uint32_t)a.epi_bytes);
   if (a.stages < 2 || smem > kMaxSmem) {
     exg_set_error("gemm_tc2: %u bytes of shared memory (BN=%d NCTA=%d aux_in=%d)", smem, BN, NCTA, a.has_aux_in);
     return EXG_EINVAL;
   }
   if (!attr_set) {
-    const uint32_t mx = C_::smem_bytes(0) > C_::smem_bytes(1) ? C_::smem_bytes(0) : C_::smem_bytes(1);
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mx);
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmem);
     if (e != cudaSuccess) { exg_set_error("gemm_tc2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
     attr_set = true;
   }
@@ -584,6 +742,10 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.has_aux_out = q->aux_out ? 1 : 0;
   a.has_aux_in = (q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD) ? 1 : 0;
   a.trace = g_trace; a.trace_cap = g_trace_cap; a.trace_cta = g_trace_cta;
+  static const int direct_env = getenv("EXG_GEMM_DIRECT") ? atoi(getenv("EXG_GEMM_DIRECT")) : 1;
+  a.direct = direct_env;
+  a.c_ptr = q->C; a.auxo_ptr = q->aux_out; a.auxi_ptr = q->aux;
+  a.ldc = q->ldc; a.strideC = q->strideC; a.ldaux = q->ldaux; a.strideAux = q->strideAux;
 
   const int kblocks = (q->K + BK - 1) / BK;
   const long tm1 = (q->M + BM - 1) / BM;

@@ -17,6 +17,7 @@ import math
 import numpy as np
 import torch
 
+from .. import ops
 from ..model import functional as Fn
 
 INV_TEMP = 1.0 / 0.07
@@ -121,20 +122,13 @@ def align_video(model, video, text, start, end, aligned, seq_len=64, use_alignab
     dev = video.device
     vlen, K = video.shape[1], text.shape[0]
     plan = window_plan(vlen, seq_len, start, end, aligned)
-    logits = torch.zeros(K, vlen, device=dev)
-    logits_dual = torch.zeros(K, vlen, device=dev)
-    count = torch.zeros(K, vlen, device=dev)
     a_dual = torch.zeros(K, device=dev)
     a_joint = torch.zeros(K, device=dev)
     tcount = torch.zeros(K, device=dev)
+    Kb = ops.get()
     if plan and batched:
         sj, sd, ad, aj, (vidx, tidx, vmask, tmask) = _window_sims_batched(model, video, text, plan, seq_len,
                                                                           use_alignability_head)
-        ok = (~vmask)[:, :, None] & (~tmask)[:, None, :]                          # [W, T, N]
-        flat = (tidx[:, None, :] * vlen + vidx[:, :, None]).expand_as(ok)[ok]     # index into [K, vlen]
-        logits.view(-1).index_add_(0, flat, sj[ok])
-        logits_dual.view(-1).index_add_(0, flat, sd[ok])
-        count.view(-1).index_add_(0, flat, torch.ones_like(sj[ok]))
         tok = ~tmask
         if use_alignability_head:
             va_d, va_j = ad, aj
@@ -146,26 +140,32 @@ def align_video(model, video, text, start, end, aligned, seq_len=64, use_alignab
         a_joint.index_add_(0, tidx[tok], va_j[tok])
         tcount.index_add_(0, tidx[tok], torch.ones_like(va_d[tok]))
     elif plan:
-        for (s, ln, l, r), (sj, sd, ad, aj) in zip(plan, _window_sims_loop(model, video, text, plan,
-                                                                           use_alignability_head)):
-            logits[l:r + 1, s:s + ln] += sj.t()
-            logits_dual[l:r + 1, s:s + ln] += sd.t()
-            count[l:r + 1, s:s + ln] += 1
+        T = max(p[1] for p in plan)
+        N = max(p[3] - p[2] + 1 for p in plan)
+        sj = torch.zeros(len(plan), T, N, device=dev)
+        sd = torch.zeros(len(plan), T, N, device=dev)
+        for w, ((s, ln, l, r), (wj, wd, ad, aj)) in enumerate(zip(plan, _window_sims_loop(model, video, text, plan,
+                                                                                         use_alignability_head))):
+            sj[w, :ln, :r - l + 1] = wj
+            sd[w, :ln, :r - l + 1] = wd
             if not use_alignability_head:
-                ad, aj = sd.max(0).values, sj.max(0).values
+                ad, aj = wd.max(0).values, wj.max(0).values
             a_dual[l:r + 1] += ad
             a_joint[l:r + 1] += aj
             tcount[l:r + 1] += 1
+    if plan:
+        # stitch + overlap average + `sim == 0 -> -6e4` + softmax over time + argmax in ONE launch (csrc/align.cu)
+        win = torch.tensor(plan, dtype=torch.int32).to(dev)
+        sim, prob, pred, row_max = Kb.align_finish(sj.contiguous(), sd.contiguous(), win, K, vlen)
+    else:
+        sim = torch.full((K, vlen), -6e4, device=dev)
+        prob = sim.softmax(-1)
+        pred, row_max = prob.argmax(-1), sim.max(-1).values
     eps = torch.tensor(1e-5, device=dev)
-    logits = logits / torch.maximum(count, eps)
-    logits_dual = logits_dual / torch.maximum(count, eps)
     a_dual = a_dual / torch.maximum(tcount, eps)
     a_joint = a_joint / torch.maximum(tcount, eps)
-    sim = (logits + logits_dual) / 2
-    sim = sim.masked_fill(sim == 0, -6e4)
-    prob = sim.softmax(-1)
-    score = a_joint if use_alignability_head else sim.max(-1).values
-    return {'sim': sim, 'prob': prob, 'pred': prob.argmax(-1), 'align_score': score, 'windows': len(plan)}
+    score = a_joint if use_alignability_head else row_max
+    return {'sim': sim, 'prob': prob, 'pred': pred, 'align_score': score, 'windows': len(plan)}
 
 
 def roc_auc(labels, scores):

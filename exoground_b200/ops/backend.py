@@ -413,6 +413,21 @@ class CudaBackend:
                 "exg_own_max")
         return out
 
+    # ------------------------------------------------------------------ alignment evaluation
+    def align_finish(self, sj, sd, win, K, vlen):
+        """sj / sd fp32 [W, T, N] window similarities (already / 0.07); win int32 [W, 4] = (first second, seconds,
+        first sentence, last sentence).  Returns (sim [K, vlen], prob [K, vlen], pred int64 [K], row_max [K])."""
+        _cuda(sj, sd, win)
+        W, T, N = sj.shape
+        dev = sj.device
+        sim = torch.empty((K, vlen), dtype=torch.float32, device=dev)
+        prob = torch.empty((K, vlen), dtype=torch.float32, device=dev)
+        pred = torch.empty(K, dtype=torch.int64, device=dev)
+        mx = torch.empty(K, dtype=torch.float32, device=dev)
+        L.check(self.lib.exg_align_finish(_p(sj), _p(sd), _p(win), W, T, N, K, vlen, _p(sim), _p(prob), _p(pred),
+                                          _p(mx), _stream()), "exg_align_finish")
+        return sim, prob, pred, mx
+
     # ------------------------------------------------------------------ optimizer
     def adamw(self, param, grad, m, v, shadow, lr, beta1, beta2, eps, wd, step, grad_scale=1.0):
         _cuda(param, grad, m, v, shadow)

@@ -43,6 +43,7 @@ _SIGS = {
     "exg_gemm": (C.c_int, [C.POINTER(GemmParams), vp]),
     "exg_gemm_tc_supported": (C.c_int, [C.POINTER(GemmParams)]),
     "exg_gemm_trace": (C.c_int, [vp, C.c_int, C.c_int]),
+    "exg_align_finish": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
     "exg_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, RowMap, vp, C.c_int, vp, C.c_long,
                                     vp, vp, C.c_long, C.c_int, C.c_float, vp]),
     "exg_add_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, vp, vp, C.c_int, RowMap, C.c_long, C.c_int,

@@ -261,6 +261,15 @@ int exg_ground_loss(const float* preds, const float* gt_a, const float* gt_b, co
                     int use_center_duration, float eps, const float* thresholds, int n_thresh, float* stats,
                     float* iou, float* dpreds, void* stream);
 
+/* Sliding-window alignment evaluation, device side (eval/eval_zeroshot_align.py:200-237): stitches the per-window
+ * similarity blocks sj / sd [W, T, N] fp32 (joint / dual logits, already divided by 0.07) of one video into
+ * sim [K, vlen] = overlap-averaged (joint + dual) / 2 with the reference's `sim == 0 -> -6e4` rule, prob = softmax over
+ * time, pred = argmax over time of prob (first index among equals), row_max = max over time of sim.  win int32 [W, 4] =
+ * (first second, seconds, first sentence, last sentence) per window; windows are summed in index order (the order of
+ * the reference's loop), W <= 1024. */
+int exg_align_finish(const float* sj, const float* sd, const int* win, int W, int T, int N, int K, int vlen,
+                     float* sim, float* prob, long long* pred, float* row_max, void* stream);
+
 /* Development aid: per-role pipeline event log of the persistent tcgen05 GEMM (csrc/gemm_tc2.cu; read by
  * scripts/gemm_trace.py).  buf: device uint64 [11][cap] or NULL (off); cta: which CTA of each launch records. */
 int exg_gemm_trace(void* buf, int cap, int cta);

@@ -409,6 +409,22 @@ class TorchBackend:
         if shadow is not None:
             shadow.copy_(param)
 
+    def align_finish(self, sj, sd, win, K, vlen):
+        """Spec = the reference's loop (eval_zeroshot_align.py:200-222), windows in order."""
+        logits = torch.zeros(K, vlen)
+        dual = torch.zeros(K, vlen)
+        count = torch.zeros(K, vlen)
+        for w, (s, ln, l, r) in enumerate(win.tolist()):
+            n = r - l + 1
+            logits[l:r + 1, s:s + ln] += sj[w, :ln, :n].t().float().cpu()
+            dual[l:r + 1, s:s + ln] += sd[w, :ln, :n].t().float().cpu()
+            count[l:r + 1, s:s + ln] += 1
+        eps = torch.tensor(1e-5)
+        sim = (logits / torch.maximum(count, eps) + dual / torch.maximum(count, eps)) / 2
+        sim = sim.masked_fill(sim == 0, -6e4).to(sj.device)
+        prob = sim.softmax(-1)
+        return sim, prob, prob.argmax(-1), sim.max(-1).values
+
     def grad_sumsq(self, grad, blk2seg, n_seg, out=None):
         sq = grad.double().pow(2).view(-1, 64).sum(1)
         res = torch.zeros(n_seg, dtype=torch.float64, device=grad.device).index_add_(0, blk2seg.long(), sq).float()

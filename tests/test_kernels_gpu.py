@@ -433,6 +433,35 @@ def test_adamw_and_ema(K):
     _check(t, tr, torch.float32, "ema")
 
 
+def test_align_finish(K):
+    """exg_align_finish vs the reference's stitch loop (eval_zeroshot_align.py:200-222): overlapping windows, sentences
+    covered by 1-3 windows, a sentence covered by none (all-zero row -> -6e4 everywhere), fp32 exact argmax."""
+    from exoground_b200.eval.align import window_plan
+    g = torch.Generator().manual_seed(11)
+    vlen, Kn, seq = 301, 37, 64
+    start = sorted((torch.rand(Kn, generator=g) * (vlen - 10)).tolist())
+    end = [s_ + 2 + 5 * float(torch.rand(1, generator=g)) for s_ in start]
+    aligned = [1] * Kn
+    plan = window_plan(vlen, seq, start, end, aligned)
+    assert len(plan) > 4
+    T = max(p_[1] for p_ in plan)
+    N = max(p_[3] - p_[2] + 1 for p_ in plan)
+    sj = torch.randn(len(plan), T, N, generator=g).to(DEV) * 3
+    sd = torch.randn(len(plan), T, N, generator=g).to(DEV) * 3
+    win = torch.tensor(plan, dtype=torch.int32, device=DEV)
+    got = K.align_finish(sj, sd, win, Kn, vlen)
+    ref = REF.align_finish(sj, sd, win, Kn, vlen)
+    _check(got[0], ref[0], torch.float32, "align sim")
+    assert torch.allclose(got[1], ref[1], rtol=1e-4, atol=1e-7), "align prob"
+    assert torch.equal(got[2].cpu(), ref[2].cpu()), "align pred"
+    _check(got[3], ref[3], torch.float32, "align max")
+    covered = torch.zeros(Kn, dtype=torch.bool)
+    for s_, ln, l, r in plan:
+        covered[l:r + 1] = True
+    if (~covered).any():
+        assert float(got[0][~covered].max()) == -6e4
+
+
 def test_per_parameter_clip(K):
     """exg_grad_sumsq / exg_grad_clip_scale / exg_adamw_clip vs utils/train_utils.py:3-13 + torch.optim.AdamW."""
     sizes = [512, 1536 * 512, 70, 2048 * 512 + 3, 64, 4096 * 512, 1]

@@ -1,0 +1,131 @@
+"""SURVEY §8f rank 1 on the REAL kernels: the reference's UNMODIFIED `train()` and `evaluate()`
+(train/main_egoexo4d_distributed.py:105-222, :225-362), its `optim_policy` (:544-570), `clip_gradients`
+(utils/train_utils.py:3-13), torch.optim.AdamW, LambdaLR, GradScaler and DistributedDataParallel wrapping (:611-614,
+`find_unused_parameters=True`) drive the drop-in ExoGroundingTransformer + drop-in get_loss on the CUDA kernels; the
+same loop drives the reference model + reference get_loss on the same GPU for comparison.
+
+The reference loop runs under `amp.autocast()` (fp16 on CUDA), so the two sides agree to autocast precision, not to
+1e-4: average epoch losses within 2e-2, every logged scalar within 3e-2 of its scale, evaluation metrics likewise.
+The reference comes from oracle/_ref (packed archive) on the GPU box."""
+import copy
+import importlib
+import math
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from exoground_b200 import ops
+from exoground_b200.model import ExoGroundingTransformer
+from exoground_b200.train import loss_egoexo4d as exo_loss
+from exoground_b200.utils import synth
+from oracle import ref_import
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not ref_import.available(), reason="oracle/_ref archive missing")]
+
+
+class _Plotter:
+    def __init__(self):
+        self.rows = []
+        self.writer = types.SimpleNamespace(flush=lambda: None)
+
+    def add_data(self, k, v, it):
+        self.rows.append((k, float(v), it))
+
+    def log_gpustat(self, step=None):
+        pass
+
+
+def _args(tmp):
+    a = synth.exo_args(use_distill_nce_loss=True, same_view_negative=True)
+    for k, v in dict(rank=0, views="exo", backprop_freq=1, clip_grad=3.0, iteration=0, prof=None, runtime_save_iter=4,
+                     model_path=str(tmp), log_path=str(tmp), lr=1e-3, wd=1e-2, train_plotter=_Plotter(), print_freq=1,
+                     visualize=False, vis_freq=1, save_features=False, dataset="egoexo4d", seq_len=32,
+                     feature_dim=512).items():
+        setattr(a, k, v)
+    return a
+
+
+@pytest.fixture(scope="module")
+def ddp_group():
+    import torch.distributed as dist
+    created = False
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda:0"))
+        created = True
+    yield dist.group.WORLD
+    if created:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+def test_unmodified_train_and_evaluate_on_cuda_ddp_wrapped(tmp_path, ddp_group, dtype):
+    assert ops.get().name == "cuda"
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    r = ref_import.load()
+    with ref_import.quiet():
+        trainer = importlib.import_module("main_egoexo4d_distributed")
+    ref_get_loss = trainer.get_loss
+    dev = torch.device("cuda:0")
+    Dv, Dt, B, T, N = 256, 512, 4, 32, 8
+    loader = [synth.exo_batch(B=B, T=T, N=N, d_video=Dv, d_text=Dt, d_ego=Dv, seed=s) for s in (1, 2, 3)]
+    for b in loader:
+        b["ego_video_features_all"] = b["ego_video_features"]
+    with ref_import.quiet():
+        ref = r.exo_ground_model.ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt,
+                                                         use_distill_nce_loss=True)
+    sd = synth.fill_state_dict({k: v.shape for k, v in ref.state_dict().items()})
+    ref.load_state_dict(sd)
+    own = ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt, use_distill_nce_loss=True,
+                                  compute_dtype=dtype)
+    own.load_state_dict({"module." + k: v for k, v in sd.items()})
+
+    def drive(model, get_loss, args):
+        trainer.get_loss = get_loss
+        model = DDP(model.to(dev), device_ids=[0], find_unused_parameters=True)      # main_egoexo4d_distributed.py:611-614
+        opt = torch.optim.AdamW(trainer.optim_policy(model, args), lr=args.lr, weight_decay=args.wd)
+        total, warm = 12, 2
+        sched = torch.optim.lr_scheduler.LambdaLR(
+            opt, lambda it: (it + 1) / warm if it < warm else 0.5 * (1 + math.cos(math.pi * (it - warm) / (total - warm))))
+        scaler = torch.amp.GradScaler("cuda", init_scale=256.0)      # low enough that fp16 never skips a step
+        np.random.seed(21)
+        with ref_import.quiet():
+            avg = [trainer.train(copy.deepcopy(loader), model, opt, sched, scaler, dev, ep, args) for ep in range(2)]
+            np.random.seed(22)
+            val = trainer.evaluate(copy.deepcopy(loader), model, dev, 2, args)
+        return avg, val, model
+
+    try:
+        a_ref, a_own = _args(tmp_path / "ref"), _args(tmp_path / "own")
+        os.makedirs(a_ref.model_path), os.makedirs(a_own.model_path)
+        before = ops.lib.launch_count()
+        avg_own, val_own, m_own = drive(own, exo_loss.get_loss, a_own)
+        assert ops.lib.launch_count() - before > 500           # the drop-in really ran on libexg.so
+        avg_ref, val_ref, m_ref = drive(ref, ref_get_loss, a_ref)
+    finally:
+        trainer.get_loss = ref_get_loss
+    assert a_own.iteration == a_ref.iteration == 6
+    assert all(math.isfinite(x) for x in avg_own)
+    np.testing.assert_allclose(avg_own, avg_ref, rtol=2e-2)
+    assert abs(val_own - val_ref) <= 2e-2 * max(1.0, abs(val_ref)), (val_own, val_ref)
+    kr = {(k, it): v for k, v, it in a_ref.train_plotter.rows if not k.startswith("device/")}
+    ko = {(k, it): v for k, v, it in a_own.train_plotter.rows if not k.startswith("device/")}
+    assert kr.keys() == ko.keys()
+    for key in kr:
+        if key[0].split("/")[-1].startswith("IoU>="):
+            continue                                   # threshold counts: discrete in the predictions
+        assert abs(kr[key] - ko[key]) <= 3e-2 * max(1.0, abs(kr[key])), (key, kr[key], ko[key])
+    # the DDP-wrapped runtime checkpoint (module.-prefixed keys) written by the reference's save path loads back
+    import glob
+    cks = sorted(glob.glob(os.path.join(a_own.model_path, "runtime*.pth.tar")))
+    assert cks, os.listdir(a_own.model_path)
+    ck = torch.load(cks[-1], weights_only=False)
+    assert all(k.startswith("module.") for k in ck["state_dict"])
+    fresh = ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt, use_distill_nce_loss=True,
+                                    compute_dtype=dtype)
+    fresh.load_state_dict(ck["state_dict"])
