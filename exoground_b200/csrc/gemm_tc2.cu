@@ -49,29 +49,17 @@ struct Tc2Args {
   int has_aux_in;    // QGELU_BWD / RELU_BWD: bf16 aux tile streamed in by TMA, chunk by chunk, by the epilogue warps
   unsigned long long* trace;   // optional per-role event log of ONE CTA (exg_gemm_trace; scripts/gemm_trace.py)
   int trace_cap, trace_cta;
-  // direct epilogue: outputs leave the registers as 16-byte global stores (thread = row, 128 contiguous bytes per thread
-  // and chunk) and the aux-in tile arrives by 16-byte global loads issued a chunk ahead, so the SM's TMA unit - which
-  // the operand ring already saturates (profiles/gemm_trace_r02b.txt) - carries operands only, and the shared memory
-  // of the staging buffers goes to a deeper operand ring
-  int direct;
   int epi_bytes;               // shared memory of the epilogue region (staging buffers + bias strips)
-  void* c_ptr; void* auxo_ptr; const void* auxi_ptr;
-  long ldc, strideC, ldaux, strideAux;
+  // 0: every staged chunk leaves with its own proxy fence + TMA store (the buffer it reuses was stored two chunks
+  //    ago: a whole tile of slack for the store's shared-memory read, ~2000 cycles measured);
+  // 1: the chunks of a tile leave as one fence + store group (fewer fences, but the next tile's first chunk then waits
+  //    for stores issued a moment ago) - measured slower inside the train step (profiles/gemm_epilogue_r02.txt)
+  int flush_mode;
+  // development: 1 = the epilogue only waits for / releases the accumulator (no TMEM reads, math or stores): time of
+  // the operand feed + MMA pipeline alone; 2 = no TMA loads and no MMAs (accumulator stages are handed over at once):
+  // time of the epilogue + stores alone.  Results are garbage in both modes (scripts/bench_gemm.py ABLATE=...).
+  int ablate;
 };
-
-__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-  return r;
-}
-__device__ __forceinline__ void stg_v4(void* p, uint4 v) {
-  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-__device__ __forceinline__ void red_add_v4_f32(void* p, uint4 v) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(__uint_as_float(v.x)),
-               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
-}
 
 // Event log for pipeline analysis without a profiler: role r (0 producer, 1 MMA issuer, 2..9 epilogue warps, 10 CTA)
 // appends clock64() * 256 + tag to its own row of the buffer.  Costs one uniform predicate per event when off.
@@ -95,7 +83,6 @@ template <int BN, int NCTA> struct Cfg2 {
   __host__ __device__ static constexpr uint32_t epi_bytes(int aux_in) {
     return kEpiWarps * ((aux_in ? kAuxBufs : kOutBufs) * kStageBufBytes + kBiasStripBytes);
   }
-  static constexpr uint32_t kDirectEpiBytes = kEpiWarps * kBiasStripBytes;
   __host__ __device__ static constexpr int stages_for(uint32_t epi) {
     const int n = (int)((kMaxSmem - 1024 - 512 - epi) / kStageBytes);
     return n > kMaxStages ? kMaxStages : n;
@@ -187,7 +174,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int i = 0; i < kMaxStages; ++i)
         full_addr[i] = NCTA == 2 ? mapa_u32(smem_u32(&full[i]), 0) : smem_u32(&full[i]);
       constexpr int BNL = BN / NCTA;              // B rows staged by this CTA
-      for (int tile = unit; tile < total_tiles; tile += n_units) {
+      for (int tile = unit; tile < (p.ablate == 2 ? 0 : total_tiles); tile += n_units) {
         const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
         const int za = p.a_bcast ? 0 : t.z, zb = p.b_bcast ? 0 : t.z;
         const int nb0 = t.n0 + cta_rank * BNL;
@@ -234,7 +221,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         tr.ev(2);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int i = 0; i < t.nkb; ++i) {
+        for (int i = 0; i < (p.ablate == 2 ? 0 : t.nkb); ++i) {
           mbar_wait(&full[s], ph);
           tr.ev(3);
           tc_fence_after();
@@ -277,7 +264,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int b_col = c_first + b_chunk * c_step + b_within;
     // plain epilogues: chunks are staged into the warp's buffers and leave as ONE fence + store group per
     // kOutBufs buffers (one per tile for bf16 outputs), instead of a proxy fence per chunk
-    uint32_t pend = 0;
+    uint32_t pend = 0, sbuf = 0;
     static_assert(kOutBufs == 2, "the pending-store bookkeeping below is written for two buffers");
     int pend_x0 = 0, pend_x1 = 0, pend_k0 = 0, pend_k1 = 0;    // kind: 0 store C, 1 reduce-add C, 2 store aux-out
     auto issue = [&](const uint8_t* b, int kind, int x, int row0, int z) {
@@ -310,140 +297,6 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
       }
     };
-    if (p.direct) {
-      // ================= direct epilogue (no staging buffers, no TMA stores) =================
-      uint4 axn[8];                                 // aux rows of the NEXT chunk (bf16, thread = row), loaded a chunk ahead
-      auto aux_ld = [&](const TileCoord& tc_, int c0) {
-        const long row = (long)tc_.m0 + lg * 32 + lane;
-        const uint16_t* src = reinterpret_cast<const uint16_t*>(p.auxi_ptr) + (long)tc_.z * p.strideAux +
-                              row * p.ldaux + tc_.n0 + c0;
-        const bool ok = row < p.M;
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          axn[u] = (ok && tc_.n0 + c0 + 8 * u < p.N) ? ldg_nc_v4(src + 8 * u) : make_uint4(0u, 0u, 0u, 0u);
-      };
-      if (p.has_aux_in && unit < total_tiles) aux_ld(tile_coord(p, unit, BN, BM * NCTA, cta_rank), c_first);
-      for (int tile = unit; tile < total_tiles; tile += n_units, ++ti) {
-        const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
-        const uint32_t as = ti & 1, aph = (ti >> 1) & 1;
-        float4 bpre = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (p.bias && b_col < BN && t.n0 + b_col < p.N) bpre = __ldg(reinterpret_cast<const float4*>(p.bias + t.n0 + b_col));
-        mbar_wait(&tmem_full[as], aph);
-        tr.ev(5);
-        tc_fence_after();
-        if (p.bias) {
-          __syncwarp();
-          *reinterpret_cast<float4*>(bias_s + lane * 4) = bpre;
-          __syncwarp();
-        }
-        const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(lg * 32) << 16);
-        const int row0 = t.m0 + lg * 32;
-        const bool rows_live = row0 < p.M;
-        const long row = (long)row0 + lane;
-        const bool row_ok = row < p.M;
-        const int n_live = min(BN, p.N - t.n0);
-        int chunk_k = 0;
-#pragma unroll 1
-        for (int c0 = c_first; c0 < BN; c0 += c_step, ++chunk_k) {
-          const bool live = rows_live && c0 < n_live;      // warp-uniform
-          const bool last_chunk = c0 + c_step >= BN;
-          uint32_t r[64];
-          uint4 ax[8];
-          if (p.has_aux_in) {
-#pragma unroll
-            for (int u = 0; u < 8; ++u) ax[u] = axn[u];
-            int nt = tile, nc = c0 + c_step;
-            if (nc >= BN) { nt = tile + n_units; nc = c_first; }
-            if (nt < total_tiles) aux_ld(nt == tile ? t : tile_coord(p, nt, BN, BM * NCTA, cta_rank), nc);
-          }
-          if (live) {
-            tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-            if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
-            tmem_ld_wait();
-          }
-          tr.ev(6);
-          if (last_chunk) {
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
-          }
-          if (!live) continue;
-          const int ncols = cols_per_chunk;
-          const int nbase = t.n0 + c0;
-          if (use_alpha) {
-#pragma unroll
-            for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
-          }
-          if (p.bias) {
-            const float* bs = bias_s + chunk_k * cols_per_chunk;
-#pragma unroll
-            for (int j = 0; j < 64; j += 4) {
-              if (j >= ncols) break;
-              const float4 b = *reinterpret_cast<const float4*>(bs + j);
-              r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
-              r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
-              r[j + 2] = __float_as_uint(__uint_as_float(r[j + 2]) + b.z);
-              r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
-            }
-          }
-          auto store_bf16 = [&](void* base) {
-            if (!row_ok) return;
-            uint16_t* dst = reinterpret_cast<uint16_t*>(base) + (long)t.z * p.strideC + row * p.ldc + nbase;
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              if (nbase + 8 * u < p.N) {
-                uint4 q;
-                q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
-                q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
-                q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
-                q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
-                stg_v4(dst + 8 * u, q);
-              }
-            }
-          };
-          if (p.has_aux_out) store_bf16(p.auxo_ptr);        // the pre-activation (same leading dimension as C)
-          if (p.epilogue == EXG_EPI_QGELU) {
-#pragma unroll
-            for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(quick_gelu_fast(__uint_as_float(r[j])));
-          } else if (p.epilogue == EXG_EPI_RELU) {
-#pragma unroll
-            for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
-          } else if (p.epilogue == EXG_EPI_QGELU_BWD || p.epilogue == EXG_EPI_RELU_BWD) {
-            const bool gelu = p.epilogue == EXG_EPI_QGELU_BWD;
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const uint32_t w[4] = {ax[u].x, ax[u].y, ax[u].z, ax[u].w};
-#pragma unroll
-              for (int h = 0; h < 4; ++h) {
-                const float a0 = __uint_as_float(w[h] << 16), a1 = __uint_as_float(w[h] & 0xffff0000u);
-                const int j = u * 8 + h * 2;
-                const float v0 = __uint_as_float(r[j]), v1 = __uint_as_float(r[j + 1]);
-                r[j] = __float_as_uint(gelu ? v0 * quick_gelu_grad_fast(a0) : (a0 > 0.f ? v0 : 0.f));
-                r[j + 1] = __float_as_uint(gelu ? v1 * quick_gelu_grad_fast(a1) : (a1 > 0.f ? v1 : 0.f));
-              }
-            }
-          }
-          tr.ev(7);
-          if (p.out_f32) {
-            if (row_ok) {
-              float* dst = reinterpret_cast<float*>(p.c_ptr) + (long)t.z * p.strideC + row * p.ldc + nbase;
-#pragma unroll
-              for (int u = 0; u < 8; ++u) {
-                if (nbase + 4 * u < p.N) {
-                  const uint4 q = make_uint4(r[u * 4], r[u * 4 + 1], r[u * 4 + 2], r[u * 4 + 3]);
-                  if (p.splits > 1) red_add_v4_f32(dst + 4 * u, q); else stg_v4(dst + 4 * u, q);
-                }
-              }
-            }
-          } else {
-            store_bf16(p.c_ptr);
-          }
-          tr.ev(9);
-        }
-        tr.ev(10);
-      }
-      tr.ev(15);
-    } else {
     if (p.has_aux_in && lane == 0 && unit < total_tiles) {
       const TileCoord t0 = tile_coord(p, unit, BN, BM * NCTA, cta_rank);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
@@ -469,6 +322,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const bool rows_live = row0 < p.M;
       const int n_live = min(BN, p.N - t.n0);
       int chunk_k = 0;                                    // index of the chunk within this warp's strip
+      if (p.ablate == 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
+        continue;
+      }
 #pragma unroll 1
       for (int c0 = c_first; c0 < BN; c0 += c_step, ++chunk_k) {
         const bool live = rows_live && c0 < n_live;      // warp-uniform
@@ -536,10 +395,20 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         // ---- optional second output: the pre-activation (bf16), staged first
         if (p.has_aux_out) {
-          if (pend == 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
-          stage_bf16(stage + (size_t)pend * kStageBufBytes, r);
-          note(nbase, 2);
-          if (pend == kOutBufs) flush(row0, t.z);
+          if (p.flush_mode == 0) {
+            if (lane == 0) bulk_wait_read<kOutBufs - 1>();      // the store that last used this buffer is done reading
+            __syncwarp();
+            stage_bf16(stage + (size_t)(sbuf & 1) * kStageBufBytes, r);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) { tma_store_3d(&tmAux, stage + (size_t)(sbuf & 1) * kStageBufBytes, nbase, row0, t.z); bulk_commit(); }
+            ++sbuf;
+          } else {
+            if (pend == 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+            stage_bf16(stage + (size_t)pend * kStageBufBytes, r);
+            note(nbase, 2);
+            if (pend == kOutBufs) flush(row0, t.z);
+          }
         }
         if (p.epilogue == EXG_EPI_QGELU) {
 #pragma unroll
@@ -575,10 +444,16 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           tr.ev(9);
           continue;
         }
-        // ---- stage (128B-swizzled rows); the stores leave together once the buffers are full / the tile is done
-        if (pend == 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+        // ---- stage (128B-swizzled rows) and store
+        if (p.flush_mode == 0) {
+          if (lane == 0) bulk_wait_read<kOutBufs - 1>();
+          __syncwarp();
+        } else if (pend == 0) {
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+        }
         tr.ev(8);
-        uint8_t* buf = stage + (size_t)pend * kStageBufBytes;
+        uint8_t* buf = stage + (size_t)(p.flush_mode == 0 ? (sbuf & 1) : pend) * kStageBufBytes;
         if (p.out_f32) {
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
@@ -588,15 +463,21 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         } else {
           stage_bf16(buf, r);
         }
-        note(nbase, p.splits > 1 ? 1 : 0);
-        if (pend == kOutBufs || last_chunk) flush(row0, t.z);
+        if (p.flush_mode == 0) {
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) { issue(buf, p.splits > 1 ? 1 : 0, nbase, row0, t.z); bulk_commit(); }
+          ++sbuf;
+        } else {
+          note(nbase, p.splits > 1 ? 1 : 0);
+          if (pend == kOutBufs || last_chunk) flush(row0, t.z);
+        }
         tr.ev(9);
       }
       tr.ev(10);
     }
     if (lane == 0) bulk_wait_all();
     tr.ev(15);
-    }
   }
   if (threadIdx.x == 64) tr_cta.ev(13);
   tc_fence_before();
@@ -655,7 +536,7 @@ int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
   using C_ = Cfg2<BN, NCTA>;
   static bool attr_set = false;
   auto kfn = gemm_tc2_kernel<BN, NCTA>;
-  a.epi_bytes = a.direct ? (int)C_::kDirectEpiBytes : (int)C_::epi_bytes(a.has_aux_in);
+  a.epi_bytes = (int)C_::epi_bytes(a.has_aux_in);
   a.stages = C_::stages_for((uint32_t)a.epi_bytes);
   const uint32_t smem = C_::smem_for((uint32_t)a.epi_bytes);
   if (a.stages < 2 || smem > kMaxSmem) {
@@ -742,10 +623,10 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.has_aux_out = q->aux_out ? 1 : 0;
   a.has_aux_in = (q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD) ? 1 : 0;
   a.trace = g_trace; a.trace_cap = g_trace_cap; a.trace_cta = g_trace_cta;
-  static const int direct_env = getenv("EXG_GEMM_DIRECT") ? atoi(getenv("EXG_GEMM_DIRECT")) : 1;
-  a.direct = direct_env;
-  a.c_ptr = q->C; a.auxo_ptr = q->aux_out; a.auxi_ptr = q->aux;
-  a.ldc = q->ldc; a.strideC = q->strideC; a.ldaux = q->ldaux; a.strideAux = q->strideAux;
+  static const int flush_env = getenv("EXG_GEMM_FLUSH") ? atoi(getenv("EXG_GEMM_FLUSH")) : 0;
+  a.flush_mode = flush_env;
+  static const int ablate_env = getenv("EXG_GEMM_ABLATE") ? atoi(getenv("EXG_GEMM_ABLATE")) : 0;
+  a.ablate = ablate_env;
 
   const int kblocks = (q->K + BK - 1) / BK;
   const long tm1 = (q->M + BM - 1) / BM;

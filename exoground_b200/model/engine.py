@@ -44,10 +44,26 @@ def _mask_u8(mask):
 def _self_attn_fwd(K, xn, in_w, in_b, out_w, out_b, key_pad, B, S):
     """Returns the residual-branch output (delta, compute dtype); the `x + delta` of tfm_model.py:36 is fused
     into the LayerNorm that follows (exg_add_layernorm_fwd), so the GEMM epilogue stays a pure TMA store."""
-    qkv = K.gemm(xn, in_w, bias=in_b)                                            # [M,3C]
-    o, lse = K.attn_fwd(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], key_pad, B, HEADS, S, S, SCALE)
+    qkv, o, lse = _self_attn_core(K, xn, in_w, in_b, key_pad, B, S)
     delta = K.gemm(o, out_w, bias=out_b)
     return delta, (qkv, o, lse)
+
+
+def _self_attn_core(K, xn, in_w, in_b, key_pad, B, S):
+    """qkv projection + attention; the out-projection is the caller's (fused with the add + LayerNorm that follow)."""
+    qkv = K.gemm(xn, in_w, bias=in_b)                                            # [M,3C]
+    o, lse = K.attn_fwd(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], key_pad, B, HEADS, S, S, SCALE)
+    return qkv, o, lse
+
+
+def _proj_add_ln(K, a, wT, bias, resid, g, b, T, out=None):
+    """(LN(resid + a @ wT^T + bias), resid + a @ wT^T + bias): the out-projection of a sub-block, the residual add of
+    tfm_model.py:36-37 and the LayerNorm the next sub-block opens with.  bf16: ONE kernel (exg_gemm_add_ln, the row is
+    one TMEM accumulator); fp32 parity path: GEMM + exg_add_layernorm_fwd."""
+    if T == torch.bfloat16 and K.gemm_add_ln_ok(a, wT):
+        return K.gemm_add_ln(a, wT, bias, resid, g, b, out=out)
+    d = K.gemm(a, wT, bias=bias)
+    return K.add_layernorm_fwd(d, resid, g, b, out_dtype=T, out=out)
 
 
 def _sk(sinks, i):
@@ -117,13 +133,14 @@ class EncoderStackFn(torch.autograd.Function):
             if i == 0:
                 xn, _ = K.layernorm_fwd(x, g1, b1, out_dtype=T)
             else:   # x_i = x_mid_{i-1} + ffn_{i-1}; stage i-1 = ln_1^{(i)}(x_i)  (tfm_model.py:35-38,49-55)
-                xn, x = K.add_layernorm_fwd(d2, x, g1, b1, out_dtype=T, out=stages[i - 1])
-            d1, att = _self_attn_fwd(K, xn, in_wT, in_b, out_wT, out_b, key_pad, B, S)
-            h, x_mid = K.add_layernorm_fwd(d1, x, g2, b2, out_dtype=T)
-            d2, ffn = _ffn_fwd(K, h, fc_wT, fc_b, pj_wT, pj_b)
-            saved.append((x, xn, att, x_mid, h, ffn, (in_wT, out_wT, fc_wT, pj_wT)))
+                xn, x = _proj_add_ln(K, f_prev, pj_prev[0], pj_prev[1], x, g1, b1, T, out=stages[i - 1])
+            att = _self_attn_core(K, xn, in_wT, in_b, key_pad, B, S)
+            h, x_mid = _proj_add_ln(K, att[1], out_wT, out_b, x, g2, b2, T)
+            f_prev, u = K.gemm(h, fc_wT, bias=fc_b, epilogue=ops.EPI_QGELU, want_preact=True)
+            pj_prev = (pj_wT, pj_b)
+            saved.append((x, xn, att, x_mid, h, (u, f_prev), (in_wT, out_wT, fc_wT, pj_wT)))
             x = x_mid
-        _, x = K.add_layernorm_fwd(d2, x, g_post, b_post, out_dtype=T, out=stages[L - 1])
+        _, x = _proj_add_ln(K, f_prev, pj_prev[0], pj_prev[1], x, g_post, b_post, T, out=stages[L - 1])
         ctx.saved = saved
         ctx.x_last = x
         ctx.key_pad = key_pad
@@ -198,13 +215,12 @@ class DecoderStackFn(torch.autograd.Function):
                 xn, _ = K.layernorm_fwd(x, g1, b1, out_dtype=T)
             else:
                 xn, x = K.add_layernorm_fwd(d3, x, g1, b1, out_dtype=T)
-            d1, att = _self_attn_fwd(K, xn, sin_wT, sin_b, sout_wT, sout_b, tgt_pad, B, N)
-            h2, x1 = K.add_layernorm_fwd(d1, x, g2, b2, out_dtype=T)
+            att = _self_attn_core(K, xn, sin_wT, sin_b, tgt_pad, B, N)
+            h2, x1 = _proj_add_ln(K, att[1], sout_wT, sout_b, x, g2, b2, T)
             q = K.gemm(h2, cin_wT[:C], bias=cin_b[:C])                            # [B*N, C]
             kv = K.gemm(mem, cin_wT[C:], bias=cin_b[C:])                          # [B*Sm, 2C]
             o, lse = K.attn_fwd(q, kv[:, :C], kv[:, C:], mem_pad, B, HEADS, N, Sm, SCALE)
-            d2 = K.gemm(o, cout_wT, bias=cout_b)
-            h3, x2 = K.add_layernorm_fwd(d2, x1, g3, b3, out_dtype=T)
+            h3, x2 = _proj_add_ln(K, o, cout_wT, cout_b, x1, g3, b3, T)
             d3, ffn = _ffn_fwd(K, h3, fc_wT, fc_b, pj_wT, pj_b)
             saved.append((x, xn, att, x1, h2, q, kv, o, lse, x2, h3, ffn,
                           (cin_wT, cout_wT, fc_wT, pj_wT, sin_wT, sout_wT)))

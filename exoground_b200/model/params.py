@@ -155,11 +155,20 @@ class ExgModule(torch.nn.Module):
             params = dict(self.named_parameters())
             return lambda name: params[name]
         managed = getattr(self, "_shadow_managed", False)     # a trainer's fused AdamW keeps the shadow current
-        if rebuilt or fp.shadow is None or self._shadow_stale or \
-                (not managed and (self.training or torch.is_grad_enabled())):
+        refresh = rebuilt or fp.shadow is None or self._shadow_stale or \
+            (not managed and (self.training or torch.is_grad_enabled()))
+        if not refresh and not managed:
+            # evaluation right after an external optimizer step (the reference's evaluate() follows train() with
+            # torch.optim.AdamW): in-place updates bump the parameters' version counters
+            refresh = self._param_version() != getattr(self, "_shadow_version", None)
+        if refresh:
             fp.refresh_shadow()
             self._shadow_stale = False
+            self._shadow_version = self._param_version()
         return fp.shadow_view
+
+    def _param_version(self):
+        return sum(p._version for p in self.parameters())
 
     def load_state_dict(self, state_dict, strict=True, **kw):
         # accept checkpoints saved from a DDP wrapper (keys carry "module.":

@@ -9,6 +9,7 @@ Conventions: "T" = compute dtype (torch.float32 or torch.bfloat16); rm = row map
 (group, group_stride, offset) or None for contiguous rows (see exg_rowmap in include/exg.h).
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -101,6 +102,31 @@ class CudaBackend:
         p.alpha, p.impl = float(alpha), impl
         L.check(self.lib.exg_gemm(C.byref(p), _stream()), "exg_gemm")
         return (out, pre) if want_preact else out
+
+    def gemm_add_ln_ok(self, A, W):
+        """True if (A [M,K] bf16, W [512,K] bf16) can take the fused out-projection + residual add + LayerNorm kernel."""
+        if os.environ.get("EXG_NO_GEMM_LN") or A.dtype != torch.bfloat16 or W.dtype != torch.bfloat16:
+            return False
+        if A.dim() != 2 or W.dim() != 2 or W.shape[0] != 512 or A.shape[1] != W.shape[1]:
+            return False
+        if A.stride(1) != 1 or W.stride(1) != 1:
+            return False
+        return bool(self.lib.exg_gemm_add_ln_supported(_p(A), _p(W), A.shape[0], A.shape[1], _rows2d(A), _rows2d(W)))
+
+    def gemm_add_ln(self, A, W, bias, resid, gamma, beta, *, out=None, eps=1e-5):
+        """s = resid + A @ W^T + bias (fp32, new tensor);  y = LN(s) * gamma + beta (bf16; `out` if given).
+        Returns (y, s) like add_layernorm_fwd."""
+        _cuda(A, W, bias, resid, gamma, beta, out)
+        M, Kd = A.shape
+        if out is None:
+            out = torch.empty((M, 512), dtype=torch.bfloat16, device=A.device)
+        if not (resid.is_contiguous() and out.is_contiguous() and resid.dtype == torch.float32
+                and out.dtype == torch.bfloat16 and tuple(resid.shape) == (M, 512) and tuple(out.shape) == (M, 512)):
+            raise ValueError("gemm_add_ln: resid fp32 [M,512] / out bf16 [M,512] contiguous expected")
+        s = torch.empty((M, 512), dtype=torch.float32, device=A.device)
+        L.check(self.lib.exg_gemm_add_ln(_p(A), _p(W), _p(bias), _p(resid), _p(gamma), _p(beta), float(eps), _p(s),
+                                         _p(out), M, Kd, _rows2d(A), _rows2d(W), _stream()), "exg_gemm_add_ln")
+        return out, s
 
     # ------------------------------------------------------------------ row-wise
     def layernorm_fwd(self, x, gamma, beta, *, out_dtype, out=None, out_map=None, y2_dtype=None, add=None,

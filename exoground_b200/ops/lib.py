@@ -43,6 +43,8 @@ _SIGS = {
     "exg_gemm": (C.c_int, [C.POINTER(GemmParams), vp]),
     "exg_gemm_tc_supported": (C.c_int, [C.POINTER(GemmParams)]),
     "exg_gemm_trace": (C.c_int, [vp, C.c_int, C.c_int]),
+    "exg_gemm_add_ln_supported": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_long, C.c_long]),
+    "exg_gemm_add_ln": (C.c_int, [vp, vp, vp, vp, vp, vp, C.c_float, vp, vp, C.c_int, C.c_int, C.c_long, C.c_long, vp]),
     "exg_align_finish": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
     "exg_layernorm_fwd": (C.c_int, [vp, C.c_int, vp, vp, vp, C.c_int, RowMap, vp, C.c_int, vp, C.c_long,
                                     vp, vp, C.c_long, C.c_int, C.c_float, vp]),

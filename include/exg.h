@@ -261,6 +261,17 @@ int exg_ground_loss(const float* preds, const float* gt_a, const float* gt_b, co
                     int use_center_duration, float eps, const float* thresholds, int n_thresh, float* stats,
                     float* iou, float* dpreds, void* stream);
 
+/* Out-projection GEMM with the residual add and the LayerNorm that follow it fused into the epilogue
+ * (model/tfm_model.py:22,28,34-38: `x = x + attn(..)` / `x = x + mlp(..)` and the LayerNorm the next sub-block opens with):
+ *   s = resid + A @ W^T + bias  (fp32 [M, 512]),   y = LayerNorm(s) * gamma + beta  (bf16 [M, 512]).
+ * A bf16 [M, K] (lda), W bf16 [512, K] (ldb: nn.Linear layout), bias fp32 [512] or NULL, resid / s_out fp32 [M, 512]
+ * contiguous, y_out bf16 [M, 512] contiguous.  One 128 x 512 tcgen05 tile per CTA (the width C = 512 is one TMEM
+ * accumulator), thread = row.  exg_gemm_add_ln_supported: 1 if the operands qualify (16-byte aligned rows, K >= 64). */
+int exg_gemm_add_ln_supported(const void* A, const void* W, int M, int K, long lda, long ldb);
+int exg_gemm_add_ln(const void* A, const void* W, const float* bias, const float* resid, const float* gamma,
+                    const float* beta, float eps, float* s_out, void* y_out, int M, int K, long lda, long ldb,
+                    void* stream);
+
 /* Sliding-window alignment evaluation, device side (eval/eval_zeroshot_align.py:200-237): stitches the per-window
  * similarity blocks sj / sd [W, T, N] fp32 (joint / dual logits, already divided by 0.07) of one video into
  * sim [K, vlen] = overlap-averaged (joint + dual) / 2 with the reference's `sim == 0 -> -6e4` rule, prob = softmax over

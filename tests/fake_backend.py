@@ -409,6 +409,19 @@ class TorchBackend:
         if shadow is not None:
             shadow.copy_(param)
 
+    def gemm_add_ln_ok(self, A, W):
+        import os
+        return (not os.environ.get("EXG_NO_GEMM_LN") and A.dtype == torch.bfloat16 and W.dtype == torch.bfloat16
+                and A.dim() == 2 and W.dim() == 2 and W.shape[0] == 512 and A.shape[1] % 8 == 0 and A.shape[1] >= 64)
+
+    def gemm_add_ln(self, A, W, bias, resid, gamma, beta, *, out=None, eps=1e-5):
+        s = resid + A.float() @ W.float().t() + (bias if bias is not None else 0.0)
+        y = torch.nn.functional.layer_norm(s, (512,), gamma, beta, eps).to(torch.bfloat16)
+        if out is not None:
+            out.copy_(y)
+            y = out
+        return y, s
+
     def align_finish(self, sj, sd, win, K, vlen):
         """Spec = the reference's loop (eval_zeroshot_align.py:200-222), windows in order."""
         logits = torch.zeros(K, vlen)
