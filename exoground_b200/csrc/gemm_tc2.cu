@@ -174,7 +174,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int i = 0; i < kMaxStages; ++i)
         full_addr[i] = NCTA == 2 ? mapa_u32(smem_u32(&full[i]), 0) : smem_u32(&full[i]);
       constexpr int BNL = BN / NCTA;              // B rows staged by this CTA
-      for (int tile = unit; tile < (p.ablate == 2 ? 0 : total_tiles); tile += n_units) {
+      for (int tile = unit; tile < ((p.ablate & 2) ? 0 : total_tiles); tile += n_units) {
         const TileCoord t = tile_coord(p, tile, BN, BM * NCTA, cta_rank);
         const int za = p.a_bcast ? 0 : t.z, zb = p.b_bcast ? 0 : t.z;
         const int nb0 = t.n0 + cta_rank * BNL;
@@ -221,7 +221,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         tr.ev(2);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int i = 0; i < (p.ablate == 2 ? 0 : t.nkb); ++i) {
+        for (int i = 0; i < ((p.ablate & 2) ? 0 : t.nkb); ++i) {
           mbar_wait(&full[s], ph);
           tr.ev(3);
           tc_fence_after();
@@ -322,7 +322,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const bool rows_live = row0 < p.M;
       const int n_live = min(BN, p.N - t.n0);
       int chunk_k = 0;                                    // index of the chunk within this warp's strip
-      if (p.ablate == 1) {
+      if (p.ablate & 1) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
@@ -445,6 +445,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           continue;
         }
         // ---- stage (128B-swizzled rows) and store
+        if (p.ablate & 8) { tr.ev(9); continue; }
         if (p.flush_mode == 0) {
           if (lane == 0) bulk_wait_read<kOutBufs - 1>();
           __syncwarp();
@@ -463,6 +464,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         } else {
           stage_bf16(buf, r);
         }
+        if (p.ablate & 4) { ++sbuf; tr.ev(9); continue; }
         if (p.flush_mode == 0) {
           fence_proxy_async();
           __syncwarp();

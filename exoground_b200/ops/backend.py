@@ -104,8 +104,11 @@ class CudaBackend:
         return (out, pre) if want_preact else out
 
     def gemm_add_ln_ok(self, A, W):
-        """True if (A [M,K] bf16, W [512,K] bf16) can take the fused out-projection + residual add + LayerNorm kernel."""
-        if os.environ.get("EXG_NO_GEMM_LN") or A.dtype != torch.bfloat16 or W.dtype != torch.bfloat16:
+        """True if (A [M,K] bf16, W [512,K] bf16) should take the fused out-projection + residual add + LayerNorm kernel.
+        Opt-in (EXG_GEMM_LN=1): inside the train step it measured SLOWER than GEMM + exg_add_layernorm_fwd (7.86 vs
+        7.40 ms per step, profiles/gemm_ln_r02.txt) - the 128 x 512 tile fills TMEM, so MMA and epilogue of a tile cannot
+        overlap, only M/128 <= 96 CTAs run, and its thread = row global accesses are uncoalesced."""
+        if os.environ.get("EXG_GEMM_LN", "0") != "1" or A.dtype != torch.bfloat16 or W.dtype != torch.bfloat16:
             return False
         if A.dim() != 2 or W.dim() != 2 or W.shape[0] != 512 or A.shape[1] != W.shape[1]:
             return False

@@ -411,7 +411,7 @@ class TorchBackend:
 
     def gemm_add_ln_ok(self, A, W):
         import os
-        return (not os.environ.get("EXG_NO_GEMM_LN") and A.dtype == torch.bfloat16 and W.dtype == torch.bfloat16
+        return (os.environ.get("EXG_GEMM_LN", "0") == "1" and A.dtype == torch.bfloat16 and W.dtype == torch.bfloat16
                 and A.dim() == 2 and W.dim() == 2 and W.shape[0] == 512 and A.shape[1] % 8 == 0 and A.shape[1] >= 64)
 
     def gemm_add_ln(self, A, W, bias, resid, gamma, beta, *, out=None, eps=1e-5):

@@ -173,3 +173,12 @@ def test_symmetric_infonce_matches_reference_formula():
     L["loss"].backward()
     _close(v2.grad, gv, atol=1e-5, what="dv")
     _close(t2.grad, gt, atol=1e-5, what="dt")
+
+
+def test_clip_retrieval_head_host_logic():
+    """eval/eval_zeroshot_retrieval.py:157-258 (YouCook2 retrieval head) on the op-spec backend."""
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("reference not present")
+    from tests.retrieval_cases import run_retrieval_case
+    run_retrieval_case("cpu", torch.float32)

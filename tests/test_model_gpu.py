@@ -82,3 +82,13 @@ def test_sliding_window_alignment(golden_dir, dt, tol):
     tolerance; fp32 Recall / AUC / predicted seconds exact; one batched forward == the window loop."""
     from tests.align_cases import run_align_case
     run_align_case(load_golden(golden_dir, "tan_align"), "cuda", dt, tol)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_clip_retrieval_head(dt):
+    """eval/eval_zeroshot_retrieval.py:157-258 (YouCook2 retrieval head): features 1e-4 / 2e-2, fp32 metrics exact."""
+    from oracle import ref_import
+    if not ref_import.available():
+        pytest.skip("oracle/_ref archive missing")
+    from tests.retrieval_cases import run_retrieval_case
+    run_retrieval_case("cuda", dt)

@@ -29,3 +29,7 @@ def test_cotrain_and_learn_agreement_step():
 
 def test_shape_validation():
     tc.check_shape_validation_and_shadow_reload("cpu", torch.float32)
+
+
+def test_repaired_tan_loop(tmp_path):
+    tc.check_tan_loop("cpu", torch.float32, False, tmp_path)

@@ -244,3 +244,10 @@ def test_cotrain_and_learn_agreement_step(dtype, use_graph):
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_shape_validation_and_shadow_reload(dtype):
     tc.check_shape_validation_and_shadow_reload("cuda", dtype)
+
+
+@pytest.mark.parametrize("use_graph", GRAPH)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_repaired_tan_loop(dtype, use_graph, tmp_path):
+    """train/main.py:36-157 repaired (exoground_b200/train/tan_loop.py): generic and fused modes agree."""
+    tc.check_tan_loop("cuda", dtype, use_graph, tmp_path)

@@ -198,3 +198,67 @@ def check_shape_validation_and_shadow_reload(device, dtype):
         m.load_state_dict(new)
         fp = m.flat_params()
         assert torch.equal(fp.shadow_view("video_pre_proj.weight"), m.video_pre_proj.weight.detach().to(torch.bfloat16))
+
+
+def check_tan_loop(device, dtype, use_graph, tmp_path):
+    """The repaired train/main.py::train loop (exoground_b200/train/tan_loop.py): generic mode (autograd + torch AdamW +
+    clip_gradients + LambdaLR + runtime checkpoint) and fused mode (TanTrainStep) over the same synthetic loader in the
+    collate format of data/loader_egoexo4d_tan.py:333-341 give the same epoch losses and parameters."""
+    import math
+    import types
+    from exoground_b200.train import tan_loop
+    fp32 = dtype == torch.float32
+    lr, wd, eps, clip = 1e-3, 1e-2, 1e-4, 0.05
+
+    def loader():
+        out = []
+        for s in (5, 6, 7):
+            b = _batch(seed=s)
+            out.append({"video": b["video"], "padding_mask": b["video_padding_mask"].long(), "start": b["start"],
+                        "end": b["end"], "narration_features": b["text"],
+                        "narration_padding_mask": b["text_padding_mask"], "metadata": {}})
+        return out
+
+    def args_(path):
+        a = synth.tan_args(loss_threshold=0.0, use_alignability_head=0)
+        rows = []
+        plot = types.SimpleNamespace(add_data=lambda k, v, it: rows.append((k, float(v), it)))
+        for k, v in dict(rank=0, backprop_freq=1, clip_grad=clip, iteration=0, runtime_save_iter=2, model_path=str(path),
+                         train_plotter=plot).items():
+            setattr(a, k, v)
+        a.rows = rows
+        return a
+
+    def sched(opt_or_none, get_lr=None):
+        lam = lambda it: (it + 1) / 2 if it < 2 else 0.5 * (1 + math.cos(math.pi * (it - 2) / 10))
+        if opt_or_none is None:      # a scheduler needs an optimizer object: one dummy parameter
+            opt_or_none = torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=lr)
+        return torch.optim.lr_scheduler.LambdaLR(opt_or_none, lam)
+
+    import os
+    pg, pf = tmp_path / "generic", tmp_path / "fused"
+    os.makedirs(pg), os.makedirs(pf)
+    # generic
+    mG = _model(dtype).to(device); mG.random_pos_start = 0
+    optG = _torch_adamw(mG, lr, wd, eps)
+    aG = args_(pg)
+    scaler = torch.amp.GradScaler("cuda", enabled=False)
+    sG = sched(optG)
+    avgG = [tan_loop.train(loader(), mG, optG, sG, scaler, device, ep, aG) for ep in range(2)]
+    # fused
+    mF = _model(dtype); mF.random_pos_start = 0
+    aF = args_(pf)
+    trF = TanTrainStep(mF, aF, B, T, N, DIN, DIN, device=device, use_graph=use_graph, lr=lr, wd=wd, eps=eps,
+                       clip_grad=clip)
+    sF = sched(None)
+    avgF = [tan_loop.train(loader(), mF, None, sF, None, device, ep, aF, fused_step=trF) for ep in range(2)]
+    assert aG.iteration == aF.iteration == 6
+    assert np.allclose(avgG, avgF, rtol=1e-4 if fp32 else 3e-2), (avgG, avgF)
+    if fp32:
+        _assert_params_close(mF, mG, lr, 6, "tan_loop fused vs generic")
+    # both wrote a runtime checkpoint whose optimizer state a torch.optim.AdamW over the policy groups accepts
+    for path, m in ((pg, mG), (pf, mF)):
+        ck = torch.load(os.path.join(path, "runtime.pth.tar"), weights_only=False)
+        assert ck["iteration"] == 6 and set(ck["optimizer"]) == {"state", "param_groups"}
+        _torch_adamw(m, lr, wd, eps).load_state_dict(ck["optimizer"])
+    assert any(k == "train/lr" for k, _, _ in aG.rows) and any(k == "global/loss" for k, _, _ in aF.rows)
