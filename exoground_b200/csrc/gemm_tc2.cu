@@ -50,6 +50,11 @@ struct Tc2Args {
   unsigned long long* trace;   // optional per-role event log of ONE CTA (exg_gemm_trace; scripts/gemm_trace.py)
   int trace_cap, trace_cta;
   int epi_bytes;               // shared memory of the epilogue region (staging buffers + bias strips)
+  // 0: every staged chunk leaves with its own proxy fence + TMA store (the buffer it reuses was stored two chunks
+  //    ago: a whole tile of slack for the store's shared-memory read, ~2000 cycles measured);
+  // 1: the chunks of a tile leave as one fence + store group (fewer fences, but the next tile's first chunk then waits
+  //    for stores issued a moment ago) - measured slower inside the train step (profiles/gemm_epilogue_r02.txt)
+  int flush_mode;
   // development: 1 = the epilogue only waits for / releases the accumulator (no TMEM reads, math or stores): time of
   // the operand feed + MMA pipeline alone; 2 = no TMA loads and no MMAs (accumulator stages are handed over at once):
   // time of the epilogue + stores alone.  Results are garbage in both modes (scripts/bench_gemm.py ABLATE=...).
@@ -238,11 +243,6 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
   } else {
     // ===================== epilogue =====================
-    // Each warp owns a 32-lane quarter of the accumulator and, with the other warp of that quarter, alternate chunks of
-    // its columns (64 per chunk for bf16 outputs, 32 for fp32: one 128-byte staging row).  The accumulator is read in
-    // 32-column sub-chunks with the NEXT sub-chunk's tcgen05.ld already in flight (register double buffer): TMEM reads
-    // run at ~64 B/clk per SM (profiles/gemm_ablation_r02.txt: 128 x 256 fp32 = 2048 cycles of the 4096-cycle K = 512
-    // MMA time), so their latency must not be added to the math / staging time.
     const int ew = warp - 2;                      // staging slot
     Tracer tr(p, 2 + ew);
     if (lane != 0) tr.row = nullptr;
@@ -252,22 +252,51 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint8_t* stage = epi_smem + (size_t)ew * n_bufs * kStageBufBytes;
     float* bias_s = reinterpret_cast<float*>(epi_smem + p.epi_bytes - kEpiWarps * kBiasStripBytes) + ew * 128;
     uint32_t ti = 0;
-    const bool f32o = p.out_f32 != 0;
-    const int cols_per_chunk = f32o ? 32 : 64;
+    const int cols_per_chunk = p.out_f32 ? 32 : 64;
     const int c_first = half * cols_per_chunk, c_step = 2 * cols_per_chunk;
-    constexpr int NSUB = BN / 64;                 // 32-column sub-chunks per warp and tile (the warp owns BN / 2 columns)
     uint64_t* my_aux_bar = aux_bar + kAuxBufs * ew;
     uint32_t ci = 0;                              // running chunk index of this warp (aux ring position)
-    uint32_t sbuf = 0;                            // running staging-buffer index (plain epilogues)
     const uint32_t tmem_empty_addr[2] = {NCTA == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u,
                                          NCTA == 2 ? mapa_u32(smem_u32(&tmem_empty[1]), 0) : 0u};
     const bool use_alpha = p.alpha != 1.0f;
-    // this lane's float4 of the warp's bias strip: strip element e = 4 * lane belongs to sub-chunk e / 32
-    const int b_sub = (lane * 4) >> 5, b_within = (lane * 4) & 31;
-    auto sub_col = [&](int sub) {                 // first column (within the tile) of sub-chunk `sub`
-      return f32o ? c_first + sub * c_step : c_first + (sub >> 1) * c_step + (sub & 1) * 32;
+    // this lane's float4 of the warp's bias strip: strip element e = 4 * lane covers chunk e / cols_per_chunk
+    const int b_chunk = (lane * 4) / cols_per_chunk, b_within = (lane * 4) % cols_per_chunk;
+    const int b_col = c_first + b_chunk * c_step + b_within;
+    // plain epilogues: chunks are staged into the warp's buffers and leave as ONE fence + store group per
+    // kOutBufs buffers (one per tile for bf16 outputs), instead of a proxy fence per chunk
+    uint32_t pend = 0, sbuf = 0;
+    static_assert(kOutBufs == 2, "the pending-store bookkeeping below is written for two buffers");
+    int pend_x0 = 0, pend_x1 = 0, pend_k0 = 0, pend_k1 = 0;    // kind: 0 store C, 1 reduce-add C, 2 store aux-out
+    auto issue = [&](const uint8_t* b, int kind, int x, int row0, int z) {
+      if (kind == 2) tma_store_3d(&tmAux, b, x, row0, z);
+      else if (kind == 1) tma_reduce_add_3d(&tmC, b, x, row0, z);
+      else tma_store_3d(&tmC, b, x, row0, z);
     };
-    const int b_col = sub_col(b_sub) + b_within;
+    auto flush = [&](int row0, int z) {
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        issue(stage, pend_k0, pend_x0, row0, z);
+        if (pend > 1) issue(stage + kStageBufBytes, pend_k1, pend_x1, row0, z);
+        bulk_commit();
+      }
+      pend = 0;
+    };
+    auto note = [&](int x, int kind) {
+      if (pend == 0) { pend_x0 = x; pend_k0 = kind; } else { pend_x1 = x; pend_k1 = kind; }
+      ++pend;
+    };
+    auto stage_bf16 = [&](uint8_t* buf, const uint32_t (&r)[64]) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        uint4 q;
+        q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
+        q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
+        q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
+        q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
+        *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
+      }
+    };
     if (p.has_aux_in && lane == 0 && unit < total_tiles) {
       const TileCoord t0 = tile_coord(p, unit, BN, BM * NCTA, cta_rank);
       mbar_arrive_expect_tx(&my_aux_bar[0], kStageBufBytes);
@@ -279,7 +308,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       // the tile's bias values are requested BEFORE the wait for the accumulator (their L2 latency hides behind it) and
       // parked in shared memory; the math below reads them as warp-wide broadcasts
       float4 bpre = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (p.bias && b_sub < NSUB && t.n0 + b_col < p.N) bpre = __ldg(reinterpret_cast<const float4*>(p.bias + t.n0 + b_col));
+      if (p.bias && b_col < BN && t.n0 + b_col < p.N) bpre = __ldg(reinterpret_cast<const float4*>(p.bias + t.n0 + b_col));
       mbar_wait(&tmem_full[as], aph);
       tr.ev(5);
       tc_fence_after();
@@ -292,25 +321,20 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const int row0 = t.m0 + lg * 32;
       const bool rows_live = row0 < p.M;
       const int n_live = min(BN, p.N - t.n0);
+      int chunk_k = 0;                                    // index of the chunk within this warp's strip
       if (p.ablate & 1) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
         continue;
       }
-      uint32_t rr[2][32];
-      uint4 ax[8];
-      if (rows_live && sub_col(0) < n_live) tmem_ld_32x32(taddr + sub_col(0), rr[0]);
-#pragma unroll
-      for (int sub = 0; sub < NSUB; ++sub) {
-        uint32_t (&r)[32] = rr[sub & 1];
-        const int c0 = sub_col(sub);
-        const bool live = rows_live && c0 < n_live;            // warp-uniform
-        const bool first_part = f32o || (sub & 1) == 0;        // this sub-chunk opens a staging row
-        const bool last_part = f32o || (sub & 1) == 1;         // ... / completes it
-        const int part = f32o ? 0 : (sub & 1);
-        const int nbase = t.n0 + c0 - part * 32;               // first column of the chunk this sub-chunk belongs to
-        if (p.has_aux_in && first_part) {
+#pragma unroll 1
+      for (int c0 = c_first; c0 < BN; c0 += c_step, ++chunk_k) {
+        const bool live = rows_live && c0 < n_live;      // warp-uniform
+        const bool last_chunk = c0 + c_step >= BN;
+        uint32_t r[64];
+        uint4 ax[8];
+        if (p.has_aux_in) {
           // prefetch the aux chunk after this one (same tile, or first chunk of this CTA's next tile) into the ring
           // buffer after this one: its last user is the store issued two chunks ago
           if (lane == 0) {
@@ -334,26 +358,34 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             ax[u] = *reinterpret_cast<const uint4*>(abuf + lane * 128 + ((u ^ (lane & 7)) << 4));
           ++ci;
         }
-        if (live) tmem_ld_wait();
-        // next sub-chunk's TMEM read goes out before this one is processed
-        if (sub + 1 < NSUB && rows_live && sub_col(sub + 1) < n_live) tmem_ld_32x32(taddr + sub_col(sub + 1), rr[(sub + 1) & 1]);
+        if (live) {
+          tmem_ld_32x32(taddr + c0, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+          if (!p.out_f32) tmem_ld_32x32(taddr + c0 + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+          tmem_ld_wait();
+        }
         tr.ev(6);
-        if (sub == NSUB - 1) {
+        if (last_chunk) {
           // all TMEM reads of this tile are done: hand the accumulator stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) { if (NCTA == 2) mbar_arrive_remote(tmem_empty_addr[as]); else mbar_arrive(&tmem_empty[as]); }
         }
-        if (!live) continue;
+        if (!live) {
+          if (last_chunk && pend) flush(row0, t.z);
+          continue;
+        }
         // ---- math in the thread = row layout
+        const int ncols = cols_per_chunk;
+        const int nbase = t.n0 + c0;
         if (use_alpha) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
         }
         if (p.bias) {
-          const float* bs = bias_s + sub * 32;
+          const float* bs = bias_s + chunk_k * cols_per_chunk;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
+          for (int j = 0; j < 64; j += 4) {
+            if (j >= ncols) break;
             const float4 b = *reinterpret_cast<const float4*>(bs + j);         // same address in every lane: broadcast
             r[j] = __float_as_uint(__uint_as_float(r[j]) + b.x);
             r[j + 1] = __float_as_uint(__uint_as_float(r[j + 1]) + b.y);
@@ -361,43 +393,34 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             r[j + 3] = __float_as_uint(__uint_as_float(r[j + 3]) + b.w);
           }
         }
-        if (p.ablate & 8) continue;
-        // staging buffers of this chunk: plain = ring of kOutBufs; aux-out = both (pre-activation, output); aux-in = the
-        // buffer the aux rows came in
-        uint8_t* buf_pre = stage + (size_t)(sbuf & 1) * kStageBufBytes;
-        uint8_t* buf = p.has_aux_in ? stage + (size_t)((ci - 1) % kAuxBufs) * kStageBufBytes
-                                    : stage + (size_t)((p.has_aux_out ? sbuf + 1 : sbuf) & 1) * kStageBufBytes;
-        if (first_part && !p.has_aux_in) {
-          // the store(s) that last used the buffer(s) have finished reading
-          if (lane == 0) { if (p.has_aux_out) bulk_wait_read<0>(); else bulk_wait_read<kOutBufs - 1>(); }
-          __syncwarp();
-        }
-        if (p.has_aux_in && first_part) __syncwarp();          // every lane has taken its aux row out of the buffer
-        tr.ev(8);
-        auto stage32_bf16 = [&](uint8_t* b) {
-#pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            uint4 q;
-            q.x = pack_bf16x2(__uint_as_float(r[u * 8 + 0]), __uint_as_float(r[u * 8 + 1]));
-            q.y = pack_bf16x2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3]));
-            q.z = pack_bf16x2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5]));
-            q.w = pack_bf16x2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7]));
-            *reinterpret_cast<uint4*>(b + lane * 128 + (((part * 4 + u) ^ (lane & 7)) << 4)) = q;
+        // ---- optional second output: the pre-activation (bf16), staged first
+        if (p.has_aux_out) {
+          if (p.flush_mode == 0) {
+            if (lane == 0) bulk_wait_read<kOutBufs - 1>();      // the store that last used this buffer is done reading
+            __syncwarp();
+            stage_bf16(stage + (size_t)(sbuf & 1) * kStageBufBytes, r);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) { tma_store_3d(&tmAux, stage + (size_t)(sbuf & 1) * kStageBufBytes, nbase, row0, t.z); bulk_commit(); }
+            ++sbuf;
+          } else {
+            if (pend == 0) { if (lane == 0) bulk_wait_read<0>(); __syncwarp(); }
+            stage_bf16(stage + (size_t)pend * kStageBufBytes, r);
+            note(nbase, 2);
+            if (pend == kOutBufs) flush(row0, t.z);
           }
-        };
-        if (p.has_aux_out) stage32_bf16(buf_pre);              // the pre-activation (bf16)
+        }
         if (p.epilogue == EXG_EPI_QGELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(quick_gelu_fast(__uint_as_float(r[j])));
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(quick_gelu_fast(__uint_as_float(r[j])));
         } else if (p.epilogue == EXG_EPI_RELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
+          for (int j = 0; j < 64; ++j) if (j < ncols) r[j] = __float_as_uint(fmaxf(__uint_as_float(r[j]), 0.f));
         } else if (p.epilogue == EXG_EPI_QGELU_BWD || p.epilogue == EXG_EPI_RELU_BWD) {
           const bool gelu = p.epilogue == EXG_EPI_QGELU_BWD;
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            const uint4 a4 = ax[(sub & 1) * 4 + u];            // (aux-in epilogues write bf16: part == sub & 1)
-            const uint32_t w[4] = {a4.x, a4.y, a4.z, a4.w};
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t w[4] = {ax[u].x, ax[u].y, ax[u].z, ax[u].w};
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
               const float a0 = __uint_as_float(w[h] << 16), a1 = __uint_as_float(w[h] & 0xffff0000u);
@@ -409,28 +432,48 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
         }
         tr.ev(7);
-        // ---- stage (128B-swizzled rows)
-        if (f32o) {
+        if (p.has_aux_in) {
+          // stage into the buffer this chunk's aux rows came in (they are in registers) and store it right away
+          uint8_t* buf = stage + (size_t)((ci - 1) % kAuxBufs) * kStageBufBytes;
+          __syncwarp();                   // every lane has taken its aux row out of the buffer
+          tr.ev(8);
+          stage_bf16(buf, r);
+          fence_proxy_async();            // also orders the generic reads of the aux rows before later TMA writes
+          __syncwarp();
+          if (lane == 0) { tma_store_3d(&tmC, buf, nbase, row0, t.z); bulk_commit(); }
+          tr.ev(9);
+          continue;
+        }
+        // ---- stage (128B-swizzled rows) and store
+        if (p.ablate & 8) { tr.ev(9); continue; }
+        if (p.flush_mode == 0) {
+          if (lane == 0) bulk_wait_read<kOutBufs - 1>();
+          __syncwarp();
+        } else if (pend == 0) {
+          if (lane == 0) bulk_wait_read<0>();
+          __syncwarp();
+        }
+        tr.ev(8);
+        uint8_t* buf = stage + (size_t)(p.flush_mode == 0 ? (sbuf & 1) : pend) * kStageBufBytes;
+        if (p.out_f32) {
 #pragma unroll
           for (int u = 0; u < 8; ++u) {
             const uint4 q = make_uint4(r[u * 4], r[u * 4 + 1], r[u * 4 + 2], r[u * 4 + 3]);
             *reinterpret_cast<uint4*>(buf + lane * 128 + ((u ^ (lane & 7)) << 4)) = q;
           }
         } else {
-          stage32_bf16(buf);
+          stage_bf16(buf, r);
         }
-        if (!last_part && c0 + 32 < n_live) continue;          // the row's second half follows
-        if (p.ablate & 4) { sbuf += p.has_aux_out ? 2 : 1; continue; }
-        // ---- the chunk is complete: one proxy fence, then its TMA store(s)
-        fence_proxy_async();            // (aux-in: also orders the generic reads of the aux rows before later TMA writes)
-        __syncwarp();
-        if (lane == 0) {
-          if (p.has_aux_out) tma_store_3d(&tmAux, buf_pre, nbase, row0, t.z);
-          if (p.splits > 1) tma_reduce_add_3d(&tmC, buf, nbase, row0, t.z);
-          else tma_store_3d(&tmC, buf, nbase, row0, t.z);
-          bulk_commit();
+        if (p.ablate & 4) { ++sbuf; tr.ev(9); continue; }
+        if (p.flush_mode == 0) {
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) { issue(buf, p.splits > 1 ? 1 : 0, nbase, row0, t.z); bulk_commit(); }
+          ++sbuf;
+        } else {
+          note(nbase, p.splits > 1 ? 1 : 0);
+          if (pend == kOutBufs || last_chunk) flush(row0, t.z);
         }
-        if (!p.has_aux_in) sbuf += p.has_aux_out ? 2 : 1;
         tr.ev(9);
       }
       tr.ev(10);
@@ -531,6 +574,12 @@ bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 unsigned long long* g_trace = nullptr;
 int g_trace_cap = 0, g_trace_cta = 0;
 
+double wave_eff(long tiles) {
+  const long sms = exg_num_sms();
+  const long waves = (tiles + sms - 1) / sms;
+  return (double)tiles / (double)(waves * sms);
+}
+
 }  // namespace
 
 // Pipeline event log of the persistent GEMM (development aid, scripts/gemm_trace.py): while `buf` (device, 11 rows of
@@ -576,6 +625,8 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   a.has_aux_out = q->aux_out ? 1 : 0;
   a.has_aux_in = (q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD) ? 1 : 0;
   a.trace = g_trace; a.trace_cap = g_trace_cap; a.trace_cta = g_trace_cta;
+  static const int flush_env = getenv("EXG_GEMM_FLUSH") ? atoi(getenv("EXG_GEMM_FLUSH")) : 0;
+  a.flush_mode = flush_env;
   static const int ablate_env = getenv("EXG_GEMM_ABLATE") ? atoi(getenv("EXG_GEMM_ABLATE")) : 0;
   a.ablate = ablate_env;
 

@@ -106,10 +106,23 @@ class ExoGroundingTransformer(ExgModule):
                 raise ValueError("exoground_b200 runs on CUDA only (no CPU fallback); move inputs to the GPU")
 
     def _draw(self, n):
+        """Random positional offset (exo_ground_model.py:305,338,377: np.random.randint(0, n/2)).  A trainer that
+        replays a captured CUDA graph installs device-side offsets (`_pos_offsets`: 0-d int64 CUDA tensors it refreshes
+        before every replay), consumed in draw order inside forward() only."""
+        offs = getattr(self, "_pos_offsets", None) if getattr(self, "_in_forward", False) else None
+        if offs is not None and self.random_pos_start:
+            i = self._pos_cursor
+            self._pos_cursor = i + 1
+            return offs[i]
         return int(np.random.randint(0, int(n / 2))) if self.random_pos_start else 0
 
     def _pos_ln(self, table, p0, size, interpolate_from, repeat=1):
-        rows = interp_rows(table, interpolate_from, size) if interpolate_from else table[p0:p0 + size]
+        if interpolate_from:
+            rows = interp_rows(table, interpolate_from, size)
+        elif torch.is_tensor(p0):      # device-side offset (graph replay): rows p0 .. p0 + size - 1
+            rows = table.index_select(0, p0 + torch.arange(size, device=table.device))
+        else:
+            rows = table[p0:p0 + size]
         if repeat > 1:
             rows = rows.repeat(repeat, 1)
         return Fn.LayerNormFn.apply(rows.contiguous(), self.ln_position_init.weight, self.ln_position_init.bias,
@@ -213,6 +226,16 @@ class ExoGroundingTransformer(ExgModule):
     def forward(self, video_embed, lang_embed, video_padding_mask, lang_padding_mask, audio_embed=None,
                 audio_padding_mask=None, egocentric_video_embed=None, view_mask=None, interpolate_from=None):
         self._check(video_embed, lang_embed, audio_embed)
+        self._pos_cursor = 0
+        self._in_forward = True
+        try:
+            return self._forward(video_embed, lang_embed, video_padding_mask, lang_padding_mask, audio_embed,
+                                 audio_padding_mask, egocentric_video_embed, view_mask, interpolate_from)
+        finally:
+            self._in_forward = False
+
+    def _forward(self, video_embed, lang_embed, video_padding_mask, lang_padding_mask, audio_embed,
+                 audio_padding_mask, egocentric_video_embed, view_mask, interpolate_from):
         wT = self._weights()
         B, T, _ = video_embed.shape
         N = lang_embed.shape[1]

@@ -70,6 +70,38 @@ def ground_loss_core(preds, gt_a, gt_b, text_padding_mask, use_center_duration, 
                                  bool(use_center_duration), float(eps), tuple(float(t) for t in thresholds))
 
 
+def grounding_dict(stats, host, use_center_duration, thresholds):
+    """The logged entries of get_grounding_loss_reg_head (loss_egoexo4d.py:102-137) from the kernel's statistics:
+    `stats` = tensor (mean|d0|, mean|d1|, mean IoU, n_valid, counts...) on any device, `host` = the same as floats."""
+    d = {}
+    if use_center_duration:
+        d['Center L1 loss'] = stats[0]
+        d['Duration L1 loss'] = stats[1]
+    else:
+        d['Timestamp L1 loss'] = (stats[0] + stats[1]) / 2
+    d['IoU loss'] = 1.0 - stats[2]
+    d['mean IoU'] = stats[2]
+    n_valid = host[3]
+    for i, theta in enumerate(thresholds):
+        d[f'IoU>={theta}'] = host[4 + i] / n_valid
+    return d
+
+
+def view_invariant_dict(host, view_rank_names, means):
+    """The logged entries of get_view_invariant_loss (loss_egoexo4d.py:173-198): per-camera-rank bins from the
+    per-(clip, second) values `host` = float64 [4, B*T] (L1, pos cosine, neg cosine, InfoNCE) and the four means."""
+    d = {}
+    names, inverse = np.unique(np.asarray(flatten_list_of_lists(view_rank_names), dtype=object).astype(str),
+                               return_inverse=True)
+    counts = np.bincount(inverse, minlength=len(names))
+    for metric, vals in zip(("L1", "pos_cosine", "avg_neg_cosine", "InfoNCE"), host):
+        totals = np.bincount(inverse, weights=vals, minlength=len(names))        # float64 sums, as the reference's
+        for name, tot, cnt in zip(names, totals, counts):
+            d[f"Rank {name} {metric}"] = {'total': float(tot), 'count': int(cnt), 'mean': float(tot / cnt)}
+    d["L1 loss"], d["Pos cosine sim"], d["Avg neg cosine sim"], d['InfoNCE loss'] = means
+    return d
+
+
 def get_grounding_loss_reg_head(input_data, logits, text_padding_mask, args):
     """loss_egoexo4d.py:73-145."""
     preds = logits['interval_preds']
@@ -84,18 +116,7 @@ def get_grounding_loss_reg_head(input_data, logits, text_padding_mask, args):
     thresholds = list(args.iou_thresholds)
     loss, stats, iou_all = ground_loss_core(preds, gt_a, gt_b, text_padding_mask, args.use_center_duration,
                                             args.iou_loss_eps, thresholds)
-    loss_dict = {}
-    if args.use_center_duration:
-        loss_dict['Center L1 loss'] = stats[0]
-        loss_dict['Duration L1 loss'] = stats[1]
-    else:
-        loss_dict['Timestamp L1 loss'] = (stats[0] + stats[1]) / 2
-    loss_dict['IoU loss'] = 1.0 - stats[2]
-    loss_dict['mean IoU'] = stats[2]
-    host = stats.tolist()                      # the reference's .item() calls (:121-122): one read-back here
-    n_valid = host[3]
-    for i, theta in enumerate(thresholds):
-        loss_dict[f'IoU>={theta}'] = host[4 + i] / n_valid
+    loss_dict = grounding_dict(stats, stats.tolist(), args.use_center_duration, thresholds)   # one read-back (:121-122)
     iou = iou_all[~text_padding_mask.reshape(-1).bool()]
     if getattr(args, 'test', False):
         cam_ranks = get_mode_cam_rank(input_data['metadata']['per_second_views'])
@@ -159,23 +180,12 @@ def get_view_invariant_loss(input_data, logits, args):
         same_idx = same_feat = None
     nce, l1, pos_cos, neg_cos = _xview(features, ego_seq, pos_idx, neg_idx, same_idx, same_feat,
                                        getattr(args, 'only_same_view_negative', False), INV_TEMP)
-    loss_dict = {}
     # per-camera-rank bins (reference :173-187, one .item() per element there; one read-back here)
     host = torch.stack((l1, pos_cos, neg_cos, nce.detach()), dim=0).reshape(4, -1).double().cpu().numpy()
-    names, inverse = np.unique(np.asarray(flatten_list_of_lists(view_rank_names), dtype=object).astype(str),
-                               return_inverse=True)
-    counts = np.bincount(inverse, minlength=len(names))
-    for metric, vals in zip(("L1", "pos_cosine", "avg_neg_cosine", "InfoNCE"), host):
-        totals = np.bincount(inverse, weights=vals, minlength=len(names))        # float64 sums, as the reference's
-        for name, tot, cnt in zip(names, totals, counts):
-            loss_dict[f"Rank {name} {metric}"] = {'total': float(tot), 'count': int(cnt), 'mean': float(tot / cnt)}
-    loss_dict["L1 loss"] = l1.mean()
-    loss_dict["Pos cosine sim"] = pos_cos.mean()
-    loss_dict["Avg neg cosine sim"] = neg_cos.mean()
     if not args.use_distill_nce_loss:
         raise UnboundLocalError("total_loss is undefined unless args.use_distill_nce_loss "
                                 "(reference loss_egoexo4d.py:195-198 fails the same way)")
-    loss_dict['InfoNCE loss'] = nce.mean()
+    loss_dict = view_invariant_dict(host, view_rank_names, (l1.mean(), pos_cos.mean(), neg_cos.mean(), nce.mean()))
     loss_dict['loss'] = loss_dict['InfoNCE loss'].clone()
     return loss_dict, None
 
