@@ -642,7 +642,10 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   static const int no_pair = getenv("EXG_NO_GEMM_PAIR") ? atoi(getenv("EXG_NO_GEMM_PAIR")) : 0;
   const bool splittable = q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && kblocks >= 8;
   int ncta = 1;
-  if (!no_pair && q->M > BM && q->epilogue == EXG_EPI_NONE && !q->bias && !q->aux_out) {
+  // (aux-in epilogues: with the cheap peer arrive the pair wins there too, 47.6 -> 43.0 us on du + QuickGELU',
+  // profiles/gemm_ablation_r02.txt; bias / aux-out epilogues stay single-CTA: within noise either way)
+  const bool aux_in_epi = q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD;
+  if (!no_pair && q->M > BM && (q->epilogue == EXG_EPI_NONE || aux_in_epi) && !q->bias && !q->aux_out) {
     const long tn = (q->N + bn - 1) / bn;
     const long t1 = tm1 * tn * q->batch, t2 = ((q->M + 2 * BM - 1) / (2 * BM)) * tn * q->batch;
     const long sms = exg_num_sms(), pairs = sms / 2;
