@@ -62,14 +62,14 @@ def run_exo(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
         pg = dist.group.WORLD
-    B, T, N = a.batch or 16, 1024, 32
+    B, T, N, L = a.batch or 16, 1024, 64, a.layers             # SURVEY cfg-3: E6D6, T=1024, N=64, 768-d / 4096-d
     torch.manual_seed(0); np.random.seed(0)
-    m = ExoGroundingTransformer(2, 2, video_embed_dim=768, text_embed_dim=4096, use_distill_nce_loss=True,
+    m = ExoGroundingTransformer(L, L, video_embed_dim=768, text_embed_dim=4096, use_distill_nce_loss=a.distill,
                                 random_pos_start=0, compute_dtype=torch.bfloat16)   # T = the whole 1024-row table
-    b = synth.exo_batch(B=B, T=T, N=N, d_video=768, d_text=4096, d_ego=768, seed=888 + rank)
+    b = synth.exo_batch(B=B, T=T, N=N, d_video=768, d_text=4096, d_ego=768 if a.distill else None, seed=888 + rank)
     b = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in b.items()}
-    args = synth.exo_args(use_distill_nce_loss=True, same_view_negative=True)
-    st = ExoTrainStep(m, args, device=f"cuda:{local}", process_group=pg)
+    args = synth.exo_args(use_distill_nce_loss=a.distill, same_view_negative=a.distill)
+    st = ExoTrainStep(m, args, device=f"cuda:{local}", process_group=pg, use_graph=not a.no_graph)
 
     def step():
         st.step(b, next_batch=b)      # double-buffered input: every step contains one full H2D copy (copy stream)
@@ -79,14 +79,26 @@ def run_exo(a):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t[0])
+    graph, st.graph = st.graph, None           # per-class breakdown from one eager step
+    ug, st.use_graph = st.use_graph, False
     bd = breakdown(step)
+    st.graph, st.use_graph = graph, ug
+    # algorithmic train FLOPs per clip (SURVEY §8d formulas): unimodal video + text encoders, joint encoder, decoder
+    C, F = 512, 2048
+    per_tok = lambda S: 2 * C * 3 * C + 2 * C * C + 4 * C * F + 4 * S * C
+    dec_tok = per_tok(N) + (2 * C * C + 2 * C * C + 4 * T * C)          # self block + cross q / out proj + cross attn
+    fwd = (T * 2 * 768 * C + N * 2 * 4096 * C + L * T * per_tok(T) + L * N * per_tok(N) + L * (T + N) * per_tok(T + N)
+           + L * (N * dec_tok + T * 2 * C * 2 * C) + (T * 2 * C * 768 if a.distill else 0))
+    gf = 3 * fwd / 1e9
     if rank == 0:
-        print(json.dumps({"config": "ExoGround E2D2 keystep grounding, full train step: H2D + fwd + grounding / "
-                                    "view-invariant InfoNCE loss + bwd + grad all-reduce + AdamW (BASELINE configs[2])",
+        cps = B * world / (ms * 1e-3)
+        print(json.dumps({"config": f"ExoGround E{L}D{L} keystep grounding, full train step: H2D + fwd + grounding"
+                                    f"{' / view-invariant InfoNCE' if a.distill else ''} loss + bwd + grad all-reduce + "
+                                    f"AdamW (BASELINE configs[2])",
                           "T": T, "N": N, "n_gpus": world, "per_gpu_batch": B, "dtype": "bf16",
-                          "ms_per_step": round(ms, 3), "clips_per_s": round(B * world / (ms * 1e-3), 1),
-                          "h2d_bytes_per_step": st.h2d_bytes,
-                          "note": "eager (no CUDA graph): the reference loss dict carries host-side per-rank statistics",
+                          "ms_per_step": round(ms, 3), "clips_per_s": round(cps, 1),
+                          "train_gflop_per_clip": round(gf, 1), "model_tflops_per_gpu": round(cps / world * gf / 1e3, 1),
+                          "h2d_bytes_per_step": st.h2d_bytes, "cuda_graph": bool(ug),
                           "breakdown": bd}), flush=True)
     if world > 1:
         dist.barrier()
@@ -149,6 +161,9 @@ def main():
     ap.add_argument("--sweep", action="store_true")
     ap.add_argument("--align", action="store_true")
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--layers", type=int, default=6, help="--exo: encoder = decoder depth (SURVEY cfg-3: 6)")
+    ap.add_argument("--distill", action="store_true", help="--exo: with the ego-distillation InfoNCE (768-d ego features)")
+    ap.add_argument("--no-graph", action="store_true", help="--exo: eager step instead of the CUDA-graph replay")
     ap.add_argument("--videos", type=int, default=80)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)

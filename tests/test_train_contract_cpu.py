@@ -33,3 +33,8 @@ def test_shape_validation():
 
 def test_repaired_tan_loop(tmp_path):
     tc.check_tan_loop("cpu", torch.float32, False, tmp_path)
+
+
+@pytest.mark.parametrize("distill", [False, True])
+def test_exo_step_device_loss_matches_get_loss(distill):
+    tc.check_exo_step_paths("cpu", torch.float32, distill)

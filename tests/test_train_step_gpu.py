@@ -251,3 +251,11 @@ def test_shape_validation_and_shadow_reload(dtype):
 def test_repaired_tan_loop(dtype, use_graph, tmp_path):
     """train/main.py:36-157 repaired (exoground_b200/train/tan_loop.py): generic and fused modes agree."""
     tc.check_tan_loop("cuda", dtype, use_graph, tmp_path)
+
+
+@pytest.mark.parametrize("random_pos", [0, 1])
+@pytest.mark.parametrize("distill", [False, True])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_exo_step_graph_matches_eager(dtype, distill, random_pos):
+    """ExoTrainStep: CUDA-graph replay == eager device-loss step == eager step through get_loss."""
+    tc.check_exo_step_paths("cuda", dtype, distill, random_pos)

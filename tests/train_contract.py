@@ -262,3 +262,41 @@ def check_tan_loop(device, dtype, use_graph, tmp_path):
         assert ck["iteration"] == 6 and set(ck["optimizer"]) == {"state", "param_groups"}
         _torch_adamw(m, lr, wd, eps).load_state_dict(ck["optimizer"])
     assert any(k == "train/lr" for k, _, _ in aG.rows) and any(k == "global/loss" for k, _, _ in aF.rows)
+
+
+def check_exo_step_paths(device, dtype, distill, random_pos=1):
+    """ExoTrainStep: the device-loss step (one read-back; captured into a CUDA graph on the GPU) against the eager step
+    through the drop-in get_loss (train/main_egoexo4d_distributed.py:105-222): same loss dictionary, same parameters."""
+    from exoground_b200.model import ExoGroundingTransformer
+    from exoground_b200.train.step_exo import ExoTrainStep
+    fp32 = dtype == torch.float32
+    Dv, Dt, Bx, Tx, Nx = 48, 64, 3, 16, 8
+    args = synth.exo_args(use_distill_nce_loss=distill, same_view_negative=distill)
+    batches = [synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=s) for s in (1, 2, 3)]
+
+    def run(mode):
+        m = ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt, use_distill_nce_loss=distill,
+                                    random_pos_start=random_pos, use_text_pos_enc=1, compute_dtype=dtype)
+        m.load_state_dict(synth.fill_state_dict({k: v.shape for k, v in m.state_dict().items()}, seed=3))
+        st = ExoTrainStep(m, args, lr=1e-3, wd=1e-2, eps=1e-4, clip_grad=0.5, device=device,
+                          use_graph=(mode == "graph"))
+        if mode == "legacy":
+            st.device_loss = False
+            st.use_graph = False
+        np.random.seed(17)
+        out = [st.step(b) for b in batches]
+        if mode == "graph":
+            assert st.graph is not None
+        return m, out
+    modes = ["legacy", "device"] + (["graph"] if torch.device(device).type == "cuda" else [])
+    res = {md: run(md) for md in modes}
+    m0, L0 = res["legacy"]
+    for md in modes[1:]:
+        m1, L1 = res[md]
+        for a, b in zip(L0, L1):
+            assert set(a) == set(b), (md, set(a) ^ set(b))
+            for k in a:
+                va = a[k]["mean"] if isinstance(a[k], dict) else float(a[k])
+                vb = b[k]["mean"] if isinstance(b[k], dict) else float(b[k])
+                assert abs(va - vb) <= (1e-5 if fp32 else 2e-3) * max(1.0, abs(va)), (md, k, va, vb)
+        _assert_params_close(m1, m0, 1e-3, 3, f"exo step {md}", mult=1.0 if fp32 else 30.0)
