@@ -62,7 +62,13 @@ def _manual_step(model, opt, b, args, device, clip=0.0, target=None):
 def _assert_params_close(a, b, lr, steps, what, mult=1.0):
     pb = dict(b.named_parameters())
     for n, p in a.named_parameters():
-        d = (p.detach() - pb[n].detach()).abs().max().item()
+        x, y = p.detach(), pb[n].detach()
+        if n.endswith("in_proj_bias"):
+            # the key bias has an identically-zero gradient (softmax is shift-invariant per query): what AdamW normalises
+            # there is rounding noise, different in any two correct runs -> compare the q and v thirds
+            keep = torch.cat((torch.arange(0, 512), torch.arange(1024, 1536))).to(x.device)
+            x, y = x[keep], y[keep]
+        d = (x - y).abs().max().item()
         assert d <= mult * (2e-5 + 1e-3 * pb[n].detach().abs().max().item() * lr * steps), (what, n, d)
 
 
