@@ -229,7 +229,7 @@ def _exo_worker(rank, world, port, q):
         batches = [synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=500 + r) for r in range(world)]
         st = ExoTrainStep(make(), args, lr=1e-3, wd=1e-2, clip_grad=3.0, device="cpu", process_group=dist.group.WORLD)
         L = st.step(batches[rank])
-        g_dist = st.opt.flat_grad().clone()            # all-reduced (sum) and clipped
+        g_dist = st.opt.flat_grad().clone()            # all-reduced (sum); the clip is folded into the AdamW read
 
         # single-process restatement: mean of the two ranks' gradients, the reference's per-parameter clip, AdamW
         grads, models = [], []
@@ -246,14 +246,17 @@ def _exo_worker(rank, world, port, q):
         assert (grads[0] - grads[1]).abs().max() > 1e-7
         ref = models[0]
         ref.opt.flat_grad().copy_((grads[0] + grads[1]) / world)
+        want = ref.opt.flat_grad().clone()
+        assert torch.allclose(g_dist / world, want, rtol=1e-5, atol=1e-7), (g_dist / world - want).abs().max()
+        clipped = 0
         for _, p in ref.model.named_parameters():      # utils/train_utils.py:3-13
             if p.grad is not None:
                 n = p.grad.norm(2)
                 c = 3.0 / (n + 1e-6)
                 if c < 1:
                     p.grad.mul_(c)
-        want = ref.opt.flat_grad().clone()
-        assert torch.allclose(g_dist / world, want, rtol=1e-5, atol=1e-7), (g_dist / world - want).abs().max()
+                    clipped += 1
+        assert clipped > 0, "case does not exercise the clip"
         ref.opt.step()
         mine, theirs = st.model.flat_params().flat, ref.model.flat_params().flat
         assert ((mine - theirs).abs() > 2e-4).float().mean() < 1e-3, (mine - theirs).abs().max()

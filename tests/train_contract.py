@@ -299,10 +299,14 @@ def check_exo_step_paths(device, dtype, distill, random_pos=1):
     m0, L0 = res["legacy"]
     for md in modes[1:]:
         m1, L1 = res[md]
-        for a, b in zip(L0, L1):
+        for i, (a, b) in enumerate(zip(L0, L1)):
             assert set(a) == set(b), (md, set(a) ^ set(b))
+            # bf16: the first step runs on identical parameters (2e-3); after an AdamW step at lr 1e-3 the two runs'
+            # parameters differ by the split-K reduction order of the weight gradients, and the per-rank monitors are
+            # means over a handful of seconds (1e-2)
+            tol = 1e-5 if fp32 else (2e-3 if i == 0 else 1e-2)
             for k in a:
                 va = a[k]["mean"] if isinstance(a[k], dict) else float(a[k])
                 vb = b[k]["mean"] if isinstance(b[k], dict) else float(b[k])
-                assert abs(va - vb) <= (1e-5 if fp32 else 2e-3) * max(1.0, abs(va)), (md, k, va, vb)
+                assert abs(va - vb) <= tol * max(1.0, abs(va)), (md, i, k, va, vb)
         _assert_params_close(m1, m0, 1e-3, 3, f"exo step {md}", mult=1.0 if fp32 else 30.0)
