@@ -13,6 +13,8 @@
 //                      sums, three quantiles by 8-bit radix selection (shared-memory histograms), BCE value +
 //                      gradient, and the row / column weights exg_nce_bwd needs.
 // Latency-bound: (2R + 2Cc) * S * 8 B read by the first, ~(2 R W + 8 Cc + 4 R) * 4 B by the second.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -364,5 +366,74 @@ extern "C" int exg_tan_loss_tail(const uint32_t* tgt_bits, const uint8_t* valid,
   ExgProfScope prof(EXG_PC_ROWWISE, (double)B * T * W * 8.0 + (double)(B * T + Cc) * 8.0 * 4.0, stream);
   tan_loss_tail_kernel<<<1, NT, smem, (cudaStream_t)stream>>>(a);
   EXG_LAUNCH_CHECK("tan_loss_tail");
+  return 0;
+}
+
+// ---------------------------------------------------------------- allocation-free variant
+// exg_tan_loss_tail_static: the same kernel with its scratch (`ws`: three [B*N] fp32 columns + the row / column /
+// kept flags) in a file-scope device array instead of a caller-allocated buffer, for callers that cannot allocate
+// (code under CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the
+// library holds kTailStaticBytes until exit.  The kernel writes every scratch element before reading it, so nothing
+// has to be cleared between calls; all calls on one device share the array, so two calls that overlap on the GPU
+// (different streams, no ordering between them) race.
+namespace {
+constexpr size_t kTailStaticBytes = 1u << 20;             // 1 MiB: e.g. B*T = 128 Ki rows with B*N = 64 Ki sentences
+static __device__ __align__(256) unsigned char g_tail_scratch[kTailStaticBytes];
+constexpr int kMaxDevices = 64;
+void* g_tail_scratch_addr[kMaxDevices] = {};              // per device: the DEVICE address of g_tail_scratch
+std::mutex g_tail_scratch_mu;
+
+// In host code `g_tail_scratch` is only a handle for the symbol, not a device address: resolve it once per device,
+// with that device current.
+int tail_scratch_ptr(void** out) {
+  int dev = -1;
+  EXG_CUDA(cudaGetDevice(&dev));
+  EXG_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "tan_loss_tail_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_tail_scratch_mu);
+  if (g_tail_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    EXG_CUDA(cudaGetSymbolAddress(&p, g_tail_scratch));
+    EXG_CHECK_ARG(p != nullptr, "tan_loss_tail_static: cudaGetSymbolAddress returned null");
+    g_tail_scratch_addr[dev] = p;
+  }
+  *out = g_tail_scratch_addr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" size_t exg_tan_loss_tail_static_max_bytes(void) { return kTailStaticBytes; }
+
+extern "C" int exg_tan_loss_tail_static(const uint32_t* tgt_bits, const uint8_t* valid, const float* vr_d,
+                                        const float* tc_d, const float* vr_j, const float* tc_j,
+                                        const float* own_max_d, const float* own_max_j, const float* la,
+                                        const float* abs_c, int B, int T, int N, int E, int D, float inv_temp,
+                                        float loss_threshold, int use_head, float nce_weight, float* wr_d,
+                                        float* wc_d, float* wr_j, float* wc_j, float* dla, float* out, void* stream) {
+  EXG_CHECK_ARG(tgt_bits && valid && vr_d && tc_d && vr_j && tc_j && own_max_d && own_max_j && wr_d && wc_d && wr_j &&
+                wc_j && out, "tan_loss_tail_static: null pointer");
+  EXG_CHECK_ARG(B > 0 && T > 0 && N > 0 && E > 0 && D > 0, "tan_loss_tail_static: bad sizes");
+  EXG_CHECK_ARG(!use_head || (la && dla), "tan_loss_tail_static: the alignability head needs la and dla");
+  const size_t need = exg_tan_loss_tail_workspace(B, T, N);
+  EXG_CHECK_ARG(need <= kTailStaticBytes,
+                "tan_loss_tail_static: B=%d T=%d N=%d needs %zu scratch bytes, the built-in scratch holds %zu "
+                "(use exg_tan_loss_tail with a caller-allocated workspace)", B, T, N, need, kTailStaticBytes);
+  const long Cc = (long)B * N;
+  const int W = (N + 31) / 32;
+  const size_t smem = (size_t)2 * B * W * sizeof(uint32_t);
+  EXG_CHECK_ARG(smem <= 160 * 1024, "tan_loss_tail_static: B*ceil(N/32) = %d too large for the per-clip bit rows",
+                B * W);
+  void* ws = nullptr;
+  if (int rc = tail_scratch_ptr(&ws)) return rc;
+  TailArgs a = {};
+  a.bits = tgt_bits; a.valid = valid; a.vr_d = vr_d; a.tc_d = tc_d; a.vr_j = vr_j; a.tc_j = tc_j;
+  a.md = own_max_d; a.mj = own_max_j; a.la = la; a.abs_c = abs_c;
+  a.ws = (float*)ws; a.flags = (uint8_t*)ws + 3 * Cc * sizeof(float);
+  a.wr_d = wr_d; a.wc_d = wc_d; a.wr_j = wr_j; a.wc_j = wc_j; a.dla = dla; a.out = out;
+  a.B = B; a.T = T; a.N = N; a.E = E; a.D = D; a.W = W;
+  a.inv_temp = inv_temp; a.q = loss_threshold; a.use_head = use_head; a.nce_weight = nce_weight;
+  if (smem > 40 * 1024)
+    EXG_CUDA(cudaFuncSetAttribute(tan_loss_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tan_loss_tail_kernel<<<1, NT, smem, (cudaStream_t)stream>>>(a);     // no profiling scope: its events allocate
+  EXG_LAUNCH_CHECK("tan_loss_tail_static");
   return 0;
 }

@@ -87,6 +87,9 @@ _SIGS = {
     "exg_tan_loss_tail_workspace": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "exg_tan_loss_tail": (C.c_int, [vp] * 10 + [C.c_int] * 5 + [C.c_float, C.c_float, C.c_int, C.c_float] +
                           [vp] * 7 + [C.c_size_t, vp]),
+    "exg_tan_loss_tail_static_max_bytes": (C.c_size_t, []),
+    "exg_tan_loss_tail_static": (C.c_int, [vp] * 10 + [C.c_int] * 5 + [C.c_float, C.c_float, C.c_int, C.c_float] +
+                                 [vp] * 7),
     "exg_adamw": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, C.c_float, C.c_float, C.c_float, C.c_float,
                             C.c_float, C.c_int, C.c_float, vp]),
     "exg_adamw_dev": (C.c_int, [vp, vp, vp, vp, vp, C.c_long, vp, C.c_float, C.c_float, C.c_float, C.c_float,

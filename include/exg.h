@@ -229,6 +229,20 @@ int exg_tan_loss_tail(const uint32_t* tgt_bits, const uint8_t* valid, const floa
                       const float* la, const float* abs_c, int B, int T, int N, int E, int D, float inv_temp,
                       float loss_threshold, int use_head, float nce_weight, float* wr_d, float* wc_d, float* wr_j,
                       float* wc_j, float* dla, float* out, void* ws, size_t ws_bytes, void* stream);
+/* Allocation-free variant of exg_tan_loss_tail.  No counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same arguments and results as exg_tan_loss_tail minus (ws, ws_bytes): the scratch lives in a
+ * file-scope device array of exg_tan_loss_tail_static_max_bytes() = 1 MiB that every GPU loading the library holds
+ * until exit; the call performs no cudaMalloc / cudaFree / allocating library call.  Sizes whose
+ * exg_tan_loss_tail_workspace(B,T,N) exceeds that maximum return EXG_EINVAL with a message naming both numbers.  All
+ * calls on one device share the array (the kernel writes every element before reading it, so no clearing is needed
+ * between calls): calls that overlap on the GPU - different streams without ordering - race. */
+size_t exg_tan_loss_tail_static_max_bytes(void);
+int exg_tan_loss_tail_static(const uint32_t* tgt_bits, const uint8_t* valid, const float* vr_d, const float* tc_d,
+                             const float* vr_j, const float* tc_j, const float* own_max_d, const float* own_max_j,
+                             const float* la, const float* abs_c, int B, int T, int N, int E, int D, float inv_temp,
+                             float loss_threshold, int use_head, float nce_weight, float* wr_d, float* wc_d,
+                             float* wr_j, float* wc_j, float* dla, float* out, void* stream);
 
 /* ---------------------------------------------------------------- ExoGround losses ------------
  * Row-wise softmax cross-entropy with the target on the diagonal: the per-clip T x T InfoNCE of
