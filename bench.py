@@ -235,14 +235,17 @@ def time_cpu(B, steps, warmup, kind_pref="auto"):
             "ms_per_step": sec * 1e3}
 
 
-def workload_config(n_gpus, xneg=False, batch=0, overlap=False):
+def workload_config(n_gpus, xneg=False, batch=0, overlap=False, chunks=4, wire="fp32", host_dtype="fp32"):
     global PER_GPU_BATCH
     if batch:
         PER_GPU_BATCH = batch
     cfg = _workload_config(n_gpus)
+    cfg["host_features"] = f"{host_dtype}, pinned, copied every step on a copy stream while the previous step computes"
     if n_gpus > 1:
         cfg["grad_allreduce"] = ("NCCL, per-block buckets (~25 MB) issued asynchronously during backward, inside the "
-                                 "step's CUDA graph" if overlap else "NCCL, one call after backward")
+                                 "step's CUDA graph" if overlap else
+                                 f"NCCL, {wire} gradients in {chunks} parameter-aligned chunks after backward, "
+                                 f"overlapped with the optimizer (AdamW of chunk i runs under the all-reduce of chunk i+1)")
     if xneg and n_gpus > 1:
         cfg["parallelism"] = f"dp{n_gpus} + cross-GPU negatives (text features all-gathered; NCE over the global batch)"
     return cfg
@@ -303,6 +306,9 @@ def run_ours(a):
         raise SystemExit("bench.py: no CUDA device (exoground_b200 has no CPU fallback; use --impl reference)")
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
+    # the rank's thread (and the first touch of its pinned staging pool) on the GPU's own NUMA node
+    from exoground_b200.utils import affinity
+    a.placement = "unchanged: EXG_NO_BIND" if os.environ.get("EXG_NO_BIND") else affinity.bind_to_gpu(local)
     pg = None
     if world > 1:
         # NCCL writes its version / debug lines to stdout by default; stdout carries the ONE JSON line
@@ -320,10 +326,14 @@ def run_ours(a):
     tr = TanTrainStep(model, args, B, T, N, D_IN, D_IN, device=dev, use_graph=not a.no_graph, process_group=pg,
                       cross_gpu_negatives=a.xneg, overlap_allreduce=a.overlap,
                       comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")), branch_streams=not a.single_stream,
-                      early_adamw=a.early_adamw)
+                      early_adamw=a.early_adamw, comm_chunks=a.comm_chunks,
+                      comm_dtype=torch.bfloat16 if a.grad_comm == "bf16" else None,
+                      host_dtype=torch.bfloat16 if a.host_dtype == "bf16" else torch.float32)
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
+    if a.host_dtype == "bf16":                     # a feature store kept in half precision (converted offline)
+        batch["video"], batch["text"] = batch["video"].bfloat16(), batch["text"].bfloat16()
     for k in ("video", "text", "video_padding_mask", "text_padding_mask"):
         batch[k] = batch[k].pin_memory()
     h2d = tr.load_batch(batch)
@@ -448,7 +458,8 @@ def run_ours(a):
         gf = train_gflop_per_clip(B)
         line = {"metric": METRIC, "value": round(value, 1), "unit": "clips/s", "n_gpus": world, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(world, a.xneg, a.batch, a.overlap),
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": dict(workload_config(world, a.xneg, a.batch, a.overlap, a.comm_chunks, a.grad_comm, a.host_dtype),
+                               host_placement=a.placement),
                 "e2e": {"value": round(gb / (ms_e2e * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_e2e, 4),
                         "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last},
                 "gpu_launches": int(launches_per_step * a.steps),
@@ -521,6 +532,13 @@ def main():
     ap.add_argument("--overlap", action="store_true",
                     help="N>1: per-block gradient buckets all-reduced asynchronously during backward instead of one "
                          "all-reduce after it (measured: no gain, see DESIGN.md §6)")
+    ap.add_argument("--comm-chunks", type=int, default=4,
+                    help="N>1: chunks of the gradient all-reduce (AdamW of chunk i under the all-reduce of chunk i+1)")
+    ap.add_argument("--grad-comm", default="fp32", choices=["fp32", "bf16"],
+                    help="N>1: dtype of the gradients on the wire (fp32 = DistributedDataParallel's; bf16 = its "
+                         "bf16_compress_hook)")
+    ap.add_argument("--host-dtype", default="fp32", choices=["fp32", "bf16"],
+                    help="dtype of the pinned host features (fp32 = what the reference's loaders hand over)")
     ap.add_argument("--xneg", action="store_true",
                     help="N > 1: cross-GPU negatives (text features all-gathered, NCE over the global batch; "
                          "train/xneg.py) instead of the DDP-equivalent local negatives")

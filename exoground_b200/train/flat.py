@@ -88,6 +88,51 @@ def load_optim_state_dict(model, m1, m2, sd):
     return (steps.pop() if steps else 0), float(groups[-1]["lr"]), float(groups[-1]["weight_decay"])
 
 
+def plan_chunks(fp, n_chunks, wd):
+    """[(lo, hi, weight decay)]: the used part of the flat buffer cut at parameter boundaries into about `n_chunks`
+    equal pieces (a parameter never straddles two chunks, so its clipping norm is complete when its chunk is updated);
+    the no-decay / decay boundary is always a cut."""
+    starts = sorted(off for n, (off, numel, _) in fp.index.items() if n not in fp.unused and off < fp.n_used)
+    want = max(1, (fp.n_used + n_chunks - 1) // max(1, n_chunks))
+    cuts, last = [0], 0
+    for off in starts[1:] + [fp.n_used]:
+        if (off == fp.n_no_decay or off - last >= want or off == fp.n_used) and off > last:
+            cuts.append(off)
+            last = off
+    plan = [(lo, hi, 0.0 if hi <= fp.n_no_decay else wd) for lo, hi in zip(cuts[:-1], cuts[1:])]
+    assert plan and plan[0][0] == 0 and plan[-1][1] == fp.n_used
+    return plan
+
+
+def reduce_and_update(fp, plan, pg, m1, m2, lr, betas, eps, step, gscale, clip, blk2seg, n_seg, seg_sumsq, gcomm=None,
+                      shadow=False):
+    """The data-parallel replacement of DDP's bucketed all-reduce + optimizer.step() (train/main.py:413,111;
+    main_egoexo4d_distributed.py:611-614,181): every chunk of `plan` is all-reduced asynchronously on NCCL's stream and
+    the (clip +) AdamW launch of chunk i is issued on the current stream as soon as chunk i has arrived, i.e. it runs
+    under the all-reduce of chunk i+1; only the last chunk's update is exposed.  `gcomm` (bf16 buffer, optional): the
+    gradients travel in bf16 - cast, summed on the wire, cast back (DDP's bf16_compress_hook semantics)."""
+    K = ops.get()
+    g = fp.grad
+    wire = g
+    if gcomm is not None:
+        K.cast(g[:fp.n_used], gcomm.dtype, out=gcomm)
+        wire = gcomm
+    works = [torch.distributed.all_reduce(wire[lo:hi], group=pg, async_op=True) for lo, hi, _ in plan]
+    b1, b2 = betas
+    sh_all = fp.shadow if shadow else None
+    for w, (lo, hi, wd) in zip(works, plan):
+        w.wait()                                        # the current stream waits for this chunk only
+        if gcomm is not None:
+            K.cast(gcomm[lo:hi], torch.float32, out=g[lo:hi])
+        sh = sh_all[lo:hi] if sh_all is not None else None
+        if clip > 0:
+            K.grad_sumsq(g[lo:hi], blk2seg[lo // ALIGN:hi // ALIGN], n_seg, out=seg_sumsq)
+            K.adamw_clip(fp.flat[lo:hi], g[lo:hi], m1[lo:hi], m2[lo:hi], sh, lr, b1, b2, eps, wd, step,
+                         blk2seg[lo // ALIGN:], seg_sumsq, clip, grad_scale=gscale)
+        else:
+            K.adamw(fp.flat[lo:hi], g[lo:hi], m1[lo:hi], m2[lo:hi], sh, lr, b1, b2, eps, wd, step, grad_scale=gscale)
+
+
 class FlatAdamW:
     def __init__(self, model, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8, process_group=None, sum_grads=False):
         self.model, self.lr, self.wd, self.betas, self.eps = model, lr, wd, betas, eps
@@ -133,6 +178,19 @@ class FlatAdamW:
     def allreduce(self):
         if self.world > 1:
             torch.distributed.all_reduce(self.flat_grad(), group=self.pg)
+
+    def reduce_and_step(self, clip_grad=0.0, chunks=4):
+        """allreduce() + step() as one pipelined pass (world > 1): chunked all-reduce, AdamW of chunk i under the
+        all-reduce of chunk i+1.  Single process: step()."""
+        if self.world == 1:
+            return self.step(clip_grad=clip_grad)
+        fp = self.model.flat_params()
+        if getattr(self, "_plan", None) is None:
+            self._plan = plan_chunks(fp, chunks, self.wd)
+        self.step_count += 1
+        reduce_and_update(fp, self._plan, self.pg, self.m1, self.m2, self.lr, self.betas, self.eps, self.step_count,
+                          self.grad_scale, clip_grad, self.blk2seg, len(self.seg_names), self.seg_sumsq,
+                          shadow=self.model.compute_dtype == torch.bfloat16)
 
     def grad_norms(self):
         """Per-parameter norms of the (mean) gradient in `seg_names` order: one launch (exg_grad_sumsq), no host

@@ -6,11 +6,13 @@ the reference's optimiser policy (train/main.py:350-376,418: AdamW, no weight de
 B200 design:
   * parameters, gradients and AdamW moments live in flat fp32 buffers (model/params.py); the optimizer is two
     launches of exg_adamw (no-decay segment, decay segment) which also refresh the bf16 shadow weights;
-  * the data-parallel replacement of DistributedDataParallel (train/main.py:413) is ONE NCCL all-reduce of the
-    flat gradient buffer per step (sum; the 1/world_size of DDP's mean is folded into the AdamW kernel);
+  * the data-parallel replacement of DistributedDataParallel (train/main.py:413) is an NCCL all-reduce of the flat
+    gradient buffer (sum; the 1/world_size of DDP's mean is folded into the AdamW kernel), issued in a few
+    parameter-aligned chunks with the AdamW launch of each chunk pipelined behind its arrival, so the optimizer runs
+    under the wire time of the following chunk (`comm_chunks`, `comm_dtype`);
     `cross_gpu_negatives=True` additionally all-gathers the text features so the NCE runs over the global batch
     (train/xneg.py) -- the step is then numerically the single-process step on the concatenated batch;
-  * host batches land in fp32 staging buffers (optionally on a copy stream while the previous step computes:
+  * host batches land in staging buffers of the host's dtype (optionally on a copy stream while the previous step computes:
     `step(batch, next_batch=...)` / `prefetch()`), and one cast kernel per feature tensor moves them into the
     compute-dtype buffers the step reads, so the forward has no input cast and the PCIe copy overlaps compute;
   * the video-encoder and joint-encoder branches are independent given the shared input projections
@@ -33,7 +35,7 @@ class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
                  device="cuda", use_graph=True, process_group=None, cross_gpu_negatives=False,
                  overlap_allreduce=False, bucket_mb=25.0, comm_sms=0, branch_streams=True, early_adamw=False,
-                 clip_grad=0.0):
+                 clip_grad=0.0, comm_chunks=4, comm_dtype=None, host_dtype=torch.float32):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
@@ -72,6 +74,15 @@ class TanTrainStep:
         # (SM count - comm_sms) CTAs instead of queueing a second wave behind the SMs NCCL holds
         self.comm_sms = int(comm_sms)
         self._pending, self._works = [], []
+        # default multi-GPU path: after backward the flat gradient buffer is all-reduced in `comm_chunks`
+        # parameter-aligned chunks on NCCL's stream, and the AdamW launch of chunk i runs on the main stream as soon as
+        # chunk i has arrived - i.e. under the all-reduce of chunk i+1 - so only the last chunk's update is exposed.
+        # comm_dtype=torch.bfloat16 sends bf16 gradients (half the wire bytes; DDP's bf16_compress_hook semantics:
+        # cast, sum in bf16 on the wire, cast back), the default sends the fp32 buffer like DDP does.
+        self.comm_chunks = max(1, int(comm_chunks))
+        self.comm_dtype = comm_dtype if comm_dtype in (torch.bfloat16,) else None
+        self._gcomm = None
+        self._chunk_plan = None
         # the joint encoder branch on a stream of its own (model/tan_model.py::forward), forward and backward
         self.branch_stream = None
         if branch_streams and self._on_cuda and self.xneg is None:
@@ -101,8 +112,11 @@ class TanTrainStep:
         self.graph = None
         dev = self.device
         # staging buffers (targets of the per-step H2D copies, possibly written by the copy stream while a step runs)
-        self.video_s = torch.zeros(B, T, d_video, device=dev)
-        self.text_s = torch.zeros(B, N, d_text, device=dev)
+        # host_dtype: dtype of the feature tensors the host hands over (fp32 = what the reference's loaders produce;
+        # torch.bfloat16 for feature stores kept in half precision: half the pinned pool and half the PCIe bytes)
+        self.host_dtype = host_dtype
+        self.video_s = torch.zeros(B, T, d_video, device=dev, dtype=host_dtype)
+        self.text_s = torch.zeros(B, N, d_text, device=dev, dtype=host_dtype)
         self.vmask_s = torch.zeros(B, T, dtype=torch.bool, device=dev)
         self.tmask_s = torch.zeros(B, N, dtype=torch.bool, device=dev)
         self.tgt_s = torch.zeros(B, N, T, dtype=torch.bool, device=dev)
@@ -141,6 +155,9 @@ class TanTrainStep:
                 raise ValueError(f"TanTrainStep: batch[{key!r}] has shape {tuple(src.shape)}, the step was built for "
                                  f"{tuple(dst.shape)} (B={self.B}, T={self.T}, N={self.N}); pad the batch or build "
                                  f"another step")
+            if src.dtype != dst.dtype:
+                raise ValueError(f"TanTrainStep: batch[{key!r}] is {src.dtype}, the step was built with "
+                                 f"host_dtype={dst.dtype} (a converting copy would run on the host, inside the step)")
             dst.copy_(src, non_blocking=non_blocking)
             n += src.numel() * src.element_size()
         if "tgt" in batch:
@@ -355,10 +372,21 @@ class TanTrainStep:
         if self.model.compute_dtype == torch.bfloat16:
             self.model.flat_params().refresh_shadow()      # the graph replays read the shadow, not the fp32 weights
 
-    def _allreduce(self):
-        if self.world > 1 and not self._hooked:
-            fp = self.model.flat_params()
-            torch.distributed.all_reduce(fp.grad[:fp.n_used], group=self.pg)
+    def _reduce_and_update(self):
+        """Chunked gradient all-reduce with the optimizer pipelined behind it (see __init__; train/flat.py)."""
+        from .flat import plan_chunks, reduce_and_update
+        fp = self.model.flat_params()
+        if self._chunk_plan is None:
+            self._chunk_plan = plan_chunks(fp, self.comm_chunks, self.wd)
+            if self.comm_dtype is not None:
+                self._gcomm = torch.empty(fp.n_used, dtype=self.comm_dtype, device=fp.flat.device)
+        self.step_count += 1
+        reduce_and_update(fp, self._chunk_plan, self.pg, self.m1, self.m2, self.lr, self.betas, self.eps,
+                          self.step_count, 1.0 if self.xneg is not None else 1.0 / self.world, self.clip_grad,
+                          self.blk2seg, len(self.seg_names), self.seg_sumsq, self._gcomm,
+                          shadow=self.model.compute_dtype == torch.bfloat16)
+        if self.twin is not None:                      # train/main.py:116-117
+            self.twin._momentum_update()
 
     def prepare(self):
         """Discovery pass (which parameters get gradients), flat gradient / moment buffers, kernel warm-up and,
@@ -473,8 +501,10 @@ class TanTrainStep:
             self._fwd_bwd()
             self._early_on = False
             self._skip = list(self._early_done)
-        self._allreduce()
-        self._optimizer()
+        if self.world > 1 and not self._hooked:
+            self._reduce_and_update()
+        else:
+            self._optimizer()
         return self.loss_out
 
     def step(self, batch, next_batch=None):

@@ -1,7 +1,8 @@
 """One ExoGround / keystep-grounding training step on one GPU (one process per GPU): the body of the reference's
 train() loop (train/main_egoexo4d_distributed.py:105-222: forward :145-153, get_loss :165-168, backward :175,
-clip + optimizer step :176-181) with DistributedDataParallel (:611-614) replaced by ONE NCCL all-reduce of the flat
-gradient buffer and torch.optim.AdamW by the fused kernel (train/flat.py).  The grounding / view-invariant losses
+clip + optimizer step :176-181) with DistributedDataParallel (:611-614) replaced by a chunked NCCL all-reduce of the
+flat gradient buffer with the fused clip + AdamW of each chunk pipelined behind its arrival (train/flat.py::
+reduce_and_update) instead of torch.optim.AdamW.  The grounding / view-invariant losses
 have no cross-sample terms, so the data-parallel mode is DDP-equivalent: local loss, mean gradient.
 
 Device step.  For the `grounding` / `joint` models the whole device part - forward, the interval-regression + IoU loss
@@ -247,17 +248,14 @@ class ExoTrainStep:
             if next_batch is not None:
                 self.prefetch(next_batch)
             self.graph.replay()
-            self.opt.allreduce()
-            self.opt.step(clip_grad=self.clip_grad)
+            self.opt.reduce_and_step(clip_grad=self.clip_grad)
             return self._loss_dict(self._out[0], self._out[1], self._out[2], batch)
         else:
             self.opt.zero_grad()
             if next_batch is not None:
                 self.prefetch(next_batch)
             loss, stats, per_sec = self._device_fwd_bwd(b)
-            self.opt.allreduce()
-            self.opt.step(clip_grad=self.clip_grad)
+            self.opt.reduce_and_step(clip_grad=self.clip_grad)
             return self._loss_dict(loss, stats, per_sec, batch)
-        self.opt.allreduce()
-        self.opt.step(clip_grad=self.clip_grad)       # per-parameter clip folded into the AdamW kernel's gradient read
+        self.opt.reduce_and_step(clip_grad=self.clip_grad)   # per-parameter clip folded into AdamW's gradient read
         return L

@@ -117,6 +117,96 @@ def test_two_rank_gradient_allreduce_gloo():
     assert abs(res[0][2] - res[1][2]) > 0        # different batches -> different local losses
 
 
+def _chunked_worker(rank, world, port, q, clip, bf16_wire):
+    """The default multi-GPU path: chunked all-reduce with the AdamW of chunk i issued as soon as chunk i has arrived."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from exoground_b200 import ops
+        from exoground_b200.train.step import TanTrainStep
+        from exoground_b200.utils import synth
+        from tests.fake_backend import TorchBackend
+        ops.set_backend(TorchBackend())
+        args = synth.tan_args(loss_threshold=0.0, use_alignability_head=0)
+        kw = dict(lr=1e-3, wd=1e-2, device="cpu", use_graph=False, clip_grad=clip)
+        m, b = _make(rank)
+        st = TanTrainStep(m, args, B, T, N, DIN, DIN, process_group=dist.group.WORLD, comm_chunks=3,
+                          comm_dtype=torch.bfloat16 if bf16_wire else None, **kw)
+        st.load_batch(b, non_blocking=False)
+        st.prepare()
+        calls = []
+        orig_ar = dist.all_reduce
+        dist.all_reduce = lambda t, **k: (calls.append((t.numel(), t.dtype)), orig_ar(t, **k))[1]
+        loss0 = float(st.run())
+        dist.all_reduce = orig_ar
+        fp = m.flat_params()
+        plan = st._chunk_plan
+        assert not st._hooked and len(plan) >= 3 and len(calls) == len(plan), (plan, calls)
+        assert sum(n for n, _ in calls) == fp.n_used and plan[0][0] == 0 and plan[-1][1] == fp.n_used
+        assert all(dt == (torch.bfloat16 if bf16_wire else torch.float32) for _, dt in calls)
+        assert any(hi == fp.n_no_decay for _, hi, _ in plan) and all(lo % 64 == 0 for lo, _, _ in plan)
+        starts = {off for n, (off, numel, _) in fp.index.items()}
+        assert all(lo in starts for lo, _, _ in plan)                 # cuts at parameter boundaries only
+
+        grads = []
+        for r in range(world):
+            mr, br = _make(r)
+            sr = TanTrainStep(mr, args, B, T, N, DIN, DIN, **kw)
+            sr.load_batch(br, non_blocking=False)
+            sr.prepare()
+            fr = mr.flat_params()
+            fr.grad.zero_()
+            sr._draw_offsets()
+            sr._fwd_bwd()
+            grads.append(fr.grad[:fr.n_used].clone())
+        want_sum = sum(grads)
+        mref, _ = _make(0)
+        sref = TanTrainStep(mref, args, B, T, N, DIN, DIN, **kw)
+        sref.load_batch(_make(0)[1], non_blocking=False)
+        sref.prepare()
+        fref = mref.flat_params()
+        fref.grad.zero_()
+        fref.grad[:fref.n_used] = want_sum / world
+        sref._optimizer()                                              # per-parameter clip + AdamW on the mean gradient
+        if clip > 0:
+            assert bool((sref.seg_sumsq.sqrt() > clip).any()) and bool((sref.seg_sumsq.sqrt() < clip).any())
+        diff = (fp.flat - fref.flat).abs()
+        if bf16_wire:
+            # the first AdamW step moves every weight by ~lr * sign(g): bf16 rounding on the wire matters only where
+            # g is ~0 (and through the clip factor's 3-digit norm)
+            assert float(diff.max()) <= 2.1e-3 and float((diff > 2e-5).float().mean()) < 2e-2, (diff.max(),)
+        else:
+            assert torch.allclose(fp.flat, fref.flat, rtol=1e-5, atol=1e-7), diff.max()
+        st.run()
+        mine = fp.flat.clone()
+        both = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(both, mine)
+        assert torch.equal(both[0], both[1])
+        q.put((rank, "ok", loss0))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, "fail", traceback.format_exc() + repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("clip,bf16_wire", [(0.0, False), (0.05, False), (0.05, True)])
+def test_two_rank_chunked_allreduce_pipelined_adamw_gloo(clip, bf16_wire):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_chunked_worker, args=(r, 2, port, q, clip, bf16_wire)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, status, info in res:
+        assert status == "ok", f"rank {rank}: {info}"
+
+
 # ----------------------------------------------------------------------------------------------- cross-GPU negatives
 def _cat_batches(bs):
     out = {}
