@@ -20,6 +20,9 @@ struct AtcArgs {
   float scale;
   const uint8_t* key_pad;
   float* lse;
+  // attention_tc.cu only: rows of the smem query / key tiles (multiples of 16, <= 128) - short sequences get short
+  // tiles, which is what lets several CTAs share an SM
+  int tq_rows, tk_rows;
 };
 
 // ---- smem addressing of a 128B-swizzled [rows][64 bf16] tile: 16-byte unit u of row r
@@ -64,13 +67,13 @@ EncodeTiledFn enc_fn() {
   return fn;
 }
 
-// [B][S][ld] bf16 view of one of q / k / v / o (head h at column h*64): box = 64 columns x 128 rows x 1 clip
-int seq_map(CUtensorMap* out, const void* base, int B, int S, int cols, long ld) {
+// [B][S][ld] bf16 view of one of q / k / v / o (head h at column h*64): box = 64 columns x box_rows rows x 1 clip
+int seq_map(CUtensorMap* out, const void* base, int B, int S, int cols, long ld, int box_rows = 128) {
   EncodeTiledFn fn = enc_fn();
   if (!fn) { exg_set_error("attn_tc: cuTensorMapEncodeTiled unavailable"); return EXG_EUNSUPPORTED; }
   cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)S, (cuuint64_t)B};
   cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)S * ld * 2};
-  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,

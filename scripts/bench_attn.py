@@ -10,8 +10,11 @@ from exoground_b200 import ops  # noqa: E402
 K = ops.get()
 H, d = 8, 64
 print(f"{'B':>4} {'S':>6} {'fwd ms':>9} {'fwd TF/s':>9} {'bwd ms':>9} {'bwd TF/s':>9}")
-for S in (64, 128, 256, 512, 1024, 2048, 4096):
-    B = max(1, 16384 // S)
+only = [int(x) for x in sys.argv[1:]]
+# (S, B): the train step's own shapes first (video encoder T=64, joint encoder T+N=96, 128 clips), then the sweep
+for S, B in [(64, 128), (96, 128), (32, 128)] + [(S, max(1, 16384 // S)) for S in (64, 128, 256, 512, 1024, 2048, 4096)]:
+    if only and S not in only:
+        continue
     qkv = torch.randn(B * S, 3 * H * d, device="cuda").bfloat16()
     q, k, v = qkv[:, :512], qkv[:, 512:1024], qkv[:, 1024:]
     scale = d ** -0.5
