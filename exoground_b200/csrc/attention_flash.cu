@@ -27,6 +27,17 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 __device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+constexpr float kLazyLog2 = 20.f;             // forward: largest 2^x a score may exceed the stale running maximum by
+// CTA-wide OR over the 128 softmax threads (named barrier 2, so it cannot pair with a bar.sync 1 of another warp)
+__device__ __forceinline__ bool softmax_bar_or(bool v) {
+  uint32_t r;
+  asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %1, 0;\n\tbar.red.or.pred q, 2, 128, p;\n\tselp.u32 %0, 1, 0, q;\n\t}"
+               : "=r"(r) : "r"((uint32_t)v) : "memory");
+  return r != 0;
+}
+constexpr int kBwdSoftmaxWarps = 8;           // backward: two warps per TMEM lane quarter
+constexpr int FTB = 32 * (kBwdSoftmaxWarps + 1);
+__device__ __forceinline__ void bwd_softmax_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // key-validity bit words for ALL keys of clip b (bit k & 31 of word k >> 5), rounded up to whole 128-key tiles
 __device__ __forceinline__ void build_mask_all(uint32_t* maskw, const AtcArgs& p, int b, int nwords, int warp, int lane,
@@ -40,12 +51,12 @@ __device__ __forceinline__ void build_mask_all(uint32_t* maskw, const AtcArgs& p
 }
 
 // O[128 x 64] = P[128 x 128 keys] V[128 keys x 64]: A = P K-major (two 64-key blocks), B = V MN-major (keys x d)
-__device__ __forceinline__ void mma_pv(uint32_t tO, uint32_t sP, uint32_t sV) {
+__device__ __forceinline__ void mma_pv(uint32_t tO, uint32_t sP, uint32_t sV, uint32_t acc) {
   const uint32_t idesc = umma_idesc_bf16(128, HD, 0, 1);
 #pragma unroll
   for (int k = 0; k < 8; ++k)
     umma_bf16(tO, umma_smem_desc(sP + (k >> 2) * kTile + (k & 3) * 32, 16, 1024),
-              umma_smem_desc(sV + k * 2048, 8192, 1024), idesc, k > 0);
+              umma_smem_desc(sV + k * 2048, 8192, 1024), idesc, acc | (uint32_t)(k > 0));
 }
 
 // ------------------------------------------------------------------------------------------ forward
@@ -59,6 +70,7 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   uint64_t *bar_q = bars, *bar_k = bars + 1 /* [2] */, *bar_v = bars + 3, *bar_s = bars + 4, *bar_p = bars + 5,
            *bar_o = bars + 6;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint32_t* pv_acc = tmem_slot + 1;               // 1: this tile's P V accumulates onto O in TMEM, 0: it restarts O
   uint32_t* maskw = tmem_slot + 4;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -95,10 +107,11 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       mma_kmajor_k64(tS, smem_u32(Qs), smem_u32(Ks), TK);
       umma_commit(bar_s);
       for (int j = 0; j < nt; ++j) {
-        mbar_wait(bar_p, j & 1);                 // P_j in smem; S_j and O_{j-1} consumed
+        mbar_wait(bar_p, j & 1);                 // P_j in smem; S_j consumed
+        const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(pv_acc);     // 0: exact tile, O restarts
         mbar_wait(bar_v, j & 1);
         tc_fence_after();
-        mma_pv(tO, smem_u32(Ps), smem_u32(Vs));
+        mma_pv(tO, smem_u32(Ps), smem_u32(Vs), acc);
         umma_commit(bar_o);
         if (j + 1 < nt) {
           mbar_wait(&bar_k[(j + 1) & 1], ((j + 1) >> 1) & 1);
@@ -125,51 +138,23 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     float o[HD];
 #pragma unroll
     for (int i = 0; i < HD; ++i) o[i] = 0.f;
+    // TMEM -> register reads are what bounds this kernel (64 B / clk / SM: one 128 x 128 fp32 score tile = 1024
+    // cycles, twice the time of its two MMAs), so the common tile reads S exactly ONCE and never reads O:
+    //   * the exponentials are taken relative to the running maximum of the PREVIOUS tiles (m); the tile maximum is
+    //     tracked alongside.  Softmax is shift-invariant, so a stale reference only matters for range: as long as no
+    //     row's tile maximum exceeds m by more than 2^kLazyLog2 the tile is done - P V accumulates onto O in TMEM.
+    //   * otherwise (the first tile, and whenever some row's maximum jumps) the whole CTA takes the exact path for
+    //     this tile: new maximum, O so far folded into registers with the rescale factor, second read of S, and the
+    //     TMEM accumulation restarts (pv_acc = 0).  O = (registers + TMEM) / l at the end either way.
     for (int j = 0; j < nt; ++j) {
       mbar_wait(bar_s, j & 1);
       tc_fence_after();
       const uint32_t* mw = maskw + j * 4;
-      // pass 1: tile max.  TMEM loads double-buffered (the next chunk is in flight while this one is reduced);
-      // 4 independent running maxima instead of one 32-deep dependency chain; unmasked fast path
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-      {
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32(tS + lane_addr, ra);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t (&cur)[32] = (c & 1) ? rb : ra;
-          uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
-          tmem_ld_wait();
-          if (c + 1 < 4) tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, nxt);
-          const uint32_t w = mw[c];
-          if (w == 0xffffffffu) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if ((w >> i) & 1) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
-          }
-        }
-      }
-      const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      const float m_new = fmaxf(m, mt);
-      const float msafe = m_new == -INFINITY ? 0.f : m_new;
-      const float alpha = ex2_approx((m - msafe) * sl2);          // m = -inf -> 0 (o and l are 0 then anyway)
-      m = m_new;
-      if (j > 0) {                                                // fold O_{j-1} (relative to the old max)
-        mbar_wait(bar_o, (j - 1) & 1);
-        tc_fence_after();
-        uint32_t r[64];
-        tmem_ld_32x32(tO + lane_addr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-        tmem_ld_32x32(tO + lane_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < HD; ++i) o[i] = (o[i] + __uint_as_float(r[i])) * alpha;
-      }
-      const float nb = -msafe * sl2;
       float sm4[4] = {0.f, 0.f, 0.f, 0.f};
-      {
+      bool exact = j == 0;
+      if (!exact) {
+        const float nb = -(m == -INFINITY ? 0.f : m) * sl2;
         uint32_t ra[32], rb[32];
         tmem_ld_32x32(tS + lane_addr, ra);
 #pragma unroll
@@ -183,13 +168,18 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           if (w == 0xffffffffu) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-              pv[i] = ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb));
+              const float sv = __uint_as_float(cur[i]);
+              mx4[i & 3] = fmaxf(mx4[i & 3], sv);
+              pv[i] = ex2_approx(fmaf(sv, sl2, nb));
               sm4[i & 3] += pv[i];
             }
           } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i) {
-              pv[i] = ((w >> i) & 1) ? ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb)) : 0.f;
+              const float sv = __uint_as_float(cur[i]);
+              const bool on = (w >> i) & 1;
+              if (on) mx4[i & 3] = fmaxf(mx4[i & 3], sv);
+              pv[i] = on ? ex2_approx(fmaf(sv, sl2, nb)) : 0.f;
               sm4[i & 3] += pv[i];
             }
           }
@@ -198,13 +188,91 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           for (int u = 0; u < 4; ++u)
             *reinterpret_cast<uint4*>(blk + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
         }
+        const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        // (m = -inf with a finite tile maximum: the difference is +inf, i.e. exact path)
+        const bool jump = mt != -INFINITY && (mt - m) * sl2 > kLazyLog2;
+        exact = softmax_bar_or(jump);                // CTA-uniform
+        if (!exact) l += (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
       }
-      const float sum = (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
-      l = l * alpha + sum;
+      if (exact) {
+        if (j == 0) {
+          // tile maximum (later tiles know it from the single pass).  TMEM loads double-buffered; 4 independent
+          // running maxima instead of one 32-deep dependency chain; unmasked fast path
+          uint32_t ra[32], rb[32];
+          tmem_ld_32x32(tS + lane_addr, ra);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+            uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+            tmem_ld_wait();
+            if (c + 1 < 4) tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, nxt);
+            const uint32_t w = mw[c];
+            if (w == 0xffffffffu) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if ((w >> i) & 1) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
+            }
+          }
+        }
+        const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        const float m_new = fmaxf(m, mt);
+        const float msafe = m_new == -INFINITY ? 0.f : m_new;
+        const float alpha = ex2_approx((m - msafe) * sl2);        // m = -inf -> 0 (o and l are 0 then anyway)
+        m = m_new;
+        if (j > 0) {                                              // fold the O accumulated in TMEM since the last exact tile
+          mbar_wait(bar_o, (j - 1) & 1);
+          tc_fence_after();
+          uint32_t r[64];
+          tmem_ld_32x32(tO + lane_addr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+          tmem_ld_32x32(tO + lane_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < HD; ++i) o[i] = (o[i] + __uint_as_float(r[i])) * alpha;
+        }
+        const float nb = -msafe * sl2;
+        sm4[0] = sm4[1] = sm4[2] = sm4[3] = 0.f;
+        {
+          uint32_t ra[32], rb[32];
+          tmem_ld_32x32(tS + lane_addr, ra);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t (&cur)[32] = (c & 1) ? rb : ra;
+            uint32_t (&nxt)[32] = (c & 1) ? ra : rb;
+            tmem_ld_wait();
+            if (c + 1 < 4) tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, nxt);
+            const uint32_t w = mw[c];
+            float pv[32];
+            if (w == 0xffffffffu) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                pv[i] = ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb));
+                sm4[i & 3] += pv[i];
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                pv[i] = ((w >> i) & 1) ? ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb)) : 0.f;
+                sm4[i & 3] += pv[i];
+              }
+            }
+            uint8_t* blk = Ps + (c >> 1) * kTile;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              *reinterpret_cast<uint4*>(blk + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
+          }
+        }
+        l = l * alpha + (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+      }
       fence_proxy_async();
       tc_fence_before();
       softmax_bar_sync();
-      if (tid == 0) mbar_arrive(bar_p);
+      if (tid == 0) {
+        *pv_acc = exact ? 0u : 1u;                   // read by the producer after its acquire of bar_p
+        mbar_arrive(bar_p);
+      }
     }
     // last tile's O, normalise, stage (the Q tile is dead: every S MMA has completed), store
     mbar_wait(bar_o, (nt - 1) & 1);
@@ -288,7 +356,7 @@ struct FlashBwdArgs {
   const float* delta;
 };
 
-__global__ void __launch_bounds__(FT, 1)
+__global__ void __launch_bounds__(FTB, 1)
 attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
                       const __grid_constant__ CUtensorMap tmdQacc, const __grid_constant__ CUtensorMap tmdK,
@@ -313,7 +381,7 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmdO);
     tma_prefetch_desc(&tmdQacc); tma_prefetch_desc(&tmdK); tma_prefetch_desc(&tmdV);
   }
-  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  if (warp == kBwdSoftmaxWarps) tmem_alloc(tmem_slot, 512);
   if (warp < 4) {
     const int key = k0 + tid;
     const bool ok = key < p.Sk && !(p.key_pad && p.key_pad[(long)b * p.Sk + key]);
@@ -326,7 +394,7 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tdP = tmem + TK, tdV = tmem + 2 * TK, tdK = tdV + HD, tdQ = tdK + HD;
 
-  if (warp == 4) {
+  if (warp == kBwdSoftmaxWarps) {
     if (lane == 0) {
       mbar_arrive_expect_tx(bar_kv, 2 * kTile);
       tma_load_3d(Ks, &tmK, bar_kv, h * HD, k0, b);
@@ -379,11 +447,15 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     }
     __syncwarp();
   } else {
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    // 8 softmax warps: warps w and w + 4 share a TMEM lane quarter (query rows 32 (w & 3) ..) and take one 64-key half
+    // each - P = exp(S - lse) needs no row reduction, so the halves are independent.  Two warps per SM sub-partition:
+    // one waits on TMEM / MUFU / shared memory while the other issues.
+    const int quarter = warp & 3, half = warp >> 2, row = quarter * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
     const float sl2 = p.scale * kLog2e;
     const uint32_t mw[4] = {maskw[0], maskw[1], maskw[2], maskw[3]};
     for (int i = 0; i < nq; ++i) {
-      const int q = i * TQ + tid;
+      const int q = i * TQ + row;
       const bool row_ok = q < p.Sq;
       const long sidx = ((long)b * p.H + h) * p.Sq + q;
       const float lse_l2 = row_ok ? p.lse[sidx] * kLog2e : 0.f;
@@ -392,18 +464,19 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       tc_fence_after();
       {
         uint32_t sa[32], da[32], sb2[32], db2[32];
-        tmem_ld_32x32(tS + lane_addr, sa);
-        tmem_ld_32x32(tdP + lane_addr, da);
+        tmem_ld_32x32(tS + lane_addr + half * 64, sa);
+        tmem_ld_32x32(tdP + lane_addr + half * 64, da);
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t (&rs)[32] = (c & 1) ? sb2 : sa;
-          uint32_t (&rd)[32] = (c & 1) ? db2 : da;
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = half * 2 + cc;                    // 32-key chunk of the tile
+          uint32_t (&rs)[32] = cc ? sb2 : sa;
+          uint32_t (&rd)[32] = cc ? db2 : da;
           tmem_ld_wait();
-          if (c + 1 < 4) {
-            tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, (c & 1) ? sa : sb2);
-            tmem_ld_32x32(tdP + lane_addr + (c + 1) * 32, (c & 1) ? da : db2);
+          if (cc == 0) {
+            tmem_ld_32x32(tS + lane_addr + (c + 1) * 32, sb2);
+            tmem_ld_32x32(tdP + lane_addr + (c + 1) * 32, db2);
           }
-          const uint32_t w = row_ok ? mw[c] : 0u;
+          const uint32_t w = row_ok ? (half ? (cc ? mw[3] : mw[2]) : (cc ? mw[1] : mw[0])) : 0u;
           float pv[32], ds[32];
           if (w == 0xffffffffu) {
 #pragma unroll
@@ -418,40 +491,36 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
               ds[j] = pv[j] * ((__uint_as_float(rd[j]) - delta) * p.scale);
             }
           }
-          uint8_t* pb = Ps + (c >> 1) * kTile; uint8_t* db = dSs + (c >> 1) * kTile;
+          uint8_t* pb = Ps + half * kTile; uint8_t* db = dSs + half * kTile;
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            *reinterpret_cast<uint4*>(pb + swz(tid, (c & 1) * 4 + u)) = pack8(&pv[u * 8]);
-            *reinterpret_cast<uint4*>(db + swz(tid, (c & 1) * 4 + u)) = pack8(&ds[u * 8]);
+            *reinterpret_cast<uint4*>(pb + swz(row, cc * 4 + u)) = pack8(&pv[u * 8]);
+            *reinterpret_cast<uint4*>(db + swz(row, cc * 4 + u)) = pack8(&ds[u * 8]);
           }
         }
       }
       fence_proxy_async();
       tc_fence_before();
-      softmax_bar_sync();
+      bwd_softmax_bar_sync();
       if (tid == 0) mbar_arrive(bar_p);
       // ---- drain dQ_i: TMEM -> fp32 staging -> TMA reduce-add into the fp32 workspace
       mbar_wait(bar_g, i & 1);
       tc_fence_after();
       if (tid == 0) bulk_wait_read<0>();         // the previous tile's reduce has finished reading the staging tile
-      softmax_bar_sync();
+      bwd_softmax_bar_sync();
       {
-        uint32_t r[64];
-        tmem_ld_32x32(tdQ + lane_addr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-        tmem_ld_32x32(tdQ + lane_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        uint32_t r[32];
+        tmem_ld_32x32(tdQ + lane_addr + half * 32, r);
         tmem_ld_wait();
-        // two [128 rows][32 fp32] halves, 128B-swizzled like every other tile here: conflict-free 16-byte stores
-        uint8_t* sb = reinterpret_cast<uint8_t*>(stage);
+        // two [128 rows][32 fp32] halves (one per warp of a quarter), 128B-swizzled: conflict-free 16-byte stores
+        uint8_t* sb = reinterpret_cast<uint8_t*>(stage) + half * kTile;
 #pragma unroll
-        for (int hf = 0; hf < 2; ++hf)
-#pragma unroll
-          for (int u = 0; u < 8; ++u)
-            *reinterpret_cast<uint4*>(sb + hf * kTile + swz(tid, u)) =
-                make_uint4(r[hf * 32 + u * 4], r[hf * 32 + u * 4 + 1], r[hf * 32 + u * 4 + 2], r[hf * 32 + u * 4 + 3]);
+        for (int u = 0; u < 8; ++u)
+          *reinterpret_cast<uint4*>(sb + swz(row, u)) = make_uint4(r[u * 4], r[u * 4 + 1], r[u * 4 + 2], r[u * 4 + 3]);
       }
       fence_proxy_async();
       tc_fence_before();
-      softmax_bar_sync();
+      bwd_softmax_bar_sync();
       if (tid == 0) {
         tma_reduce_add_3d(&tmdQacc, stage, h * HD, i * TQ, b);
         tma_reduce_add_3d(&tmdQacc, reinterpret_cast<uint8_t*>(stage) + kTile, h * HD + 32, i * TQ, b);
@@ -464,22 +533,21 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       uint8_t* dst[2] = {Qs, dOs};
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
-        uint32_t r[64];
-        tmem_ld_32x32(src[g] + lane_addr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
-        tmem_ld_32x32(src[g] + lane_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        uint32_t r[32];
+        tmem_ld_32x32(src[g] + lane_addr + half * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 4; ++u) {
           float f[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[u * 8 + j]);
-          *reinterpret_cast<uint4*>(dst[g] + swz(tid, u)) = pack8(f);
+          *reinterpret_cast<uint4*>(dst[g] + swz(row, half * 4 + u)) = pack8(f);
         }
       }
     }
     fence_proxy_async();
     tc_fence_before();
-    softmax_bar_sync();
+    bwd_softmax_bar_sync();
     if (tid == 0) {
       tma_store_3d(&tmdV, Qs, h * HD, k0, b);
       tma_store_3d(&tmdK, dOs, h * HD, k0, b);
@@ -489,7 +557,7 @@ attn_flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kBwdSoftmaxWarps) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
@@ -578,7 +646,7 @@ int exg_attn_flash_bwd(const void* q, const void* k, const void* v, const void* 
   EXG_LAUNCH_CHECK("attn_delta");
   FlashBwdArgs fa = {{B, H, Sq, Sk, scale, key_pad, const_cast<float*>(lse)}, delta};
   dim3 grid((Sk + TK - 1) / TK, H, B);
-  attn_flash_bwd_kernel<<<grid, FT, kFlashBwdSmem, st>>>(mq, mk, mv, mdo, macc, mdk, mdv, fa);
+  attn_flash_bwd_kernel<<<grid, FTB, kFlashBwdSmem, st>>>(mq, mk, mv, mdo, macc, mdk, mdv, fa);
   EXG_LAUNCH_CHECK("attn_flash_bwd");
   const long n8 = rows * H * HD / 8;
   attn_dq_convert_kernel<<<(unsigned)((n8 + 255) / 256), 256, 0, st>>>(acc, reinterpret_cast<uint16_t*>(dq), ldq, rows,

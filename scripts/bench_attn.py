@@ -30,16 +30,30 @@ for S, B in [(64, 128), (96, 128), (32, 128)] + [(S, max(1, 16384 // S)) for S i
 
     res = []
     for fn, fl in ((fwd, 4.0), (bwd, 10.0)):
+        # CUDA-graph replay of 10 launches: the eager launch path (ctypes + 4-7 tensor-map encodes per call, ~25 us of
+        # host time) would hide every kernel shorter than that
         for _ in range(3):
             fn()
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        n = 20
-        e0.record()
-        for _ in range(n):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
             fn()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        n = 10
+        with torch.cuda.graph(g):
+            for _ in range(n):
+                fn()
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 5
+        e0.record()
+        for _ in range(reps):
+            g.replay()
         e1.record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / n
+        ms = e0.elapsed_time(e1) / (n * reps)
         res += [ms, fl * B * H * S * S * d / (ms * 1e-3) / 1e12]
     print(f"{B:>4} {S:>6} {res[0]:>9.4f} {res[1]:>9.1f} {res[2]:>9.4f} {res[3]:>9.1f}", flush=True)

@@ -290,6 +290,30 @@ def test_attention(K, dt, B, Sq, Sk, masked):
         _check(dkv, dkvr, dt, "attn dkv")
 
 
+def test_flash_attention_lazy_rescale_paths(K):
+    """attention_flash.cu forward takes exponentials relative to the running maximum of the PREVIOUS key tiles and only
+    re-bases (exact two-pass tile, O folded out of TMEM) when some row's tile maximum jumps by more than 2^20.  Keys
+    whose scores jump far beyond that in later tiles, a clip whose first key tile is fully masked (running maximum
+    -inf, then finite) and ordinary tiles in between: every path against the spec."""
+    dt = torch.bfloat16
+    B, H, d, S = 3, 8, 64, 640                      # 5 key tiles
+    q = _rand((B * S, H * d), dt, 1)
+    kv = _rand((B * S, 2 * H * d), dt, 2)
+    k, v = kv[:, :512], kv[:, 512:]
+    kb = k.view(B, S, H * d)
+    kb[0, 256:384] *= 24.0                          # clip 0: tile 2 scores ~24x larger (jump), tiles 3-4 back to normal
+    kb[1, 512:] *= 40.0                             # clip 1: the last tile jumps
+    pad = torch.zeros(B, S, dtype=torch.uint8, device=DEV)
+    pad[2, :128] = 1                                # clip 2: first key tile masked out entirely
+    pad[2, 600:] = 1
+    scale = d ** -0.5
+    o, lse = K.attn_fwd(q, k, v, pad, B, H, S, S, scale)
+    orf, lser = REF.attn_fwd(q, k, v, pad, B, H, S, S, scale)
+    assert torch.isfinite(o.float()).all() and torch.isfinite(lse).all()
+    _check(o, orf, dt, "flash lazy o")
+    _check(lse, lser, dt, "flash lazy lse")
+
+
 # ------------------------------------------------------------------------------------------- NCE
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("S,B,T,N", [(2, 3, 16, 8), (3, 5, 24, 4), (6, 16, 64, 32), (2, 20, 5, 216), (1, 7, 3, 40),
