@@ -636,26 +636,14 @@ int exg_gemm_tc2(const exg_gemm_params* q, void* stream) {
   // 128-wide tile loses on every shape of the step even where it fills the last wave better: these GEMMs are bound
   // by L2 -> SM operand bytes (48 KB per k-block for 128 x 256 vs 2 x 32 KB for two 128 x 128 tiles)
   int bn = q->N <= 128 ? 128 : 256;
-  // CTA pairs (256 x BN tiles over two SMs): two thirds of the operand bytes per flop.  Measured gain: 17 % on long-K
-  // square GEMMs, 5-13 % on plain-epilogue GEMMs of the step; a loss (lock-step of the two epilogues) when the
-  // epilogue carries bias / activation / aux traffic or split-K reduce-adds, so those stay single-CTA.
+  // CTA pairs (256 x BN tiles over two SMs): two thirds of the operand bytes per flop.  Round 1 kept pairs away from
+  // epilogues with bias / activation / aux traffic and from short split-K items (the lock-step of the two epilogues
+  // cost more than the operand bytes saved); with the CTA-scope peer arrive, the smem bias strip and the 3-deep aux
+  // ring that is no longer so: in the train step pairs EVERYWHERE (M > 128) beat both the selective policy and no
+  // pairs - 7.106 vs 7.124 vs 7.359 ms per step, GEMM class 5.48 / 5.55 / 6.03 ms (run r02p).
   static const int no_pair = getenv("EXG_NO_GEMM_PAIR") ? atoi(getenv("EXG_NO_GEMM_PAIR")) : 0;
   const bool splittable = q->epilogue == EXG_EPI_NONE && !q->bias && q->out_dtype == EXG_F32 && kblocks >= 8;
-  int ncta = 1;
-  // (aux-in epilogues: with the cheap peer arrive the pair wins there too, 47.6 -> 43.0 us on du + QuickGELU',
-  // profiles/gemm_ablation_r02.txt; bias / aux-out epilogues stay single-CTA: within noise either way)
-  const bool aux_in_epi = q->epilogue == EXG_EPI_QGELU_BWD || q->epilogue == EXG_EPI_RELU_BWD;
-  if (!no_pair && q->M > BM && (q->epilogue == EXG_EPI_NONE || aux_in_epi) && !q->bias && !q->aux_out) {
-    const long tn = (q->N + bn - 1) / bn;
-    const long t1 = tm1 * tn * q->batch, t2 = ((q->M + 2 * BM - 1) / (2 * BM)) * tn * q->batch;
-    const long sms = exg_num_sms(), pairs = sms / 2;
-    const double r1 = (double)((t1 + sms - 1) / sms), r2 = (double)((t2 + pairs - 1) / pairs);
-    const bool will_split = splittable && t1 * 2 <= sms;
-    if (!will_split && r2 * 2.0 <= r1 * 3.0 + 1e-9) ncta = 2;
-    // split-K weight gradients with a long K per split (the [*, 12288] x [12288, *] GEMMs of the FFN / qkv): the main
-    // loop dominates and pairs win 5-7 % (36.0 -> 33.6, 33.2 -> 31.6, 28.6 -> 26.8 us); the 512 x 512 outputs do not
-    if (will_split && t2 >= 8 && kblocks >= 64) ncta = 2;
-  }
+  int ncta = (!no_pair && q->M > BM) ? 2 : 1;
   {  // tuning overrides (scripts/bench_gemm.py)
     static const int f_bn = getenv("EXG_GEMM_BN") ? atoi(getenv("EXG_GEMM_BN")) : 0;
     static const int f_ncta = getenv("EXG_GEMM_NCTA") ? atoi(getenv("EXG_GEMM_NCTA")) : 0;
