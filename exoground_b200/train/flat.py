@@ -179,7 +179,7 @@ class FlatAdamW:
         if self.world > 1:
             torch.distributed.all_reduce(self.flat_grad(), group=self.pg)
 
-    def reduce_and_step(self, clip_grad=0.0, chunks=4):
+    def reduce_and_step(self, clip_grad=0.0, chunks=1):
         """allreduce() + step() as one pipelined pass (world > 1): chunked all-reduce, AdamW of chunk i under the
         all-reduce of chunk i+1.  Single process: step()."""
         if self.world == 1:

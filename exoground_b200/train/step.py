@@ -35,7 +35,7 @@ class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
                  device="cuda", use_graph=True, process_group=None, cross_gpu_negatives=False,
                  overlap_allreduce=False, bucket_mb=25.0, comm_sms=0, branch_streams=True, early_adamw=False,
-                 clip_grad=0.0, comm_chunks=4, comm_dtype=None, host_dtype=torch.float32):
+                 clip_grad=0.0, comm_chunks=1, comm_dtype=None, host_dtype=torch.float32):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
@@ -74,11 +74,15 @@ class TanTrainStep:
         # (SM count - comm_sms) CTAs instead of queueing a second wave behind the SMs NCCL holds
         self.comm_sms = int(comm_sms)
         self._pending, self._works = [], []
-        # default multi-GPU path: after backward the flat gradient buffer is all-reduced in `comm_chunks`
-        # parameter-aligned chunks on NCCL's stream, and the AdamW launch of chunk i runs on the main stream as soon as
-        # chunk i has arrived - i.e. under the all-reduce of chunk i+1 - so only the last chunk's update is exposed.
-        # comm_dtype=torch.bfloat16 sends bf16 gradients (half the wire bytes; DDP's bf16_compress_hook semantics:
-        # cast, sum in bf16 on the wire, cast back), the default sends the fp32 buffer like DDP does.
+        # multi-GPU path: after backward the flat gradient buffer is all-reduced on NCCL's stream in parameter-aligned
+        # pieces (always cut at the no-decay / decay boundary; `comm_chunks` > 1 cuts further) and the AdamW launch of
+        # piece i is issued as soon as piece i has arrived, i.e. under the all-reduce of piece i+1.  Measured
+        # (profiles/scale_r02k_summary.txt, scale_r02r_summary.txt): more pieces do NOT pay - at 2 GPUs 1 / 4 / 8 chunks
+        # are alike (the 2-rank all-reduce is itself an HBM stream), at 8 GPUs 4 chunks are SLOWER than 1 (7.92 vs
+        # 7.63 ms: four 46 MB all-reduces ride lower on NCCL's latency / bandwidth curve and share HBM with AdamW) -
+        # so the default is 1.  comm_dtype=torch.bfloat16 sends bf16 gradients (half the wire bytes; DDP's
+        # bf16_compress_hook semantics: cast, sum in bf16 on the wire, cast back; -0.15 ms at 2 GPUs, -0.25 ms at 8),
+        # the default sends the fp32 buffer like DDP does.
         self.comm_chunks = max(1, int(comm_chunks))
         self.comm_dtype = comm_dtype if comm_dtype in (torch.bfloat16,) else None
         self._gcomm = None
