@@ -235,7 +235,7 @@ def time_cpu(B, steps, warmup, kind_pref="auto"):
             "ms_per_step": sec * 1e3}
 
 
-def workload_config(n_gpus, xneg=False, batch=0, overlap=False, chunks=1, wire="fp32", host_dtype="bf16"):
+def workload_config(n_gpus, xneg=False, batch=0, overlap=False, chunks=1, wire="fp32", host_dtype="bf16", sharded=True):
     global PER_GPU_BATCH
     if batch:
         PER_GPU_BATCH = batch
@@ -246,6 +246,9 @@ def workload_config(n_gpus, xneg=False, batch=0, overlap=False, chunks=1, wire="
     if n_gpus > 1:
         cfg["grad_allreduce"] = ("NCCL, per-block buckets (~25 MB) issued asynchronously during backward, inside the "
                                  "step's CUDA graph" if overlap else
+                                 f"NCCL reduce-scatter of the {wire} gradients -> AdamW on the owned 1/{n_gpus} of the flat "
+                                 f"state -> all-gather of the updated bf16 weights (sharded optimizer state; same "
+                                 f"arithmetic as all-reduce + replicated AdamW)" if sharded else
                                  f"NCCL, {wire} gradients after backward in {chunks + 1} parameter-aligned pieces; the "
                                  f"AdamW of piece i is issued when piece i has arrived (under the all-reduce of piece i+1)")
     if xneg and n_gpus > 1:
@@ -330,7 +333,8 @@ def run_ours(a):
                       comm_sms=int(os.environ.get("EXG_COMM_SMS", "0")), branch_streams=not a.single_stream,
                       early_adamw=a.early_adamw, comm_chunks=a.comm_chunks,
                       comm_dtype=torch.bfloat16 if a.grad_comm == "bf16" else None,
-                      host_dtype=torch.bfloat16 if a.host_dtype == "bf16" else torch.float32)
+                      host_dtype=torch.bfloat16 if a.host_dtype == "bf16" else torch.float32,
+                      shard_optimizer=not a.replicated_optimizer)
     # padded sentence rows hold N(0,1) noise, not zeros: with the reference's default init (LayerNorm bias 0) an
     # all-zero padded row normalises to 0/0 and the REFERENCE's own gradients turn NaN (tan_model.py:110-111)
     batch = synth.tan_batch(B=B, T=T, N=N, d_video=D_IN, d_text=D_IN, seed=888 + rank, zero_pad_text=False)
@@ -460,7 +464,7 @@ def run_ours(a):
         gf = train_gflop_per_clip(B)
         line = {"metric": METRIC, "value": round(value, 1), "unit": "clips/s", "n_gpus": world, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": dict(workload_config(world, a.xneg, a.batch, a.overlap, a.comm_chunks, a.grad_comm, a.host_dtype),
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": dict(workload_config(world, a.xneg, a.batch, a.overlap, a.comm_chunks, a.grad_comm, a.host_dtype, not a.replicated_optimizer),
                                host_placement=a.placement),
                 "e2e": {"value": round(gb / (ms_e2e * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_e2e, 4),
                         "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last},
@@ -536,6 +540,9 @@ def main():
                          "all-reduce after it (measured: no gain, see DESIGN.md §6)")
     ap.add_argument("--comm-chunks", type=int, default=1,
                     help="N>1: chunks of the gradient all-reduce (AdamW of chunk i under the all-reduce of chunk i+1)")
+    ap.add_argument("--replicated-optimizer", action="store_true",
+                    help="N>1: all-reduce + every rank runs the whole AdamW (DistributedDataParallel's scheme) instead of "
+                         "reduce-scatter -> AdamW on the owned shard -> all-gather of the bf16 weights")
     ap.add_argument("--grad-comm", default="fp32", choices=["fp32", "bf16"],
                     help="N>1: dtype of the gradients on the wire (fp32 = DistributedDataParallel's; bf16 = its "
                          "bf16_compress_hook)")

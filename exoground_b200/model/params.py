@@ -19,6 +19,9 @@ def default_compute_dtype():
     return torch.float32 if v in ("fp32", "float32", "f32") else torch.bfloat16
 
 
+SHARD_PAD = 64 * 64          # slack behind the flat buffers: up to 64 ranks x one 64-element alignment unit
+
+
 def is_no_decay(name):
     """The reference's optimiser policy (train/main.py:352): no weight decay for LayerNorms and biases."""
     name = "." + name
@@ -90,7 +93,9 @@ class FlatParams:
             return False
         named, index, total, n_no_decay, n_used = self._layout()
         dev = named[0][1].device
-        flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        # + SHARD_PAD never-used elements: a sharded optimizer (train/flat.py::ShardPlan) rounds the used part up to a
+        # whole number of equal, 64-aligned shards and reduce-scatters / all-gathers that padded range in place
+        flat = torch.zeros(total + SHARD_PAD, dtype=torch.float32, device=dev)
         self._ptr_check = []
         for n, p in named:
             off, numel, shape = index[n]

@@ -133,10 +133,75 @@ def reduce_and_update(fp, plan, pg, m1, m2, lr, betas, eps, step, gscale, clip, 
             K.adamw(fp.flat[lo:hi], g[lo:hi], m1[lo:hi], m2[lo:hi], sh, lr, b1, b2, eps, wd, step, grad_scale=gscale)
 
 
+class ShardPlan:
+    """Sharded optimizer state (ZeRO-1 style) over the flat buffers: rank r owns elements [r*S, (r+1)*S) of the used
+    part, S a multiple of 64 (the buffers carry SHARD_PAD elements of slack for the rounding)."""
+
+    def __init__(self, fp, world, rank, wd):
+        S = -(-fp.n_used // (world * ALIGN)) * ALIGN
+        self.S, self.padded, self.lo = S, S * world, rank * S
+        if self.padded > fp.flat.numel():
+            raise ValueError(f"flat buffer of {fp.flat.numel()} elements cannot hold {world} shards of {S}")
+        hi = min(self.lo + S, fp.n_used)
+        self.hi_used = max(hi, min(self.lo, fp.n_used))          # end of this rank's part of the used range
+        self.segs = []                                           # (lo, hi, weight decay) AdamW launches of this rank
+        if self.lo < hi:
+            if self.lo < fp.n_no_decay:
+                self.segs.append((self.lo, min(hi, fp.n_no_decay), 0.0))
+            if hi > fp.n_no_decay:
+                self.segs.append((max(self.lo, fp.n_no_decay), hi, wd))
+
+
+def sharded_reduce_and_update(fp, plan, pg, m1, m2, lr, betas, eps, step, gscale, clip, blk2seg, n_seg, seg_sumsq,
+                              gcomm=None, shadow=False):
+    """DistributedDataParallel's all-reduce + a replicated optimizer.step() (train/main.py:413,111) restated as
+    reduce-scatter -> AdamW on the owned shard -> all-gather of the UPDATED weights in the dtype the forward reads.
+    Same arithmetic (every parameter is updated exactly once, from the same summed gradient), less wire and less HBM:
+    the gradient crosses NVLink once (reduce-scatter = half an all-reduce), the weights come back as bf16 shadows (a
+    quarter of an all-reduce) instead of every rank repeating the whole AdamW (0.22 ms at 46 M parameters) on the
+    full fp32 state.  The fp32 master weights and the moments of a rank are current for its own shard only:
+    gather_full() before reading them (checkpoints).  Per-parameter clipping: partial squared norms over the shard,
+    one tiny all-reduce of the [n_parameters] vector."""
+    K = ops.get()
+    g, S, lo = fp.grad, plan.S, plan.lo
+    wire = g
+    if gcomm is not None:
+        K.cast(g[:plan.padded], gcomm.dtype, out=gcomm)
+        wire = gcomm
+    torch.distributed.reduce_scatter_tensor(wire[lo:lo + S], wire[:plan.padded], group=pg)
+    if gcomm is not None:
+        K.cast(gcomm[lo:lo + S], torch.float32, out=g[lo:lo + S])
+    if clip > 0:
+        if plan.hi_used > lo:
+            K.grad_sumsq(g[lo:plan.hi_used], blk2seg[lo // ALIGN:plan.hi_used // ALIGN], n_seg, out=seg_sumsq)
+        else:
+            seg_sumsq.zero_()
+        torch.distributed.all_reduce(seg_sumsq, group=pg)
+    b1, b2 = betas
+    sh_all = fp.shadow if shadow else None
+    for a, b, wd in plan.segs:
+        sh = sh_all[a:b] if sh_all is not None else None
+        if clip > 0:
+            K.adamw_clip(fp.flat[a:b], g[a:b], m1[a:b], m2[a:b], sh, lr, b1, b2, eps, wd, step, blk2seg[a // ALIGN:],
+                         seg_sumsq, clip, grad_scale=gscale)
+        else:
+            K.adamw(fp.flat[a:b], g[a:b], m1[a:b], m2[a:b], sh, lr, b1, b2, eps, wd, step, grad_scale=gscale)
+    pub = sh_all if sh_all is not None else fp.flat
+    torch.distributed.all_gather_into_tensor(pub[:plan.padded], pub[lo:lo + S], group=pg)
+
+
+def gather_full(plan, pg, *buffers):
+    """Completes sharded buffers (fp32 master weights, AdamW moments) on every rank, in place."""
+    for t in buffers:
+        torch.distributed.all_gather_into_tensor(t[:plan.padded], t[plan.lo:plan.lo + plan.S], group=pg)
+
+
 class FlatAdamW:
-    def __init__(self, model, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8, process_group=None, sum_grads=False):
+    def __init__(self, model, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8, process_group=None, sum_grads=False,
+                 shard=False):
         self.model, self.lr, self.wd, self.betas, self.eps = model, lr, wd, betas, eps
         self.pg = process_group
+        self.shard, self._shard_plan = bool(shard), None
         self.world = torch.distributed.get_world_size(process_group) if process_group is not None else 1
         self.grad_scale = 1.0 if sum_grads else 1.0 / self.world
         self.step_count = 0
@@ -185,6 +250,14 @@ class FlatAdamW:
         if self.world == 1:
             return self.step(clip_grad=clip_grad)
         fp = self.model.flat_params()
+        if self.shard:
+            if self._shard_plan is None:
+                self._shard_plan = ShardPlan(fp, self.world, torch.distributed.get_rank(self.pg), self.wd)
+            self.step_count += 1
+            sharded_reduce_and_update(fp, self._shard_plan, self.pg, self.m1, self.m2, self.lr, self.betas, self.eps,
+                                      self.step_count, self.grad_scale, clip_grad, self.blk2seg, len(self.seg_names),
+                                      self.seg_sumsq, shadow=self.model.compute_dtype == torch.bfloat16)
+            return
         if getattr(self, "_plan", None) is None:
             self._plan = plan_chunks(fp, chunks, self.wd)
         self.step_count += 1
@@ -228,8 +301,14 @@ class FlatAdamW:
                     K.adamw(fp.flat[lo:hi], fp.grad[lo:hi], self.m1[lo:hi], self.m2[lo:hi], sh, self.lr, b1, b2,
                             self.eps, wd, self.step_count, grad_scale=self.grad_scale)
 
+    def sync_full(self):
+        """shard=True: completes the fp32 master weights and the moments on every rank (collective)."""
+        if self._shard_plan is not None:
+            gather_full(self._shard_plan, self.pg, self.model.flat_params().flat, self.m1, self.m2)
+
     def state_dict(self):
         """torch.optim.AdamW layout over the reference's two parameter groups (see optim_state_dict)."""
+        self.sync_full()
         return optim_state_dict(self.model, self.m1, self.m2, self.step_count, self.lr, self.wd, self.betas, self.eps)
 
     def load_state_dict(self, sd):

@@ -35,7 +35,7 @@ class TanTrainStep:
     def __init__(self, model, args, B, T, N, d_video, d_text, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8,
                  device="cuda", use_graph=True, process_group=None, cross_gpu_negatives=False,
                  overlap_allreduce=False, bucket_mb=25.0, comm_sms=0, branch_streams=True, early_adamw=False,
-                 clip_grad=0.0, comm_chunks=1, comm_dtype=None, host_dtype=torch.float32):
+                 clip_grad=0.0, comm_chunks=1, comm_dtype=None, host_dtype=torch.float32, shard_optimizer=False):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self._on_cuda = torch.device(device).type == "cuda"      # False only under the tests' op-spec backend
@@ -83,6 +83,11 @@ class TanTrainStep:
         # so the default is 1.  comm_dtype=torch.bfloat16 sends bf16 gradients (half the wire bytes; DDP's
         # bf16_compress_hook semantics: cast, sum in bf16 on the wire, cast back; -0.15 ms at 2 GPUs, -0.25 ms at 8),
         # the default sends the fp32 buffer like DDP does.
+        # shard_optimizer=True (world > 1, no EMA twin): reduce-scatter -> AdamW on the owned 1/W of the flat buffers ->
+        # all-gather of the updated bf16 shadow weights (train/flat.py::sharded_reduce_and_update).  The fp32 master
+        # weights / moments of a rank are then current for its shard only until sync_full() (state_dict() calls it).
+        self.shard_optimizer = bool(shard_optimizer) and self.world > 1 and self.twin is None
+        self._shard_plan = None
         self.comm_chunks = max(1, int(comm_chunks))
         self.comm_dtype = comm_dtype if comm_dtype in (torch.bfloat16,) else None
         self._gcomm = None
@@ -357,6 +362,13 @@ class TanTrainStep:
             self.twin._momentum_update()
 
     # ------------------------------------------------------------------ checkpointing (train/main.py:136-146,469)
+    def sync_full(self):
+        """shard_optimizer: completes the fp32 master weights and the AdamW moments on every rank (collective; call on
+        all ranks before model.state_dict() / state_dict()).  No-op otherwise."""
+        if self._shard_plan is not None:
+            from .flat import gather_full
+            gather_full(self._shard_plan, self.pg, self.model.flat_params().flat, self.m1, self.m2)
+
     def state_dict(self):
         """Optimizer state in torch.optim.AdamW's layout over the reference's two parameter groups: what the
         reference stores under 'optimizer' in its runtime / epoch checkpoints, so training on the fused path can be
@@ -364,6 +376,7 @@ class TanTrainStep:
         from .flat import optim_state_dict
         if not self._prepared:
             self.prepare()
+        self.sync_full()
         return optim_state_dict(self.model, self.m1, self.m2, self.step_count, self.lr, self.wd, self.betas, self.eps)
 
     def load_state_dict(self, sd):
@@ -378,8 +391,19 @@ class TanTrainStep:
 
     def _reduce_and_update(self):
         """Chunked gradient all-reduce with the optimizer pipelined behind it (see __init__; train/flat.py)."""
-        from .flat import plan_chunks, reduce_and_update
+        from .flat import plan_chunks, reduce_and_update, ShardPlan, sharded_reduce_and_update
         fp = self.model.flat_params()
+        if self.shard_optimizer:
+            if self._shard_plan is None:
+                self._shard_plan = ShardPlan(fp, self.world, torch.distributed.get_rank(self.pg), self.wd)
+                if self.comm_dtype is not None:
+                    self._gcomm = torch.empty(self._shard_plan.padded, dtype=self.comm_dtype, device=fp.flat.device)
+            self.step_count += 1
+            sharded_reduce_and_update(fp, self._shard_plan, self.pg, self.m1, self.m2, self.lr, self.betas, self.eps,
+                                      self.step_count, 1.0 if self.xneg is not None else 1.0 / self.world,
+                                      self.clip_grad, self.blk2seg, len(self.seg_names), self.seg_sumsq, self._gcomm,
+                                      shadow=self.model.compute_dtype == torch.bfloat16)
+            return
         if self._chunk_plan is None:
             self._chunk_plan = plan_chunks(fp, self.comm_chunks, self.wd)
             if self.comm_dtype is not None:

@@ -28,12 +28,12 @@ _DEVICE_KEYS = ("video_features", "narration_features", "video_padding_mask", "n
 
 class ExoTrainStep:
     def __init__(self, model, args, lr=1e-4, wd=1e-5, betas=(0.9, 0.999), eps=1e-8, clip_grad=0.0, device="cuda",
-                 process_group=None, branch_streams=True, use_graph=True):
+                 process_group=None, branch_streams=True, use_graph=True, shard_optimizer=False):
         if ops.get().name == "cuda" and not (torch.cuda.is_available() and torch.device(device).type == "cuda"):
             raise RuntimeError("exoground_b200 training needs a CUDA device (no CPU fallback)")
         self.device = torch.device(device)
         self.model, self.args, self.clip_grad = model.to(device), args, clip_grad
-        self.opt = FlatAdamW(self.model, lr, wd, betas, eps, process_group)
+        self.opt = FlatAdamW(self.model, lr, wd, betas, eps, process_group, shard=shard_optimizer)
         self.h2d_bytes = 0
         self._copy_stream, self._staged = None, None
         self._on_cuda = self.device.type == "cuda" and ops.get().name == "cuda"

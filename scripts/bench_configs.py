@@ -69,7 +69,8 @@ def run_exo(a):
     b = synth.exo_batch(B=B, T=T, N=N, d_video=768, d_text=4096, d_ego=768 if a.distill else None, seed=888 + rank)
     b = {k: (v.pin_memory() if torch.is_tensor(v) else v) for k, v in b.items()}
     args = synth.exo_args(use_distill_nce_loss=a.distill, same_view_negative=a.distill)
-    st = ExoTrainStep(m, args, device=f"cuda:{local}", process_group=pg, use_graph=not a.no_graph)
+    st = ExoTrainStep(m, args, device=f"cuda:{local}", process_group=pg, use_graph=not a.no_graph,
+                      shard_optimizer=not a.replicated_optimizer)
 
     def step():
         st.step(b, next_batch=b)      # double-buffered input: every step contains one full H2D copy (copy stream)
@@ -164,6 +165,8 @@ def main():
     ap.add_argument("--layers", type=int, default=6, help="--exo: encoder = decoder depth (SURVEY cfg-3: 6)")
     ap.add_argument("--distill", action="store_true", help="--exo: with the ego-distillation InfoNCE (768-d ego features)")
     ap.add_argument("--no-graph", action="store_true", help="--exo: eager step instead of the CUDA-graph replay")
+    ap.add_argument("--replicated-optimizer", action="store_true",
+                    help="--exo, N>1: all-reduce + replicated AdamW instead of the sharded optimizer")
     ap.add_argument("--videos", type=int, default=80)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)

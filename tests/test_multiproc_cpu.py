@@ -117,7 +117,7 @@ def test_two_rank_gradient_allreduce_gloo():
     assert abs(res[0][2] - res[1][2]) > 0        # different batches -> different local losses
 
 
-def _chunked_worker(rank, world, port, q, clip, bf16_wire):
+def _chunked_worker(rank, world, port, q, clip, bf16_wire, shard=False):
     """The default multi-GPU path: chunked all-reduce with the AdamW of chunk i issued as soon as chunk i has arrived."""
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.set_num_threads(2)
@@ -132,7 +132,7 @@ def _chunked_worker(rank, world, port, q, clip, bf16_wire):
         kw = dict(lr=1e-3, wd=1e-2, device="cpu", use_graph=False, clip_grad=clip)
         m, b = _make(rank)
         st = TanTrainStep(m, args, B, T, N, DIN, DIN, process_group=dist.group.WORLD, comm_chunks=3,
-                          comm_dtype=torch.bfloat16 if bf16_wire else None, **kw)
+                          comm_dtype=torch.bfloat16 if bf16_wire else None, shard_optimizer=shard, **kw)
         st.load_batch(b, non_blocking=False)
         st.prepare()
         calls = []
@@ -141,13 +141,24 @@ def _chunked_worker(rank, world, port, q, clip, bf16_wire):
         loss0 = float(st.run())
         dist.all_reduce = orig_ar
         fp = m.flat_params()
-        plan = st._chunk_plan
-        assert not st._hooked and len(plan) >= 3 and len(calls) == len(plan), (plan, calls)
-        assert sum(n for n, _ in calls) == fp.n_used and plan[0][0] == 0 and plan[-1][1] == fp.n_used
-        assert all(dt == (torch.bfloat16 if bf16_wire else torch.float32) for _, dt in calls)
-        assert any(hi == fp.n_no_decay for _, hi, _ in plan) and all(lo % 64 == 0 for lo, _, _ in plan)
-        starts = {off for n, (off, numel, _) in fp.index.items()}
-        assert all(lo in starts for lo, _, _ in plan)                 # cuts at parameter boundaries only
+        if shard:
+            # reduce-scatter -> AdamW on the owned shard -> all-gather of the weights: the only all-reduce is the tiny
+            # vector of per-parameter squared norms; moments outside the shard are untouched (still zero)
+            sp = st._shard_plan
+            assert sp is not None and sp.S % 64 == 0 and sp.padded >= fp.n_used and sp.lo == rank * sp.S
+            assert [n for n, _ in calls] == ([len(st.seg_names)] if clip > 0 else []), calls
+            other = slice((1 - rank) * sp.S, (1 - rank) * sp.S + sp.S)
+            assert float(st.m1[other].abs().max()) == 0.0 and float(st.m1[sp.lo:sp.lo + sp.S].abs().max()) > 0.0
+            st.sync_full()
+            assert float(st.m1[other].abs().max()) > 0.0
+        else:
+            plan = st._chunk_plan
+            assert not st._hooked and len(plan) >= 3 and len(calls) == len(plan), (plan, calls)
+            assert sum(n for n, _ in calls) == fp.n_used and plan[0][0] == 0 and plan[-1][1] == fp.n_used
+            assert all(dt == (torch.bfloat16 if bf16_wire else torch.float32) for _, dt in calls)
+            assert any(hi == fp.n_no_decay for _, hi, _ in plan) and all(lo % 64 == 0 for lo, _, _ in plan)
+            starts = {off for n, (off, numel, _) in fp.index.items()}
+            assert all(lo in starts for lo, _, _ in plan)                 # cuts at parameter boundaries only
 
         grads = []
         for r in range(world):
@@ -179,10 +190,15 @@ def _chunked_worker(rank, world, port, q, clip, bf16_wire):
         else:
             assert torch.allclose(fp.flat, fref.flat, rtol=1e-5, atol=1e-7), diff.max()
         st.run()
+        st.sync_full()
         mine = fp.flat.clone()
         both = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(both, mine)
         assert torch.equal(both[0], both[1])
+        if shard:                                   # the checkpointed optimizer state is complete on every rank
+            sd = st.state_dict()
+            nz = [float(v["exp_avg"].abs().max()) > 0 for v in sd["state"].values()]
+            assert sum(nz) >= 0.9 * len(nz), (sum(nz), len(nz))
         q.put((rank, "ok", loss0))
     except Exception as e:  # noqa: BLE001
         import traceback
@@ -192,12 +208,13 @@ def _chunked_worker(rank, world, port, q, clip, bf16_wire):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("clip,bf16_wire", [(0.0, False), (0.05, False), (0.05, True)])
-def test_two_rank_chunked_allreduce_pipelined_adamw_gloo(clip, bf16_wire):
+@pytest.mark.parametrize("clip,bf16_wire,shard", [(0.0, False, False), (0.05, False, False), (0.05, True, False),
+                                                  (0.0, False, True), (0.05, False, True), (0.05, True, True)])
+def test_two_rank_chunked_allreduce_pipelined_adamw_gloo(clip, bf16_wire, shard):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_chunked_worker, args=(r, 2, port, q, clip, bf16_wire)) for r in range(2)]
+    procs = [ctx.Process(target=_chunked_worker, args=(r, 2, port, q, clip, bf16_wire, shard)) for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=240) for _ in procs]
@@ -294,7 +311,7 @@ def test_two_rank_cross_gpu_negatives_gloo(head, th):
 
 
 # ----------------------------------------------------------------------------------------------- ExoGround DDP replacement
-def _exo_worker(rank, world, port, q):
+def _exo_worker(rank, world, port, q, shard=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     torch.set_num_threads(2)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -317,9 +334,18 @@ def _exo_worker(rank, world, port, q):
             return m
 
         batches = [synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=500 + r) for r in range(world)]
-        st = ExoTrainStep(make(), args, lr=1e-3, wd=1e-2, clip_grad=3.0, device="cpu", process_group=dist.group.WORLD)
+        st = ExoTrainStep(make(), args, lr=1e-3, wd=1e-2, clip_grad=3.0, device="cpu", process_group=dist.group.WORLD,
+                          shard_optimizer=shard)
         L = st.step(batches[rank])
         g_dist = st.opt.flat_grad().clone()            # all-reduced (sum); the clip is folded into the AdamW read
+        if shard:                                      # reduce-scatter: only the owned shard holds the sum
+            sp = st.opt._shard_plan
+            both_g = [torch.zeros(sp.S) for _ in range(world)]
+            gpad = torch.zeros(sp.padded)
+            gpad[:g_dist.numel()] = g_dist
+            dist.all_gather(both_g, gpad[sp.lo:sp.lo + sp.S].clone())
+            g_dist = torch.cat(both_g)[:g_dist.numel()]
+            st.opt.sync_full()
 
         # single-process restatement: mean of the two ranks' gradients, the reference's per-parameter clip, AdamW
         grads, models = [], []
@@ -362,11 +388,12 @@ def _exo_worker(rank, world, port, q):
 
 
 @pytest.mark.timeout(300)
-def test_two_rank_exo_step_gloo():
+@pytest.mark.parametrize("shard", [False, True], ids=["replicated", "sharded"])
+def test_two_rank_exo_step_gloo(shard):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_exo_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_exo_worker, args=(r, 2, port, q, shard)) for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=240) for _ in procs]
