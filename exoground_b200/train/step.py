@@ -150,6 +150,7 @@ class TanTrainStep:
         self.model._pos_offsets = [self.pos_dev[i] for i in range(n_draw)]
         self._prepared = False
         self._hooked, self._reduced = False, 0
+        self._gacc, self._acc_pending = None, False        # gradient accumulation (run(apply_update=False))
 
     # ------------------------------------------------------------------ host -> device
     def _stage(self, batch, non_blocking=True):
@@ -504,10 +505,16 @@ class TanTrainStep:
         if self._on_cuda:
             torch.cuda.synchronize()
 
-    def run(self):
-        """Device part of one step on the current static buffers.  Returns the 0-d loss tensor (device)."""
+    def run(self, apply_update=True):
+        """Device part of one step on the current static buffers.  Returns the 0-d loss tensor (device).
+        apply_update=False: gradient accumulation (train/main.py:106-113, `backprop_freq`): forward + loss + backward
+        only; this micro-batch's gradient is ADDED to an accumulator (the reference neither divides the loss nor the
+        gradient by backprop_freq) and the next call with apply_update=True clips / all-reduces / applies the sum."""
         if not self._prepared:
             self.prepare()
+        if (self.overlap or self.early_adamw) and (not apply_update or self._acc_pending):
+            raise ValueError("gradient accumulation needs the post-backward gradient exchange (no overlap_allreduce / "
+                             "early_adamw): their collectives / updates run inside backward")
         # the tiny pinned buffers below are rewritten every step: wait until the previous step's asynchronous copies
         # have executed (i.e. the step before it has finished), so a host that runs ahead cannot overwrite them early
         if self._small_h2d is not None:
@@ -529,13 +536,24 @@ class TanTrainStep:
             self._fwd_bwd()
             self._early_on = False
             self._skip = list(self._early_done)
+        if not apply_update or self._acc_pending:
+            g = self.model.flat_params().grad
+            if self._gacc is None:
+                self._gacc = torch.zeros_like(g)
+            self._gacc.add_(g)
+            self._acc_pending = True
+            if not apply_update:
+                return self.loss_out
+            g.copy_(self._gacc)                    # the sum over the micro-batches is what gets clipped and applied
+            self._gacc.zero_()
+            self._acc_pending = False
         if self.world > 1 and not self._hooked:
             self._reduce_and_update()
         else:
             self._optimizer()
         return self.loss_out
 
-    def step(self, batch, next_batch=None):
+    def step(self, batch, next_batch=None, apply_update=True):
         """The user-facing call: host batch in, python float loss out (H2D copies and the loss read-back
         included).  `next_batch` (optional) is staged on the copy stream while this step computes, so a loop
         `for b, nb in zip(batches, batches[1:]): step(b, next_batch=nb)` hides the PCIe copy behind the step."""
@@ -543,7 +561,7 @@ class TanTrainStep:
             self._take_staged()
         else:
             self.load_batch(batch)
-        loss = self.run()
+        loss = self.run(apply_update)
         if next_batch is not None:
             self.prefetch(next_batch)
         return float(loss.item())

@@ -66,7 +66,8 @@ def train(loader, model, optimizer, lr_scheduler, grad_scaler, device, epoch, ar
         b = batch_from_collate(input_data)
         B = b["video"].shape[0]
         if fused_step is not None:
-            loss_val = fused_step.step(b)
+            # train/main.py:107: the optimizer steps on iterations 0, k, 2k, ... of the epoch; in between the gradients add up
+            loss_val = fused_step.step(b, apply_update=(idx % args.backprop_freq == 0))
             loss_dict = {"loss": torch.tensor(loss_val)}
         else:
             video = b["video"].to(device, non_blocking=True)

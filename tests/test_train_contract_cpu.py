@@ -31,8 +31,11 @@ def test_shape_validation():
     tc.check_shape_validation_and_shadow_reload("cpu", torch.float32)
 
 
-def test_repaired_tan_loop(tmp_path):
-    tc.check_tan_loop("cpu", torch.float32, False, tmp_path)
+@pytest.mark.parametrize("backprop_freq", [1, 2])
+def test_repaired_tan_loop(tmp_path, backprop_freq):
+    """backprop_freq=2: the optimizer steps on iterations 0, 2 of each epoch (train/main.py:107) and the gradients of
+    the iterations in between add up, un-normalised - generic loop and fused step (run(apply_update=False)) alike."""
+    tc.check_tan_loop("cpu", torch.float32, False, tmp_path, backprop_freq=backprop_freq)
 
 
 @pytest.mark.parametrize("distill", [False, True])

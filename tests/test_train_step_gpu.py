@@ -253,6 +253,12 @@ def test_repaired_tan_loop(dtype, use_graph, tmp_path):
     tc.check_tan_loop("cuda", dtype, use_graph, tmp_path)
 
 
+def test_repaired_tan_loop_gradient_accumulation(tmp_path):
+    """backprop_freq = 2 (train/main.py:106-113) on the captured step: micro-batch gradients add up in an accumulator
+    between optimizer steps."""
+    tc.check_tan_loop("cuda", torch.float32, True, tmp_path, backprop_freq=2)
+
+
 @pytest.mark.parametrize("random_pos", [0, 1])
 @pytest.mark.parametrize("distill", [False, True])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])

@@ -206,7 +206,7 @@ def check_shape_validation_and_shadow_reload(device, dtype):
         assert torch.equal(fp.shadow_view("video_pre_proj.weight"), m.video_pre_proj.weight.detach().to(torch.bfloat16))
 
 
-def check_tan_loop(device, dtype, use_graph, tmp_path):
+def check_tan_loop(device, dtype, use_graph, tmp_path, backprop_freq=1):
     """The repaired train/main.py::train loop (exoground_b200/train/tan_loop.py): generic mode (autograd + torch AdamW +
     clip_gradients + LambdaLR + runtime checkpoint) and fused mode (TanTrainStep) over the same synthetic loader in the
     collate format of data/loader_egoexo4d_tan.py:333-341 give the same epoch losses and parameters."""
@@ -229,8 +229,8 @@ def check_tan_loop(device, dtype, use_graph, tmp_path):
         a = synth.tan_args(loss_threshold=0.0, use_alignability_head=0)
         rows = []
         plot = types.SimpleNamespace(add_data=lambda k, v, it: rows.append((k, float(v), it)))
-        for k, v in dict(rank=0, backprop_freq=1, clip_grad=clip, iteration=0, runtime_save_iter=2, model_path=str(path),
-                         train_plotter=plot).items():
+        for k, v in dict(rank=0, backprop_freq=backprop_freq, clip_grad=clip, iteration=0, runtime_save_iter=2,
+                         model_path=str(path), train_plotter=plot).items():
             setattr(a, k, v)
         a.rows = rows
         return a
