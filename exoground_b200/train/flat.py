@@ -236,6 +236,24 @@ class FlatAdamW:
     def zero_grad(self):
         self.model.flat_params().grad.zero_()
 
+    def accumulate(self, apply_update):
+        """Gradient accumulation (`backprop_freq`, train/main_egoexo4d_distributed.py:175-181; the steps zero the flat
+        gradient before every backward): adds this micro-batch's gradient to an accumulator; at an update the sum is
+        moved back into the gradient buffer.  Returns True when the caller should reduce / clip / apply now."""
+        if apply_update and not getattr(self, "_acc_pending", False):
+            return True
+        g = self.model.flat_params().grad
+        if getattr(self, "_gacc", None) is None:
+            self._gacc = torch.zeros_like(g)
+        self._gacc.add_(g)
+        self._acc_pending = True
+        if not apply_update:
+            return False
+        g.copy_(self._gacc)
+        self._gacc.zero_()
+        self._acc_pending = False
+        return True
+
     def flat_grad(self):
         fp = self.model.flat_params()
         return fp.grad[:fp.n_used]

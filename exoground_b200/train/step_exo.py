@@ -220,9 +220,10 @@ class ExoTrainStep:
             torch.cuda.synchronize()
         self.graph = None
 
-    def step(self, batch, next_batch=None):
+    def step(self, batch, next_batch=None, apply_update=True):
         """Host batch (the collate dict of data/loader_egoexo4d.py:567-598) in, loss dict out.  `next_batch`
-        (optional) is copied to the device on the copy stream while this step computes."""
+        (optional) is copied to the device on the copy stream while this step computes.  apply_update=False:
+        gradient accumulation (`backprop_freq`, main_egoexo4d_distributed.py:176) - forward + loss + backward only."""
         self.model.train()
         b = self._take(batch)
         if not self.opt.attached:
@@ -248,14 +249,17 @@ class ExoTrainStep:
             if next_batch is not None:
                 self.prefetch(next_batch)
             self.graph.replay()
-            self.opt.reduce_and_step(clip_grad=self.clip_grad)
+            if self.opt.accumulate(apply_update):
+                self.opt.reduce_and_step(clip_grad=self.clip_grad)
             return self._loss_dict(self._out[0], self._out[1], self._out[2], batch)
         else:
             self.opt.zero_grad()
             if next_batch is not None:
                 self.prefetch(next_batch)
             loss, stats, per_sec = self._device_fwd_bwd(b)
-            self.opt.reduce_and_step(clip_grad=self.clip_grad)
+            if self.opt.accumulate(apply_update):
+                self.opt.reduce_and_step(clip_grad=self.clip_grad)
             return self._loss_dict(loss, stats, per_sec, batch)
-        self.opt.reduce_and_step(clip_grad=self.clip_grad)   # per-parameter clip folded into AdamW's gradient read
+        if self.opt.accumulate(apply_update):
+            self.opt.reduce_and_step(clip_grad=self.clip_grad)   # per-parameter clip folded into AdamW's gradient read
         return L

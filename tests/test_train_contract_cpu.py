@@ -41,3 +41,7 @@ def test_repaired_tan_loop(tmp_path, backprop_freq):
 @pytest.mark.parametrize("distill", [False, True])
 def test_exo_step_device_loss_matches_get_loss(distill):
     tc.check_exo_step_paths("cpu", torch.float32, distill)
+
+
+def test_exo_step_gradient_accumulation():
+    tc.check_exo_accumulation("cpu", torch.float32)

@@ -265,3 +265,9 @@ def test_repaired_tan_loop_gradient_accumulation(tmp_path):
 def test_exo_step_graph_matches_eager(dtype, distill, random_pos):
     """ExoTrainStep: CUDA-graph replay == eager device-loss step == eager step through get_loss."""
     tc.check_exo_step_paths("cuda", dtype, distill, random_pos)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_exo_step_gradient_accumulation(dtype):
+    """ExoTrainStep(apply_update=False) on the captured step: two micro-batches == one update with the summed gradient."""
+    tc.check_exo_accumulation("cuda", dtype)

@@ -310,3 +310,43 @@ def check_exo_step_paths(device, dtype, distill, random_pos=1):
                 vb = b[k]["mean"] if isinstance(b[k], dict) else float(b[k])
                 assert abs(va - vb) <= tol * max(1.0, abs(va)), (md, i, k, va, vb)
         _assert_params_close(m1, m0, 1e-3, 3, f"exo step {md}", mult=1.0 if fp32 else 30.0)
+
+
+def check_exo_accumulation(device, dtype):
+    """ExoTrainStep.step(apply_update=False) (`backprop_freq`, main_egoexo4d_distributed.py:175-181): two micro-batches
+    accumulated and applied == one update with the SUM of their gradients taken at the same parameters."""
+    from exoground_b200.model import ExoGroundingTransformer
+    from exoground_b200.train.step_exo import ExoTrainStep
+    Dv, Dt, Bx, Tx, Nx = 48, 64, 3, 16, 8
+    args = synth.exo_args()
+    batches = [synth.exo_batch(B=Bx, T=Tx, N=Nx, d_video=Dv, d_text=Dt, d_ego=Dv, seed=s) for s in (11, 12)]
+
+    def make(use_graph):
+        m = ExoGroundingTransformer(2, 2, video_embed_dim=Dv, text_embed_dim=Dt, random_pos_start=0, use_text_pos_enc=1,
+                                    compute_dtype=dtype)
+        m.load_state_dict(synth.fill_state_dict({k: v.shape for k, v in m.state_dict().items()}, seed=5))
+        return m, ExoTrainStep(m, args, lr=1e-3, wd=1e-2, eps=1e-4, clip_grad=0.5, device=device, use_graph=use_graph)
+    on_cuda = torch.device(device).type == "cuda"
+    mA, stA = make(on_cuda)
+    stA.step(batches[0], apply_update=False)
+    pA0 = mA.flat_params().flat.clone()
+    assert stA.opt.step_count == 0                     # nothing applied yet
+    stA.step(batches[1], apply_update=True)
+    assert stA.opt.step_count == 1 and not stA.opt._acc_pending
+    assert float(stA.opt._gacc.abs().max()) == 0.0
+    mB, stB = make(False)
+    grads = []
+    for b in batches:
+        db = stB.to_device(b)
+        if not stB.opt.attached:
+            for p in mB.parameters():
+                p.grad = None
+            stB._fwd_bwd(db)
+            stB.opt.attach()
+        stB.opt.zero_grad()
+        stB._fwd_bwd(db)
+        grads.append(stB.opt.flat_grad().clone())
+    assert torch.equal(pA0[:grads[0].numel()], mB.flat_params().flat[:grads[0].numel()])      # untouched by the first call
+    stB.opt.flat_grad().copy_(grads[0] + grads[1])
+    stB.opt.reduce_and_step(clip_grad=0.5)
+    _assert_params_close(mA, mB, 1e-3, 1, "exo accumulation", mult=1.0 if dtype == torch.float32 else 30.0)
