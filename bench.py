@@ -410,7 +410,9 @@ def run_ours(a):
                      "clocks": s2.stop() if rank == 0 else None}
 
     # ---- one profiled eager step: per-kernel-class CUDA-event timings + launch count
+    # (single stream for this one step: with the two branches on concurrent streams the per-class event times overlap)
     graph, tr.graph = tr.graph, None
+    branch, model._branch_stream = getattr(model, "_branch_stream", None), None
     tr.run(); torch.cuda.synchronize()
     c1 = lib.launch_count()
     lib.profile_begin()
@@ -418,6 +420,7 @@ def run_ours(a):
     prof = lib.profile_end()
     launches_per_step = lib.launch_count() - c1
     tr.graph = graph
+    model._branch_stream = branch
 
     if rank == 0:
         peaks = {}
@@ -445,7 +448,7 @@ def run_ours(a):
         ach = tv["work"] / (tv["ms"] * 1e-3) / (1e12 if tensor else 1e9)
         traffic, traffic_src = None, None
         try:      # DRAM bytes per launch of this kernel class from the committed `ncu --set full` capture
-            nt = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))
+            nt = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r02.json")))
             traffic = round(nt[top]["dram_bytes_per_launch"])
             traffic_src = nt["source"]
         except Exception:
@@ -458,7 +461,7 @@ def run_ours(a):
                 "traffic_source": traffic_src, "peak_source": src,
                 "launches": tv["launches"], "avg_launch_ms": round(tv["ms"] / tv["launches"], 5),
                 "how": "sum of algorithmic work / sum of CUDA-event durations of every launch of this kernel "
-                       "class in one profiled eager step"}
+                       "class in one profiled eager, single-stream step"}
         gb = B * world
         value = gb / (ms * 1e-3)
         gf = train_gflop_per_clip(B)
