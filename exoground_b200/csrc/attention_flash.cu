@@ -309,6 +309,249 @@ attn_flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
   }
 }
 
+// ------------------------------------------------------------------------------------------ forward, version 2
+// The version above serialises, per 128-key tile and CTA, softmax -> barrier -> P.V + the NEXT Q.K^T -> barrier: a
+// quarter of all stall samples sit in the softmax warps' wait for S (profiles/ncu_full_r02o_flash_summary.txt).  Here
+// the key tile is 64 keys, S and P are double-buffered (TMEM: S[2] x 64 columns + O 64 = 192; smem: Q 16 KB, K and V
+// 3 x 8 KB each, P 2 x 16 KB = 96 KB, still two CTAs per SM), and the producer issues S_{j+2} = Q K_{j+2}^T as soon as
+// the softmax warps have consumed S_j - i.e. while they work on S_{j+1} - so a score tile is always waiting for them.
+// Softmax: as above (one read of S per tile, exponentials relative to the running maximum of the previous tiles, O
+// accumulated in TMEM, exact re-base when some row's maximum jumps by more than 2^kLazyLog2).
+constexpr int KT2 = 64;                        // keys per tile
+constexpr uint32_t kKvTile = KT2 * HD * 2;     // 8 KB
+constexpr int kKvStages = 3;
+
+__global__ void __launch_bounds__(FT, 2)
+attn_flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, AtcArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* Qs = smem; uint8_t* Ks = smem + kTile; uint8_t* Vs = Ks + kKvStages * kKvTile;
+  uint8_t* Ps = Vs + kKvStages * kKvTile;        // [2][128 rows][64 keys]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * kTile);
+  uint64_t *bar_q = bars, *bar_k = bars + 1 /* [3] */, *bar_v = bars + 4 /* [3] */, *bar_s = bars + 7 /* [2] */,
+           *bar_p = bars + 9 /* [2] */, *bar_pv = bars + 11 /* [2] */;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint32_t* pv_acc = tmem_slot + 1;              // [2]: 1 = P_j V_j accumulates onto O in TMEM, 0 = it restarts O
+  uint32_t* maskw = tmem_slot + 4;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * TQ;
+  const int nt = (p.Sk + KT2 - 1) / KT2;
+  if (tid == 0) {
+    for (int i = 0; i < 13; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 256);
+  build_mask_all(maskw, p, b, nt * 2, warp, lane, FT / 32);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem /* + 64 * buffer */, tO = tmem + 2 * KT2;
+
+  if (warp == 4) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar_q, kTile);
+      tma_load_3d(Qs, &tmQ, bar_q, h * HD, q0, b);
+      for (int j = 0; j < kKvStages && j < nt; ++j) {
+        mbar_arrive_expect_tx(&bar_k[j], kKvTile);
+        tma_load_3d(Ks + j * kKvTile, &tmK, &bar_k[j], h * HD, j * KT2, b);
+        mbar_arrive_expect_tx(&bar_v[j], kKvTile);
+        tma_load_3d(Vs + j * kKvTile, &tmV, &bar_v[j], h * HD, j * KT2, b);
+      }
+      mbar_wait(bar_q, 0);
+      for (int j = 0; j < 2 && j < nt; ++j) {    // S_0, S_1: both score buffers start free
+        mbar_wait(&bar_k[j], 0);
+        tc_fence_after();
+        mma_kmajor_k64(tS + j * KT2, smem_u32(Qs), smem_u32(Ks + j * kKvTile), KT2);
+        umma_commit(&bar_s[j]);
+      }
+      const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);
+      for (int j = 0; j < nt; ++j) {
+        const int bf = j & 1, st = j % kKvStages;
+        mbar_wait(&bar_p[bf], (j >> 1) & 1);     // P_j in smem, S_j consumed
+        const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(&pv_acc[bf]);
+        mbar_wait(&bar_v[st], (j / kKvStages) & 1);
+        tc_fence_after();
+        // O (+)= P_j[128 x 64 keys] V_j[64 keys x 64]: A K-major, B MN-major
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(tO, umma_smem_desc(smem_u32(Ps) + bf * kTile + k * 32, 16, 1024),
+                    umma_smem_desc(smem_u32(Vs) + st * kKvTile + k * 2048, 8192, 1024), idesc_pv, acc | (uint32_t)(k > 0));
+        umma_commit(&bar_pv[bf]);
+        if (j + 2 < nt) {                        // the score buffer S_j lived in takes S_{j+2}
+          const int s2 = (j + 2) % kKvStages;
+          mbar_wait(&bar_k[s2], ((j + 2) / kKvStages) & 1);
+          tc_fence_after();
+          mma_kmajor_k64(tS + bf * KT2, smem_u32(Qs), smem_u32(Ks + s2 * kKvTile), KT2);
+          umma_commit(&bar_s[bf]);
+        }
+        if (j + kKvStages < nt) {                // K stage of tile j: S_j completed before the softmax warps read it
+          mbar_arrive_expect_tx(&bar_k[st], kKvTile);
+          tma_load_3d(Ks + st * kKvTile, &tmK, &bar_k[st], h * HD, (j + kKvStages) * KT2, b);
+        }
+        if (j >= 1 && j + 2 < nt) {              // V stage of tile j-1 is free once P_{j-1} V_{j-1} has completed
+          mbar_wait(&bar_pv[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          const int sv = (j + 2) % kKvStages;    // == (j - 1) % 3
+          mbar_arrive_expect_tx(&bar_v[sv], kKvTile);
+          tma_load_3d(Vs + sv * kKvTile, &tmV, &bar_v[sv], h * HD, (j + 2) * KT2, b);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    const float sl2 = p.scale * kLog2e;
+    float m = -INFINITY, l = 0.f;
+    float o[HD];
+#pragma unroll
+    for (int i = 0; i < HD; ++i) o[i] = 0.f;
+    for (int j = 0; j < nt; ++j) {
+      const int bf = j & 1;
+      const uint32_t tSj = tS + bf * KT2;
+      uint8_t* Pj = Ps + bf * kTile;
+      mbar_wait(&bar_s[bf], (j >> 1) & 1);
+      if (j >= 2) mbar_wait(&bar_pv[bf], ((j - 2) >> 1) & 1);      // P buffer: P_{j-2} V_{j-2} has read it
+      tc_fence_after();
+      const uint32_t mw0 = maskw[j * 2], mw1 = maskw[j * 2 + 1];
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      float sm4[4] = {0.f, 0.f, 0.f, 0.f};
+      bool exact = j == 0;
+      uint32_t ra[32], rb[32];
+      if (!exact) {
+        const float nb = -(m == -INFINITY ? 0.f : m) * sl2;
+        tmem_ld_32x32(tSj + lane_addr, ra);
+        tmem_ld_32x32(tSj + lane_addr + 32, rb);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t (&cur)[32] = c ? rb : ra;
+          if (c == 0) tmem_ld_wait();            // (both loads were issued together; one wait covers them)
+          const uint32_t w = c ? mw1 : mw0;
+          float pv[32];
+          if (w == 0xffffffffu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float sv = __uint_as_float(cur[i]);
+              mx4[i & 3] = fmaxf(mx4[i & 3], sv);
+              pv[i] = ex2_approx(fmaf(sv, sl2, nb));
+              sm4[i & 3] += pv[i];
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const float sv = __uint_as_float(cur[i]);
+              const bool on = (w >> i) & 1;
+              if (on) mx4[i & 3] = fmaxf(mx4[i & 3], sv);
+              pv[i] = on ? ex2_approx(fmaf(sv, sl2, nb)) : 0.f;
+              sm4[i & 3] += pv[i];
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            *reinterpret_cast<uint4*>(Pj + swz(tid, c * 4 + u)) = pack8(&pv[u * 8]);
+        }
+        const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        const bool jump = mt != -INFINITY && (mt - m) * sl2 > kLazyLog2;
+        exact = softmax_bar_or(jump);              // CTA-uniform
+        if (!exact) l += (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+      }
+      if (exact) {
+        if (j == 0) {                              // tile maximum (later tiles know it from the single pass)
+          tmem_ld_32x32(tSj + lane_addr, ra);
+          tmem_ld_32x32(tSj + lane_addr + 32, rb);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t (&cur)[32] = c ? rb : ra;
+            const uint32_t w = c ? mw1 : mw0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if ((w >> i) & 1) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(cur[i]));
+          }
+        }
+        const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        const float m_new = fmaxf(m, mt);
+        const float msafe = m_new == -INFINITY ? 0.f : m_new;
+        const float alpha = ex2_approx((m - msafe) * sl2);        // m = -inf -> 0 (o and l are 0 then anyway)
+        m = m_new;
+        if (j > 0) {                                              // fold the O accumulated in TMEM since the last exact tile
+          mbar_wait(&bar_pv[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          tc_fence_after();
+          uint32_t r[64];
+          tmem_ld_32x32(tO + lane_addr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+          tmem_ld_32x32(tO + lane_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < HD; ++i) o[i] = (o[i] + __uint_as_float(r[i])) * alpha;
+        }
+        const float nb = -msafe * sl2;
+        sm4[0] = sm4[1] = sm4[2] = sm4[3] = 0.f;
+        if (j > 0) {                               // (j == 0: ra / rb still hold the tile)
+          tmem_ld_32x32(tSj + lane_addr, ra);
+          tmem_ld_32x32(tSj + lane_addr + 32, rb);
+          tmem_ld_wait();
+        }
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t (&cur)[32] = c ? rb : ra;
+          const uint32_t w = c ? mw1 : mw0;
+          float pv[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            pv[i] = ((w >> i) & 1) ? ex2_approx(fmaf(__uint_as_float(cur[i]), sl2, nb)) : 0.f;
+            sm4[i & 3] += pv[i];
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            *reinterpret_cast<uint4*>(Pj + swz(tid, c * 4 + u)) = pack8(&pv[u * 8]);
+        }
+        l = l * alpha + (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      softmax_bar_sync();
+      if (tid == 0) {
+        pv_acc[bf] = exact ? 0u : 1u;              // read by the producer after its acquire of bar_p[bf]
+        mbar_arrive(&bar_p[bf]);
+      }
+    }
+    // last tile's O, normalise, stage (the Q tile is dead: every S MMA has completed), store
+    mbar_wait(&bar_pv[(nt - 1) & 1], ((nt - 1) >> 1) & 1);
+    tc_fence_after();
+    {
+      uint32_t r[64];
+      tmem_ld_32x32(tO + lane_addr, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+      tmem_ld_32x32(tO + lane_addr + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+      tmem_ld_wait();
+      const float inv = 1.0f / l;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = (o[u * 8 + i] + __uint_as_float(r[u * 8 + i])) * inv;
+        *reinterpret_cast<uint4*>(Qs + swz(tid, u)) = pack8(f);
+      }
+    }
+    if (q0 + tid < p.Sq && p.lse) p.lse[((long)b * p.H + h) * p.Sq + q0 + tid] = m * p.scale + __logf(l);
+    fence_proxy_async();
+    tc_fence_before();
+    softmax_bar_sync();
+    if (tid == 0) {
+      tma_store_3d(&tmO, Qs, h * HD, q0, b);
+      bulk_commit();
+      bulk_wait_all();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
 // ------------------------------------------------------------------------------------------ backward
 // delta[b, h, q] = <dO[b, q, h, :], O[b, q, h, :]>; one warp per (clip, query) row, 4 lanes per head.
 __global__ void attn_delta_kernel(const uint16_t* __restrict__ o, const uint16_t* __restrict__ dout, long ldo,
@@ -598,10 +841,26 @@ int exg_attn_flash_fwd(const void* q, const void* k, const void* v, long ldq, lo
                        float scale, void* stream) {
   CUtensorMap mq, mk, mv, mo;
   int rc;
+  // version 2 (64-key tiles, double-buffered scores) unless EXG_FLASH_FWD_V1=1
+  static const int v1 = getenv("EXG_FLASH_FWD_V1") ? atoi(getenv("EXG_FLASH_FWD_V1")) : 0;
   if ((rc = seq_map(&mq, q, B, Sq, H * HD, ldq))) return rc;
-  if ((rc = seq_map(&mk, k, B, Sk, H * HD, ldk))) return rc;
-  if ((rc = seq_map(&mv, v, B, Sk, H * HD, ldv))) return rc;
+  if ((rc = seq_map(&mk, k, B, Sk, H * HD, ldk, v1 ? 128 : KT2))) return rc;
+  if ((rc = seq_map(&mv, v, B, Sk, H * HD, ldv, v1 ? 128 : KT2))) return rc;
   if ((rc = seq_map(&mo, o, B, Sq, H * HD, ldo))) return rc;
+  if (!v1) {
+    static size_t cur2 = 0;
+    const size_t need2 = fwd_smem(Sk);           // same footprint: 96 KB of tiles + barriers + one mask word per 32 keys
+    if (need2 > cur2) {
+      cudaError_t e = cudaFuncSetAttribute(attn_flash_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need2);
+      if (e != cudaSuccess) { exg_set_error("attn_flash_fwd2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
+      cur2 = need2;
+    }
+    AtcArgs a2 = {B, H, Sq, Sk, scale, key_pad, lse};
+    dim3 grid2((Sq + TQ - 1) / TQ, H, B);
+    attn_flash_fwd2_kernel<<<grid2, FT, need2, (cudaStream_t)stream>>>(mq, mk, mv, mo, a2);
+    EXG_LAUNCH_CHECK("attn_flash_fwd2");
+    return 0;
+  }
   static size_t cur = 0;
   const size_t need = fwd_smem(Sk);
   if (need > cur) {
