@@ -372,6 +372,65 @@ __global__ void colsum_kernel(const void* __restrict__ x, int xd, const float* _
   }
 }
 
+// bf16 fast path of the above: 16-byte loads (8 columns per thread, a warp covers 512 contiguous bytes of a row) and 8
+// rows in flight per thread (32 KB per block) - the 8-byte / 4-deep version above sustains ~1.4 TB/s on the
+// [16 K x 1.5-2 K] gradient tensors of the ExoGround step, a third of what the same bytes stream at.
+__global__ void __launch_bounds__(256) colsum_bf16x8_kernel(const uint16_t* __restrict__ x, const float* __restrict__ roww,
+                                                            long M, long N, long ldx, float* __restrict__ out,
+                                                            long rows_per_block) {
+  __shared__ float sm[8][32][9];               // (+1: the cross-row reduction reads a column of this array)
+  const long col = ((long)blockIdx.x * 32 + threadIdx.x) * 8;
+  const long r0 = (long)blockIdx.y * rows_per_block;
+  const long r1 = min(M, r0 + rows_per_block);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  if (col < N) {
+    const uint16_t* base = x + col;
+    long r = r0 + threadIdx.y;
+    for (; r + 56 < r1; r += 64) {
+      uint4 v[8];
+      float w[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        v[u] = *reinterpret_cast<const uint4*>(base + (r + 8 * u) * ldx);
+        w[u] = roww ? roww[r + 8 * u] : 1.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint32_t q[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          acc[2 * k] = fmaf(__uint_as_float(q[k] << 16), w[u], acc[2 * k]);
+          acc[2 * k + 1] = fmaf(__uint_as_float(q[k] & 0xffff0000u), w[u], acc[2 * k + 1]);
+        }
+      }
+    }
+    for (; r < r1; r += 8) {
+      const uint4 v = *reinterpret_cast<const uint4*>(base + r * ldx);
+      const float w = roww ? roww[r] : 1.f;
+      const uint32_t q[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        acc[2 * k] = fmaf(__uint_as_float(q[k] << 16), w, acc[2 * k]);
+        acc[2 * k + 1] = fmaf(__uint_as_float(q[k] & 0xffff0000u), w, acc[2 * k + 1]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) sm[threadIdx.y][threadIdx.x][i] = acc[i];
+  __syncthreads();
+  // 256 threads, 256 columns of the strip: thread t sums column t over the 8 row lanes
+  const int t = threadIdx.y * 32 + threadIdx.x;
+  const long c = (long)blockIdx.x * 256 + t;
+  if (c < N) {
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sum += sm[k][t >> 3][t & 7];
+    atomicAdd(out + c, sum);
+  }
+}
+
 // y[r] = <x[r, :], w> (+ bias[0]): one warp per row (Linear with one output: the alignability head, tan_model.py:64-68)
 __global__ void rowdot_kernel(const void* __restrict__ x, int xd, const float* __restrict__ w,
                               const float* __restrict__ bias, float* __restrict__ y, long rows, int C) {
@@ -607,6 +666,18 @@ static int colsum_impl(const void* x, int x_dtype, const float* roww, long M, lo
   }
   if (!accumulate) EXG_CUDA(cudaMemsetAsync(out, 0, (size_t)N * sizeof(float), s));
   if (M <= 0) return 0;
+  if (x_dtype == EXG_BF16 && N % 8 == 0 && ldx % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const long strips8 = (N + 255) / 256;
+    const long target8 = 4L * exg_num_sms();
+    long splits8 = (target8 + strips8 - 1) / strips8;
+    long rpb = (M + splits8 - 1) / splits8;
+    if (rpb < 64) rpb = 64;
+    splits8 = (M + rpb - 1) / rpb;
+    dim3 grid8((unsigned)strips8, (unsigned)splits8), block8(32, 8);
+    colsum_bf16x8_kernel<<<grid8, block8, 0, s>>>(reinterpret_cast<const uint16_t*>(x), roww, M, N, ldx, out, rpb);
+    EXG_LAUNCH_CHECK("colsum_bf16x8");
+    return 0;
+  }
   long strips = (N + 127) / 128;
   long target = 4L * exg_num_sms();
   long splits = (target + strips - 1) / strips;

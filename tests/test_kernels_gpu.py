@@ -230,11 +230,15 @@ def test_add_rows_and_l2norm(K):
         _check(dx, dxr, dt, "l2 bwd")
 
 
-@pytest.mark.parametrize("shape", [(12288, 512), (777, 1536), (300, 2), (300, 1), (5, 2048)])
+@pytest.mark.parametrize("shape", [(12288, 512), (777, 1536), (300, 2), (300, 1), (5, 2048), (17408, 2048), (4100, 264),
+                                   (63, 8), (1000, 12)])
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 def test_colsum(K, shape, dt):
     x = _rand(shape, dt, 1)
     _check(K.colsum(x), REF.colsum(x), torch.float32, "colsum", scale=math.sqrt(shape[0]) * 3)
+    if shape[1] >= 24 and shape[1] % 8 == 0:          # a column slice (row stride > N), as the qkv gradient views are
+        v = x[:, 8:shape[1] - 8]
+        _check(K.colsum(v), REF.colsum(v), torch.float32, "colsum view", scale=math.sqrt(shape[0]) * 3)
 
 
 def test_cast_and_stage_mean(K):
