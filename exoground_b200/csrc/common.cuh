@@ -62,9 +62,17 @@ static inline bool exg_valid_dtype(int d) { return d == EXG_F32 || d == EXG_BF16
 static inline size_t exg_dtype_size(int d) { return d == EXG_F32 ? 4 : 2; }
 
 // ---------------------------------------------------------------- device helpers
+// Row r of a dense [rows, C] view -> row of the strided destination (video / text rows inside the joint sequence).
+// Row counts fit 32 bits on this path (checked on the host: EXG_MAX_ROWS), so this is ONE 32-bit division; the two
+// 64-bit ones it replaces were ~250 of the ~400 instructions a LayerNorm thread issued per row (ncu: issue slots 50 %
+// busy in an HBM-bound kernel, profiles/ncu_full_r02v_ln_summary.txt).
 __device__ __forceinline__ long exg_map_row(const exg_rowmap& m, long r) {
-  return (r / m.group) * m.group_stride + (r % m.group) + m.offset;
+  if (m.group > r) return r + m.offset;                   // identity maps (group = rows) and the first group
+  const unsigned g = (unsigned)m.group, rr = (unsigned)r;
+  const unsigned q = rr / g;
+  return (long)q * m.group_stride + (long)(rr - q * g) + m.offset;
 }
+constexpr long EXG_MAX_ROWS = 0x7fffffffL;
 
 __device__ __forceinline__ float bf16_bits_to_float(uint16_t b) {
   return __uint_as_float(((uint32_t)b) << 16);

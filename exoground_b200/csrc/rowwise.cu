@@ -52,7 +52,7 @@ ln_fwd_kernel(const void* __restrict__ x, int xd, const float* __restrict__ gamm
     if (rstd_out) rstd_out[row] = rstd;
   }
   const long orow = exg_map_row(map_y, row);
-  const long arow = add ? (row % add_period) : 0;
+  const long arow = add ? (long)((unsigned)row % (unsigned)add_period) : 0;
 #pragma unroll
   for (int j = 0; j < NCH; ++j) {
     int col = (j * 32 + lane) * 4;
@@ -541,6 +541,7 @@ extern "C" int exg_layernorm_fwd(const void* x, int x_dtype, const float* gamma,
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096, "layernorm_fwd: C=%d must be a multiple of 4, <= 4096", C);
   EXG_CHECK_ARG(rowmap_ok(map_y) && (!add || add_period > 0), "layernorm_fwd: bad row map");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   cudaStream_t s = (cudaStream_t)stream;
   int blocks = (int)((rows + 3) / 4);
   ExgProfScope prof(EXG_PC_LN_FWD, (double)rows * C * (exg_dtype_size(x_dtype) + (y ? exg_dtype_size(y_dtype) : 0) + (y2 ? exg_dtype_size(y2_dtype) : 0)), stream);
@@ -559,6 +560,7 @@ extern "C" int exg_add_layernorm_fwd(const void* x, int x_dtype, const float* re
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096, "add_layernorm_fwd: C=%d must be a multiple of 4, <= 4096", C);
   EXG_CHECK_ARG(rowmap_ok(map_y), "add_layernorm_fwd: bad row map");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   cudaStream_t s = (cudaStream_t)stream;
   int blocks = (int)((rows + 3) / 4);
   ExgProfScope prof(EXG_PC_LN_FWD, (double)rows * C * (exg_dtype_size(x_dtype) + 8 + exg_dtype_size(y_dtype)), stream);
@@ -580,6 +582,7 @@ extern "C" int exg_layernorm_bwd(const void* dy1, int dy1_dtype, exg_rowmap map1
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096, "layernorm_bwd: C=%d unsupported", C);
   EXG_CHECK_ARG(rowmap_ok(map1) && (!dy2 || rowmap_ok(map2)), "layernorm_bwd: bad row map");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   cudaStream_t s = (cudaStream_t)stream;
   const int threads = C > 1024 ? 128 : kLnBwdThreads;   // keeps the [warps][3C] reduction buffer under 227 KB
   EXG_CHECK_ARG(!dxsum || C <= 2048, "layernorm_bwd: dxsum needs C <= 2048");
@@ -614,6 +617,7 @@ extern "C" int exg_add_rows(const float* x, exg_rowmap map_x, const float* x2, e
   EXG_CHECK_ARG(rowmap_ok(map_x) && rowmap_ok(map_out) && (!x2 || rowmap_ok(map_x2)) &&
                     (!add || add_period > 0), "add_rows: bad row map");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * (4.0 + (x2 ? 4 : 0) + (out ? exg_dtype_size(out_dtype) : 0) + (out2 ? exg_dtype_size(out2_dtype) : 0)), stream);
   add_rows_kernel<<<grid_for(rows * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(
       x, map_x, x2, map_x2, add, add_period, out, out_dtype, map_out, out2, out2_dtype, rows, C);
@@ -627,6 +631,7 @@ extern "C" int exg_l2norm_fwd(const void* x, int x_dtype, exg_rowmap map_x, void
   EXG_CHECK_ARG(exg_valid_dtype(x_dtype) && exg_valid_dtype(y_dtype), "l2norm_fwd: bad dtype");
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096 && rowmap_ok(map_x), "l2norm_fwd: bad C / map");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   int blocks = (int)((rows + 3) / 4);
   ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * (exg_dtype_size(x_dtype) + exg_dtype_size(y_dtype)), stream);
   DISPATCH_NCH(C, l2n_fwd_kernel<NCH><<<blocks, kLnThreads, 0, (cudaStream_t)stream>>>(
@@ -643,6 +648,7 @@ extern "C" int exg_l2norm_bwd(const void* dy, int dy_dtype, const void* y, int y
                 "l2norm_bwd: bad dtype");
   EXG_CHECK_ARG(C > 0 && C % 4 == 0 && C <= 4096 && rowmap_ok(map_dx), "l2norm_bwd: bad C / map");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   int blocks = (int)((rows + 3) / 4);
   ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * (exg_dtype_size(dy_dtype) + exg_dtype_size(y_dtype) + exg_dtype_size(dx_dtype) * (accumulate ? 2 : 1)), stream);
   DISPATCH_NCH(C, l2n_bwd_kernel<NCH><<<blocks, kLnThreads, 0, (cudaStream_t)stream>>>(
@@ -705,6 +711,7 @@ extern "C" int exg_rowdot(const void* x, int x_dtype, const float* w, const floa
                           void* stream) {
   EXG_CHECK_ARG(x && w && y && exg_valid_dtype(x_dtype) && C > 0 && C % 4 == 0, "rowdot: bad argument");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * exg_dtype_size(x_dtype), stream);
   rowdot_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, x_dtype, w, bias, y, rows, C);
   EXG_LAUNCH_CHECK("rowdot");
@@ -715,6 +722,7 @@ extern "C" int exg_outer_rows(const float* g, const float* w, void* out, int out
                               void* stream) {
   EXG_CHECK_ARG(g && w && out && exg_valid_dtype(out_dtype) && C > 0 && C % 4 == 0, "outer_rows: bad argument");
   if (rows <= 0) return 0;
+  EXG_CHECK_ARG(rows <= EXG_MAX_ROWS, "row count exceeds 2^31 - 1");
   ExgProfScope prof(EXG_PC_ROWWISE, (double)rows * C * exg_dtype_size(out_dtype), stream);
   outer_rows_kernel<<<grid_for(rows * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(g, w, out, out_dtype, rows, C);
   EXG_LAUNCH_CHECK("outer_rows");
