@@ -552,6 +552,237 @@ attn_flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
   }
 }
 
+// ------------------------------------------------------------------------------------------ forward, version 3
+// Version 2 with 8 softmax warps (two per TMEM lane quarter): with 4 warps per CTA and two CTAs per SM every scheduler
+// had two softmax warps to pick from, 31 % of the issue slots were used and the XU pipe (ex2) sat at 38 %.
+constexpr int kFwd3Warps = 8;
+constexpr int FT3 = 32 * (kFwd3Warps + 1);
+__device__ __forceinline__ void fwd3_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ bool fwd3_bar_or(bool v) {
+  uint32_t r;
+  asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %1, 0;\n\tbar.red.or.pred q, 2, 256, p;\n\tselp.u32 %0, 1, 0, q;\n\t}"
+               : "=r"(r) : "r"((uint32_t)v) : "memory");
+  return r != 0;
+}
+
+__global__ void __launch_bounds__(FT3, 2)
+attn_flash_fwd3_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, AtcArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* Qs = smem; uint8_t* Ks = smem + kTile; uint8_t* Vs = Ks + kKvStages * kKvTile;
+  uint8_t* Ps = Vs + kKvStages * kKvTile;        // [2][128 rows][64 keys]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * kTile);
+  uint64_t *bar_q = bars, *bar_k = bars + 1 /* [3] */, *bar_v = bars + 4 /* [3] */, *bar_s = bars + 7 /* [2] */,
+           *bar_p = bars + 9 /* [2] */, *bar_pv = bars + 11 /* [2] */;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+  uint32_t* pv_acc = tmem_slot + 1;              // [2]: 1 = P_j V_j accumulates onto O in TMEM, 0 = it restarts O
+  float* xch = reinterpret_cast<float*>(tmem_slot + 4);      // [2][128]: row maxima / sums exchanged between the halves
+  uint32_t* maskw = tmem_slot + 4 + 256;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * TQ;
+  const int nt = (p.Sk + KT2 - 1) / KT2;
+  if (tid == 0) {
+    for (int i = 0; i < 13; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmO);
+  }
+  if (warp == kFwd3Warps) tmem_alloc(tmem_slot, 256);
+  build_mask_all(maskw, p, b, nt * 2, warp, lane, FT3 / 32);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem /* + 64 * buffer */, tO = tmem + 2 * KT2;
+
+  if (warp == kFwd3Warps) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar_q, kTile);
+      tma_load_3d(Qs, &tmQ, bar_q, h * HD, q0, b);
+      for (int j = 0; j < kKvStages && j < nt; ++j) {
+        mbar_arrive_expect_tx(&bar_k[j], kKvTile);
+        tma_load_3d(Ks + j * kKvTile, &tmK, &bar_k[j], h * HD, j * KT2, b);
+        mbar_arrive_expect_tx(&bar_v[j], kKvTile);
+        tma_load_3d(Vs + j * kKvTile, &tmV, &bar_v[j], h * HD, j * KT2, b);
+      }
+      mbar_wait(bar_q, 0);
+      for (int j = 0; j < 2 && j < nt; ++j) {    // S_0, S_1: both score buffers start free
+        mbar_wait(&bar_k[j], 0);
+        tc_fence_after();
+        mma_kmajor_k64(tS + j * KT2, smem_u32(Qs), smem_u32(Ks + j * kKvTile), KT2);
+        umma_commit(&bar_s[j]);
+      }
+      const uint32_t idesc_pv = umma_idesc_bf16(128, HD, 0, 1);
+      for (int j = 0; j < nt; ++j) {
+        const int bf = j & 1, st = j % kKvStages;
+        mbar_wait(&bar_p[bf], (j >> 1) & 1);     // P_j in smem, S_j consumed
+        const uint32_t acc = *reinterpret_cast<volatile uint32_t*>(&pv_acc[bf]);
+        mbar_wait(&bar_v[st], (j / kKvStages) & 1);
+        tc_fence_after();
+        // O (+)= P_j[128 x 64 keys] V_j[64 keys x 64]: A K-major, B MN-major
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          umma_bf16(tO, umma_smem_desc(smem_u32(Ps) + bf * kTile + k * 32, 16, 1024),
+                    umma_smem_desc(smem_u32(Vs) + st * kKvTile + k * 2048, 8192, 1024), idesc_pv, acc | (uint32_t)(k > 0));
+        umma_commit(&bar_pv[bf]);
+        if (j + 2 < nt) {                        // the score buffer S_j lived in takes S_{j+2}
+          const int s2 = (j + 2) % kKvStages;
+          mbar_wait(&bar_k[s2], ((j + 2) / kKvStages) & 1);
+          tc_fence_after();
+          mma_kmajor_k64(tS + bf * KT2, smem_u32(Qs), smem_u32(Ks + s2 * kKvTile), KT2);
+          umma_commit(&bar_s[bf]);
+        }
+        if (j + kKvStages < nt) {                // K stage of tile j: S_j completed before the softmax warps read it
+          mbar_arrive_expect_tx(&bar_k[st], kKvTile);
+          tma_load_3d(Ks + st * kKvTile, &tmK, &bar_k[st], h * HD, (j + kKvStages) * KT2, b);
+        }
+        if (j >= 1 && j + 2 < nt) {              // V stage of tile j-1 is free once P_{j-1} V_{j-1} has completed
+          mbar_wait(&bar_pv[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          const int sv = (j + 2) % kKvStages;    // == (j - 1) % 3
+          mbar_arrive_expect_tx(&bar_v[sv], kKvTile);
+          tma_load_3d(Vs + sv * kKvTile, &tmV, &bar_v[sv], h * HD, (j + 2) * KT2, b);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // 8 softmax warps: warps w and w + 4 share a TMEM lane quarter (query rows) and split every 64-key tile into two
+    // 32-key halves, and the 64 output columns into two 32-column halves.  The lazy reference maximum is what makes
+    // the halves independent: on an ordinary tile nothing crosses between them (partial row sums are added at the
+    // end); only an exact tile exchanges the half maxima through shared memory so that both keep the same m.
+    const int quarter = warp & 3, half = warp >> 2, row = quarter * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+    const float sl2 = p.scale * kLog2e;
+    float m = -INFINITY, l = 0.f;                  // l: this half's share of the row sum
+    float o[32];                                   // output columns [32 half, 32 half + 32)
+#pragma unroll
+    for (int i = 0; i < 32; ++i) o[i] = 0.f;
+    for (int j = 0; j < nt; ++j) {
+      const int bf = j & 1;
+      const uint32_t tSj = tS + bf * KT2 + half * 32;
+      uint8_t* Pj = Ps + bf * kTile;
+      mbar_wait(&bar_s[bf], (j >> 1) & 1);
+      if (j >= 2) mbar_wait(&bar_pv[bf], ((j - 2) >> 1) & 1);      // P buffer: P_{j-2} V_{j-2} has read it
+      tc_fence_after();
+      const uint32_t w = maskw[j * 2 + half];
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      float sm4[4] = {0.f, 0.f, 0.f, 0.f};
+      bool exact = j == 0;
+      uint32_t ra[32];
+      tmem_ld_32x32(tSj + lane_addr, ra);
+      tmem_ld_wait();
+      if (!exact) {
+        const float nb = -(m == -INFINITY ? 0.f : m) * sl2;
+        float pv[32];
+        if (w == 0xffffffffu) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float sv = __uint_as_float(ra[i]);
+            mx4[i & 3] = fmaxf(mx4[i & 3], sv);
+            pv[i] = ex2_approx(fmaf(sv, sl2, nb));
+            sm4[i & 3] += pv[i];
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float sv = __uint_as_float(ra[i]);
+            const bool on = (w >> i) & 1;
+            if (on) mx4[i & 3] = fmaxf(mx4[i & 3], sv);
+            pv[i] = on ? ex2_approx(fmaf(sv, sl2, nb)) : 0.f;
+            sm4[i & 3] += pv[i];
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          *reinterpret_cast<uint4*>(Pj + swz(row, half * 4 + u)) = pack8(&pv[u * 8]);
+        const float mt = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        const bool jump = mt != -INFINITY && (mt - m) * sl2 > kLazyLog2;
+        exact = fwd3_bar_or(jump);                 // CTA-uniform over the 256 softmax threads
+        if (!exact) l += (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if ((w >> i) & 1) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(ra[i]));
+      }
+      if (exact) {
+        // row maximum over both halves (the two warps of a row must keep the same reference)
+        xch[half * 128 + row] = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        fwd3_bar_sync();
+        const float mt = fmaxf(xch[row], xch[128 + row]);
+        fwd3_bar_sync();                           // both halves have read the pair before anyone overwrites it
+        const float m_new = fmaxf(m, mt);
+        const float msafe = m_new == -INFINITY ? 0.f : m_new;
+        const float alpha = ex2_approx((m - msafe) * sl2);        // m = -inf -> 0 (o and l are 0 then anyway)
+        m = m_new;
+        if (j > 0) {                                              // fold the O accumulated in TMEM since the last exact tile
+          mbar_wait(&bar_pv[(j - 1) & 1], ((j - 1) >> 1) & 1);
+          tc_fence_after();
+          uint32_t r[32];
+          tmem_ld_32x32(tO + lane_addr + half * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = (o[i] + __uint_as_float(r[i])) * alpha;
+        }
+        const float nb = -msafe * sl2;
+        sm4[0] = sm4[1] = sm4[2] = sm4[3] = 0.f;
+        float pv[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          pv[i] = ((w >> i) & 1) ? ex2_approx(fmaf(__uint_as_float(ra[i]), sl2, nb)) : 0.f;
+          sm4[i & 3] += pv[i];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          *reinterpret_cast<uint4*>(Pj + swz(row, half * 4 + u)) = pack8(&pv[u * 8]);
+        l = l * alpha + (sm4[0] + sm4[1]) + (sm4[2] + sm4[3]);
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      fwd3_bar_sync();
+      if (tid == 0) {
+        pv_acc[bf] = exact ? 0u : 1u;              // read by the producer after its acquire of bar_p[bf]
+        mbar_arrive(&bar_p[bf]);
+      }
+    }
+    // last tile's O, row sum over both halves, normalise, stage (the Q tile is dead), store
+    xch[half * 128 + row] = l;
+    mbar_wait(&bar_pv[(nt - 1) & 1], ((nt - 1) >> 1) & 1);
+    tc_fence_after();
+    fwd3_bar_sync();
+    const float lsum = xch[row] + xch[128 + row];
+    {
+      uint32_t r[32];
+      tmem_ld_32x32(tO + lane_addr + half * 32, r);
+      tmem_ld_wait();
+      const float inv = 1.0f / lsum;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = (o[u * 8 + i] + __uint_as_float(r[u * 8 + i])) * inv;
+        *reinterpret_cast<uint4*>(Qs + swz(row, half * 4 + u)) = pack8(f);
+      }
+    }
+    if (half == 0 && q0 + row < p.Sq && p.lse)
+      p.lse[((long)b * p.H + h) * p.Sq + q0 + row] = m * p.scale + __logf(lsum);
+    fence_proxy_async();
+    tc_fence_before();
+    fwd3_bar_sync();
+    if (tid == 0) {
+      tma_store_3d(&tmO, Qs, h * HD, q0, b);
+      bulk_commit();
+      bulk_wait_all();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kFwd3Warps) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
 // ------------------------------------------------------------------------------------------ backward
 // delta[b, h, q] = <dO[b, q, h, :], O[b, q, h, :]>; one warp per (clip, query) row, 4 lanes per head.
 __global__ void attn_delta_kernel(const uint16_t* __restrict__ o, const uint16_t* __restrict__ dout, long ldo,
@@ -848,17 +1079,22 @@ int exg_attn_flash_fwd(const void* q, const void* k, const void* v, long ldq, lo
   if ((rc = seq_map(&mv, v, B, Sk, H * HD, ldv, v1 ? 128 : KT2))) return rc;
   if ((rc = seq_map(&mo, o, B, Sq, H * HD, ldo))) return rc;
   if (!v1) {
-    static size_t cur2 = 0;
-    const size_t need2 = fwd_smem(Sk);           // same footprint: 96 KB of tiles + barriers + one mask word per 32 keys
-    if (need2 > cur2) {
-      cudaError_t e = cudaFuncSetAttribute(attn_flash_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need2);
-      if (e != cudaSuccess) { exg_set_error("attn_flash_fwd2: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
-      cur2 = need2;
+    // version 3 (8 softmax warps) unless EXG_FLASH_FWD_V2=1; + 1 KB for the half-row exchange buffer
+    static const int v2 = getenv("EXG_FLASH_FWD_V2") ? atoi(getenv("EXG_FLASH_FWD_V2")) : 0;
+    static size_t cur2 = 0, cur3 = 0;
+    const size_t need2 = fwd_smem(Sk) + (v2 ? 0 : 1024);
+    size_t& cur = v2 ? cur2 : cur3;
+    if (need2 > cur) {
+      cudaError_t e = v2 ? cudaFuncSetAttribute(attn_flash_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need2)
+                         : cudaFuncSetAttribute(attn_flash_fwd3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need2);
+      if (e != cudaSuccess) { exg_set_error("attn_flash_fwd: smem attribute: %s", cudaGetErrorString(e)); return (int)e; }
+      cur = need2;
     }
     AtcArgs a2 = {B, H, Sq, Sk, scale, key_pad, lse};
     dim3 grid2((Sq + TQ - 1) / TQ, H, B);
-    attn_flash_fwd2_kernel<<<grid2, FT, need2, (cudaStream_t)stream>>>(mq, mk, mv, mo, a2);
-    EXG_LAUNCH_CHECK("attn_flash_fwd2");
+    if (v2) attn_flash_fwd2_kernel<<<grid2, FT, need2, (cudaStream_t)stream>>>(mq, mk, mv, mo, a2);
+    else    attn_flash_fwd3_kernel<<<grid2, FT3, need2, (cudaStream_t)stream>>>(mq, mk, mv, mo, a2);
+    EXG_LAUNCH_CHECK("attn_flash_fwd");
     return 0;
   }
   static size_t cur = 0;
