@@ -182,3 +182,40 @@ def test_clip_retrieval_head_host_logic():
         pytest.skip("reference not present")
     from tests.retrieval_cases import run_retrieval_case
     run_retrieval_case("cpu", torch.float32)
+
+
+def test_warmup_cosine_schedule_matches_lambda_lr():
+    """train/schedule.py against torch's LambdaLR over the reference's lr_schedule_fn (main_egoexo4d_distributed.py:
+    832-843, restated here from its definition): same lr at every iteration the loop asks for, resume included."""
+    import functools
+    import math
+    import types
+    from exoground_b200.train.schedule import WarmupCosine, lr_multiplier
+
+    def lr_schedule_fn(iteration, iter_per_epoch, args):
+        if iteration < args.warmup_iterations:
+            return iteration / args.warmup_iterations
+        return 0.5 * (1. + math.cos(math.pi * (iteration - args.warmup_iterations)
+                                    / (args.epochs * iter_per_epoch - args.warmup_iterations)))
+    args = types.SimpleNamespace(warmup_iterations=7, epochs=3)
+    ipe, base = 11, 2e-4
+    opt = torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=base)
+    ref = torch.optim.lr_scheduler.LambdaLR(opt, functools.partial(lr_schedule_fn, iter_per_epoch=ipe, args=args))
+    tgt = types.SimpleNamespace(lr=None)
+    own = WarmupCosine(base, ipe, args.epochs, warmup_iterations=7, targets=[tgt])
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        ref.step(0)
+        assert own.get_last_lr()[0] == pytest.approx(ref.get_last_lr()[0], abs=1e-15)
+        for it in range(1, 3 * ipe + 1):
+            ref.step(it)
+            own.step(it)
+            assert own.get_last_lr()[0] == pytest.approx(ref.get_last_lr()[0], rel=1e-12, abs=1e-18), it
+            assert tgt.lr == own.get_last_lr()[0]
+    assert lr_multiplier(0, ipe, 3, 7) == 0.0 and lr_multiplier(3 * ipe, ipe, 3, 7) == pytest.approx(0.0, abs=1e-12)
+    resumed = WarmupCosine(base, ipe, args.epochs, warmup_iterations=7)
+    resumed.load_state_dict(own.state_dict())
+    assert resumed.get_last_lr() == own.get_last_lr()
+    own.step()                                     # argument-free step advances by one
+    assert own.last_epoch == 3 * ipe + 1
