@@ -371,14 +371,26 @@ def run_ours(a):
     # ---- end-to-end timing through the public step() call
     # the input pipeline is double-buffered: each step() also starts the H2D copy of the NEXT step's batch on the
     # copy stream (same synthetic batch object here), so every timed step contains one full H2D copy + loss read
+    # and the loss read-back is pipelined by one step (step_async: every step's loss is copied to pinned host memory and
+    # read by the host after the NEXT step has been launched; the last one is read inside the timed region too), so the
+    # GPU does not idle through the host's launch work.  --sync-loss restores the blocking step() per iteration.
     for _ in range(min(a.warmup, 3)):
         tr.step(batch, next_batch=batch)
     sync_all()
     t0 = time.perf_counter()
     e0.record()
     last = 0.0
-    for _ in range(a.steps):
-        last = tr.step(batch, next_batch=batch)
+    if a.sync_loss:
+        for _ in range(a.steps):
+            last = tr.step(batch, next_batch=batch)
+    else:
+        pending = None
+        for _ in range(a.steps):
+            h = tr.step_async(batch, next_batch=batch)
+            if pending is not None:
+                last = pending.result()
+            pending = h
+        last = pending.result()
     e1.record()
     sync_all()
     ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps
@@ -470,7 +482,9 @@ def run_ours(a):
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": dict(workload_config(world, a.xneg, a.batch, a.overlap, a.comm_chunks, a.grad_comm, a.host_dtype, not a.replicated_optimizer),
                                host_placement=a.placement),
                 "e2e": {"value": round(gb / (ms_e2e * 1e-3), 1), "unit": "clips/s", "ms_per_step": round(ms_e2e, 4),
-                        "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last},
+                        "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4, "last_loss": last,
+                        "loss_readback": "blocking, every step" if a.sync_loss else
+                                         "every step's loss, read one step late (TanTrainStep.step_async)"},
                 "gpu_launches": int(launches_per_step * a.steps),
                 "launches_per_step": int(launches_per_step), "cuda_graph": not a.no_graph,
                 "model_tflops": round(value / world * gf / 1e3, 1),
@@ -543,6 +557,9 @@ def main():
                          "all-reduce after it (measured: no gain, see DESIGN.md §6)")
     ap.add_argument("--comm-chunks", type=int, default=1,
                     help="N>1: chunks of the gradient all-reduce (AdamW of chunk i under the all-reduce of chunk i+1)")
+    ap.add_argument("--sync-loss", action="store_true",
+                    help="e2e leg: blocking TanTrainStep.step() (loss.item() every iteration) instead of the one-step "
+                         "pipelined read-back of step_async()")
     ap.add_argument("--replicated-optimizer", action="store_true",
                     help="N>1: all-reduce + every rank runs the whole AdamW (DistributedDataParallel's scheme) instead of "
                          "reduce-scatter -> AdamW on the owned shard -> all-gather of the bf16 weights")

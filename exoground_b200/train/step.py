@@ -151,6 +151,7 @@ class TanTrainStep:
         self._prepared = False
         self._hooked, self._reduced = False, 0
         self._gacc, self._acc_pending = None, False        # gradient accumulation (run(apply_update=False))
+        self._loss_ring, self._loss_slot = None, 0         # pinned slots of step_async()
 
     # ------------------------------------------------------------------ host -> device
     def _stage(self, batch, non_blocking=True):
@@ -552,6 +553,42 @@ class TanTrainStep:
         else:
             self._optimizer()
         return self.loss_out
+
+    class _PendingLoss:
+        """Handle of step_async(): the loss of that step, read back without stalling the stream."""
+
+        def __init__(self, host, event):
+            self._host, self._event = host, event
+
+        def result(self):
+            if self._event is not None:
+                self._event.synchronize()
+            return float(self._host.item())
+
+    def step_async(self, batch, next_batch=None, apply_update=True):
+        """step() without the host stall: the loss goes to a pinned host slot by an asynchronous copy and the call
+        returns a handle (`.result()` -> float).  A loop that reads the PREVIOUS step's handle after launching the next
+        step keeps the GPU busy through the host's launch work (the reference logs `loss.item()` every iteration,
+        train/main.py:120-126; reading it one step late changes nothing else).  Two slots: a handle must be read before
+        the second call after the one that produced it."""
+        if self._staged_id is not None and self._staged_id == id(batch):
+            self._take_staged()
+        else:
+            self.load_batch(batch)
+        loss = self.run(apply_update)
+        if next_batch is not None:
+            self.prefetch(next_batch)
+        if not self._on_cuda:
+            return TanTrainStep._PendingLoss(loss.detach().clone().cpu(), None)
+        if self._loss_ring is None:
+            self._loss_ring = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._loss_slot = 0
+        host = self._loss_ring[self._loss_slot]
+        self._loss_slot ^= 1
+        host.copy_(loss, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        return TanTrainStep._PendingLoss(host, ev)
 
     def step(self, batch, next_batch=None, apply_update=True):
         """The user-facing call: host batch in, python float loss out (H2D copies and the loss read-back

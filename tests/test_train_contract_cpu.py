@@ -45,3 +45,17 @@ def test_exo_step_device_loss_matches_get_loss(distill):
 
 def test_exo_step_gradient_accumulation():
     tc.check_exo_accumulation("cpu", torch.float32)
+
+
+def test_step_async_returns_the_same_loss_on_the_spec_backend():
+    from exoground_b200.train.step import TanTrainStep
+    from exoground_b200.utils import synth as sy
+    args = sy.tan_args(loss_threshold=0.0, use_alignability_head=0)
+    b = tc._batch()
+    losses = []
+    for mode in ("step", "async"):
+        m = tc._model(torch.float32)
+        m.random_pos_start = 0
+        tr = TanTrainStep(m, args, tc.B, tc.T, tc.N, tc.DIN, tc.DIN, device="cpu", use_graph=False)
+        losses.append(tr.step(b) if mode == "step" else tr.step_async(b).result())
+    assert losses[0] == pytest.approx(losses[1], rel=1e-6)

@@ -109,6 +109,36 @@ def test_prefetch_pipeline_matches_plain_steps():
     assert min(abs(a - b) for i, a in enumerate(runs[0]) for b in runs[0][i + 1:]) > 1e-2   # the batches really differ
 
 
+def test_step_async_pipelined_readback_matches_step():
+    """step_async(): the loss of step i read after step i+1 has been launched == the blocking step()."""
+    args = synth.tan_args(loss_threshold=0.0, use_alignability_head=0)
+    batches = [synth.tan_batch(B=B, T=T, N=N, d_video=DIN, d_text=DIN, seed=400 + i) for i in range(5)]
+    for b in batches:
+        for k in ("video", "text", "video_padding_mask", "text_padding_mask"):
+            b[k] = b[k].pin_memory()
+    runs = []
+    for mode in ("step", "async"):
+        m = _model(torch.bfloat16)
+        m.random_pos_start = 0
+        tr = TanTrainStep(m, args, B, T, N, DIN, DIN, lr=1e-3, eps=1e-4, use_graph=True)
+        out, pending = [], None
+        for i, b in enumerate(batches):
+            nb = batches[i + 1] if i + 1 < len(batches) else None
+            if mode == "step":
+                out.append(tr.step(b, next_batch=nb))
+            else:
+                h = tr.step_async(b, next_batch=nb)
+                if pending is not None:
+                    out.append(pending.result())
+                pending = h
+        if pending is not None:
+            out.append(pending.result())
+        runs.append(out)
+    assert len(runs[1]) == len(batches)
+    assert np.allclose(runs[0], runs[1], rtol=2e-3), runs
+    assert min(abs(a - b) for i, a in enumerate(runs[0]) for b in runs[0][i + 1:]) > 1e-2   # the batches really differ
+
+
 @pytest.mark.parametrize("dtype,use_graph", [(torch.float32, False), (torch.float32, True), (torch.bfloat16, True)])
 def test_branch_streams_match_single_stream(dtype, use_graph):
     """The joint-encoder branch on its own CUDA stream (forward and, through autograd's stream replay, backward) must
