@@ -124,8 +124,16 @@ def run_sweep(a):
 
         ms = timed(fwd, a.warmup, a.steps)
         bd = breakdown(fwd)
+        from exoground_b200.eval.graphed import GraphedSimilarity
+        gs = GraphedSimilarity(m, B, T, N, 1024, 4096)
+        with torch.no_grad():
+            want_j = m.get_text_visual_sim_joint(video, text)
+        got_j, _ = gs(video, text)
+        assert torch.equal(got_j, want_j), "graph replay differs from the eager helpers"
+        ms_g = timed(lambda: gs(video, text), a.warmup, a.steps)
         print(json.dumps({"config": "TAN E6D6 alignment-logit sweep (BASELINE configs[4])", "T": T, "N": N,
                           "videos_per_forward": B, "ms_per_forward": round(ms, 3),
+                          "ms_per_forward_graph": round(ms_g, 3), "videos_per_s_graph": round(B / (ms_g * 1e-3), 1),
                           "videos_per_s": round(B / (ms * 1e-3), 1),
                           "ms_80_videos": round(ms * int(np.ceil(total / B)), 2),
                           "attn_fwd": bd.get("attn_fwd"), "gemm_tc": bd.get("gemm_tc")}), flush=True)

@@ -92,3 +92,30 @@ def test_clip_retrieval_head(dt):
         pytest.skip("oracle/_ref archive missing")
     from tests.retrieval_cases import run_retrieval_case
     run_retrieval_case("cuda", dt)
+
+
+def test_graphed_similarity_matches_eager_helpers():
+    """eval/graphed.py: CUDA-graph replay of get_text_visual_sim_joint / _dual == the eager helpers, on new inputs after
+    the capture; shape changes and random offsets are refused."""
+    import pytest as _pytest
+    from exoground_b200.eval.graphed import GraphedSimilarity
+    from exoground_b200.model import TemporalAligner
+    torch.manual_seed(3)
+    m = TemporalAligner(2, 2, use_alignability_head=1, video_embed_dim=96, text_embed_dim=160, random_pos_start=0,
+                        compute_dtype=torch.bfloat16).cuda().eval()
+    B, T, N = 5, 128, 12
+    gs = GraphedSimilarity(m, B, T, N, 96, 160, interpolate_from=64)
+    for seed in (1, 2):
+        g = torch.Generator().manual_seed(seed)
+        video = torch.randn(B, T, 96, generator=g).cuda()
+        text = torch.randn(B, N, 160, generator=g).cuda()
+        with torch.no_grad():
+            want_j = m.get_text_visual_sim_joint(video, text, interpolate_from=64)
+            want_d = m.get_text_visual_sim_dual(video, text, interpolate_from=64)
+        got_j, got_d = gs(video, text)
+        assert torch.equal(got_j, want_j) and torch.equal(got_d, want_d)
+    with _pytest.raises(ValueError):
+        gs(video[:, :64], text)
+    m.random_pos_start = 1
+    with _pytest.raises(ValueError):
+        GraphedSimilarity(m, B, T, N, 96, 160)
